@@ -1,0 +1,84 @@
+"""ctypes binding of ``libgpsat_b200.so`` (the C ABI declared in ``include/gpsat_b200.h``).
+
+There is no CPU fallback: if the shared library is missing, or no B200 is visible when an engine
+is created, an exception is raised.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgpsat_b200.so")
+
+MEM_HOST = 0
+MEM_DEVICE = 1
+
+KERNEL_IDS = {"Matern12": 0, "Exponential": 0, "Matern32": 1, "Matern52": 2, "RBF": 3,
+              "SquaredExponential": 3}
+TRANSFORM_SOFTPLUS = 0
+TRANSFORM_SIGMOID = 1
+
+STATUS_OK, STATUS_NOT_PD, STATUS_LINESEARCH, STATUS_MAXITER, STATUS_BAD_INPUT = range(5)
+
+EXPORTED_SYMBOLS = (
+    "gpsat_version", "gpsat_last_error", "gpsat_engine_create", "gpsat_engine_destroy",
+    "gpsat_engine_stats", "gpsat_fit_options_default", "gpsat_gpr_lml_grad", "gpsat_gpr_fit",
+    "gpsat_gpr_predict", "gpsat_gpr_factor_debug",
+)
+
+
+class Batch(C.Structure):
+    _fields_ = [("kernel", C.c_int32), ("D", C.c_int32), ("E", C.c_int64),
+                ("off_n", C.c_void_p), ("off_m", C.c_void_p),
+                ("X", C.c_void_p), ("y", C.c_void_p), ("Xs", C.c_void_p)]
+
+
+class FitOptions(C.Structure):
+    _fields_ = [("pgtol", C.c_double), ("ftol", C.c_double), ("maxiter", C.c_int32),
+                ("maxfun", C.c_int32), ("maxls", C.c_int32), ("max_slots", C.c_int32)]
+
+
+class Stats(C.Structure):
+    _fields_ = [("kernel_launches", C.c_int64), ("ticks", C.c_int64), ("evals", C.c_int64),
+                ("slots", C.c_int64), ("h2d_bytes", C.c_double), ("d2h_bytes", C.c_double),
+                ("gpu_ms", C.c_double), ("sweep_flops", C.c_double)]
+
+
+_lib = None
+
+
+def load():
+    """Load the shared library (once).  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a). gpsat_b200 has no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    vp = C.c_void_p
+    lib.gpsat_version.restype = C.c_int
+    lib.gpsat_last_error.restype = C.c_char_p
+    lib.gpsat_engine_create.argtypes = [C.c_int, C.POINTER(vp)]
+    lib.gpsat_engine_destroy.argtypes = [vp]
+    lib.gpsat_engine_stats.argtypes = [vp, C.POINTER(Stats)]
+    lib.gpsat_fit_options_default.argtypes = [C.POINTER(FitOptions)]
+    lib.gpsat_fit_options_default.restype = None
+    lib.gpsat_gpr_lml_grad.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp]
+    lib.gpsat_gpr_fit.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp,
+                                  C.POINTER(FitOptions), vp, vp, vp, vp]
+    lib.gpsat_gpr_predict.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp, vp]
+    lib.gpsat_gpr_factor_debug.argtypes = [vp, C.POINTER(Batch), vp, vp, vp]
+    _lib = lib
+    return lib
+
+
+def last_error() -> str:
+    return load().gpsat_last_error().decode()
+
+
+def check(rc: int):
+    if rc != 0:
+        raise RuntimeError(f"libgpsat_b200 call failed (rc={rc}): {last_error()}")

@@ -1,0 +1,201 @@
+// C ABI entry points (include/gpsat_b200.h).  Included at the end of engine_host.inl.
+using namespace gpsat;
+
+struct gpsat_engine { Engine e; };
+
+extern "C" {
+
+int gpsat_version(void) { return 100; }
+const char* gpsat_last_error(void) { return g_last_error.c_str(); }
+
+void gpsat_fit_options_default(gpsat_fit_options* o) {
+  o->pgtol = 1e-5;
+  o->ftol = 2.220446049250313e-09;
+  o->maxiter = 10000;
+  o->maxfun = 15000;
+  o->maxls = 20;
+  o->max_slots = 0;
+}
+
+int gpsat_engine_create(int device, gpsat_engine** out) {
+  REQUIRE(out != nullptr, "out is NULL");
+  int count = 0;
+  CUDA_TRY(cudaGetDeviceCount(&count));
+  REQUIRE(device >= 0 && device < count, "no such CUDA device");
+  CUDA_TRY(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  REQUIRE(prop.major == 10, "libgpsat_b200 is built for sm_100a (B200) only");
+  gpsat_engine* h = new gpsat_engine();
+  h->e.device = device;
+  CUDA_TRY(cudaStreamCreateWithFlags(&h->e.stream, cudaStreamNonBlocking));
+  CUDA_TRY(cudaEventCreate(&h->e.ev0));
+  CUDA_TRY(cudaEventCreate(&h->e.ev1));
+  CUDA_TRY(cudaMallocHost(&h->e.h_counters, 4 * sizeof(int)));
+  if (engine_setup_kernels()) { delete h; return 1; }
+  *out = h;
+  return 0;
+}
+
+int gpsat_engine_destroy(gpsat_engine* h) {
+  if (!h) return 0;
+  Engine& g = h->e;
+  cudaSetDevice(g.device);
+  cudaStreamSynchronize(g.stream);
+  for (DevBuf* b : {&g.bX, &g.by, &g.bXs, &g.boffn, &g.boffm, &g.border, &g.btheta, &g.bmisc, &g.bslots,
+                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout})
+    b->release();
+  if (g.h_counters) cudaFreeHost(g.h_counters);
+  cudaEventDestroy(g.ev0); cudaEventDestroy(g.ev1);
+  cudaStreamDestroy(g.stream);
+  delete h;
+  return 0;
+}
+
+int gpsat_engine_stats(const gpsat_engine* h, gpsat_stats* out) {
+  REQUIRE(h && out, "NULL argument");
+  *out = h->e.stats;
+  return 0;
+}
+
+// ---- helpers for host<->device staging of small per-expert arrays ---------------------------
+static int stage_in(Engine& g, int mem, const void* src, size_t bytes, void* dev_dst, const void** out) {
+  if (mem == GPSAT_MEM_DEVICE) { *out = src; return 0; }
+  CUDA_TRY(cudaMemcpyAsync(dev_dst, src, bytes, cudaMemcpyHostToDevice, g.stream));
+  g.stats.h2d_bytes += (double)bytes;
+  *out = dev_dst;
+  return 0;
+}
+
+static void begin_call(Engine& g) {
+  cudaSetDevice(g.device);
+  g.stats = gpsat_stats{};
+  cudaEventRecord(g.ev0, g.stream);
+}
+static int end_call(Engine& g) {
+  CUDA_TRY(cudaEventRecord(g.ev1, g.stream));
+  CUDA_TRY(cudaStreamSynchronize(g.stream));
+  float ms = 0.f;
+  CUDA_TRY(cudaEventElapsedTime(&ms, g.ev0, g.ev1));
+  g.stats.gpu_ms = ms;
+  return 0;
+}
+
+// ---- lml + gradient at fixed theta ----------------------------------------------------------
+int gpsat_gpr_lml_grad(gpsat_engine* h, const gpsat_batch* batch, int mem, const double* theta, double* lml,
+                       double* grad, int32_t* status) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  if (check_batch(batch, false)) return 2;
+  REQUIRE(theta != nullptr && lml != nullptr, "theta / lml is NULL");
+  Engine& g = h->e;
+  begin_call(g);
+  const int64_t E = batch->E;
+  if (E == 0) return end_call(g);
+  const int P = batch->D + 2;
+  BatchDev bd;
+  if (engine_load_batch(g, batch, mem, false, bd)) return 1;
+  const int S = choose_slots(g, E, g.Tmax, g.Tmax, 0);
+  int ld = 0;
+  if (engine_alloc_slots(g, S, g.Tmax, g.Tmax, ld)) return 1;
+  // device-side theta / outputs
+  size_t o_theta = 0, o_lml = (size_t)E * P * 8, o_grad = o_lml + (size_t)E * 8, o_status = o_grad + (size_t)E * P * 8;
+  if (g.bout.ensure(o_status + (size_t)E * 4)) return 1;
+  char* base = g.bout.as<char>();
+  const void* dtheta = nullptr;
+  if (stage_in(g, mem, theta, (size_t)E * P * 8, base + o_theta, &dtheta)) return 1;
+  double* dlml = mem == GPSAT_MEM_DEVICE ? lml : reinterpret_cast<double*>(base + o_lml);
+  double* dgrad = grad ? (mem == GPSAT_MEM_DEVICE ? grad : reinterpret_cast<double*>(base + o_grad)) : nullptr;
+  int* dstatus = status ? (mem == GPSAT_MEM_DEVICE ? status : reinterpret_cast<int*>(base + o_status)) : nullptr;
+  SlotDesc* slots = g.bslots.as<SlotDesc>();
+  const SlotMem* mems = g.bmems.as<SlotMem>();
+  for (int64_t b0 = 0; b0 < E; b0 += S) {
+    int Tb = (int)((g.hn[g.order[b0]] + 1 + NB - 1) / NB);
+    eval_init_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(slots, mems, bd, (const double*)dtheta, (int)b0, S, 0, ld);
+    if (launch_sweep(g, S, Tb, Tb, grad != nullptr)) return 1;
+    eval_finish_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(slots, bd, (const double*)dtheta, dlml, dgrad, dstatus, S);
+    g.stats.kernel_launches += 2;
+    g.stats.ticks++;
+  }
+  for (int64_t e = 0; e < E; ++e) g.stats.sweep_flops += (grad ? 1.0 : 1.0 / 3.0) * (double)g.hn[e] * g.hn[e] * g.hn[e];
+  g.stats.evals = E; g.stats.slots = S;
+  if (mem == GPSAT_MEM_HOST) {
+    CUDA_TRY(cudaMemcpyAsync(lml, dlml, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
+    if (grad) CUDA_TRY(cudaMemcpyAsync(grad, dgrad, (size_t)E * P * 8, cudaMemcpyDeviceToHost, g.stream));
+    if (status) CUDA_TRY(cudaMemcpyAsync(status, dstatus, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
+    g.stats.d2h_bytes += (double)E * (8 + (grad ? P * 8 : 0) + (status ? 4 : 0));
+  }
+  CUDA_TRY(cudaGetLastError());
+  return end_call(g);
+}
+
+// ---- prediction at fixed theta --------------------------------------------------------------
+int gpsat_gpr_predict(gpsat_engine* h, const gpsat_batch* batch, int mem, const double* theta, double* fmean,
+                      double* fvar, double* yvar, double* lml, int32_t* status) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  if (check_batch(batch, true)) return 2;
+  REQUIRE(theta && fmean && fvar && yvar, "theta / output is NULL");
+  Engine& g = h->e;
+  begin_call(g);
+  const int64_t E = batch->E;
+  if (E == 0) return end_call(g);
+  const int P = batch->D + 2;
+  const int64_t M = batch->off_m[E];
+  BatchDev bd;
+  if (engine_load_batch(g, batch, mem, true, bd)) return 1;
+  const int S = choose_slots(g, E, g.Tmax, g.TRmax, 0);
+  int ld = 0;
+  if (engine_alloc_slots(g, S, g.Tmax, g.TRmax, ld)) return 1;
+  size_t o_theta = 0, o_lml = (size_t)E * P * 8, o_status = o_lml + (size_t)E * 8;
+  size_t o_pred = (o_status + (size_t)E * 4 + 15) & ~(size_t)15;
+  if (g.bout.ensure(o_pred + (size_t)std::max<int64_t>(M, 1) * 3 * 8)) return 1;
+  char* base = g.bout.as<char>();
+  const void* dtheta = nullptr;
+  if (stage_in(g, mem, theta, (size_t)E * P * 8, base + o_theta, &dtheta)) return 1;
+  const bool dev = mem == GPSAT_MEM_DEVICE;
+  double* dlml = lml ? (dev ? lml : reinterpret_cast<double*>(base + o_lml)) : nullptr;
+  int* dstatus = status ? (dev ? status : reinterpret_cast<int*>(base + o_status)) : nullptr;
+  double* dfm = dev ? fmean : reinterpret_cast<double*>(base + o_pred);
+  double* dfv = dev ? fvar : dfm + M;
+  double* dyv = dev ? yvar : dfv + M;
+  SlotDesc* slots = g.bslots.as<SlotDesc>();
+  const SlotMem* mems = g.bmems.as<SlotMem>();
+  for (int64_t b0 = 0; b0 < E; b0 += S) {
+    int Tb = 0, TRb = 0; int64_t mb = 0;
+    for (int64_t k = b0; k < std::min<int64_t>(E, b0 + S); ++k) {
+      int e = g.order[k];
+      Tb = std::max(Tb, (int)((g.hn[e] + 1 + NB - 1) / NB));
+      TRb = std::max(TRb, (int)((g.hn[e] + 1 + g.hm[e] + NB - 1) / NB));
+      mb = std::max(mb, g.hm[e]);
+    }
+    eval_init_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(slots, mems, bd, (const double*)dtheta, (int)b0, S, 1, ld);
+    if (launch_sweep(g, S, Tb, TRb, false)) return 1;
+    if (mb > 0) {
+      predict_reduce_kernel<<<dim3((unsigned)((mb * 32 + 255) / 256), S), 256, 0, g.stream>>>(slots, bd.off_m, dfm, dfv, dyv);
+      g.stats.kernel_launches++;
+    }
+    eval_finish_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(slots, bd, (const double*)dtheta, dlml, nullptr, dstatus, S);
+    g.stats.kernel_launches += 2;
+    g.stats.ticks++;
+  }
+  for (int64_t e = 0; e < E; ++e) {
+    double n = (double)g.hn[e];
+    g.stats.sweep_flops += n * n * n / 3.0 + n * n * (double)g.hm[e];
+  }
+  g.stats.evals = E; g.stats.slots = S;
+  if (!dev) {
+    if (M > 0) {
+      CUDA_TRY(cudaMemcpyAsync(fmean, dfm, (size_t)M * 8, cudaMemcpyDeviceToHost, g.stream));
+      CUDA_TRY(cudaMemcpyAsync(fvar, dfv, (size_t)M * 8, cudaMemcpyDeviceToHost, g.stream));
+      CUDA_TRY(cudaMemcpyAsync(yvar, dyv, (size_t)M * 8, cudaMemcpyDeviceToHost, g.stream));
+    }
+    if (lml) CUDA_TRY(cudaMemcpyAsync(lml, dlml, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
+    if (status) CUDA_TRY(cudaMemcpyAsync(status, dstatus, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
+    g.stats.d2h_bytes += (double)M * 24 + (double)E * 12;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return end_call(g);
+}
+
+}  // extern "C"
+
+#include "engine_fit.inl"

@@ -1,0 +1,174 @@
+// Host-side engine: memory, launch sequences, C ABI.  Included at the end of engine.cu.
+namespace gpsat {
+
+struct DevBuf {
+  void* p = nullptr;
+  size_t cap = 0;
+  int ensure(size_t bytes) {
+    if (bytes <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = bytes + (bytes >> 3);
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { cudaGetLastError(); e = cudaMalloc(&p, bytes); want = bytes; }
+    if (e != cudaSuccess) {
+      g_last_error = std::string("cudaMalloc(") + std::to_string(bytes) + "): " + cudaGetErrorString(e);
+      return 1;
+    }
+    cap = want;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct Engine {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  int* h_counters = nullptr;          // pinned [4]
+  DevBuf bX, by, bXs, boffn, boffm, border, btheta, bmisc, bslots, bmems, bA, bside, bstates, bout;
+  gpsat_stats stats{};
+  // host copy of the current batch shape
+  std::vector<int64_t> hn, hm;
+  std::vector<int> order;
+  int Tmax = 0, TRmax = 0;
+};
+
+static int align_up(int v, int a) { return (v + a - 1) / a * a; }
+
+static int engine_setup_kernels() {
+  CUDA_TRY(cudaFuncSetAttribute(diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DIAG_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STEP_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(lauum_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_SMEM_BYTES));
+  return 0;
+}
+
+static int check_batch(const gpsat_batch* b, bool need_pred) {
+  REQUIRE(b != nullptr, "batch is NULL");
+  REQUIRE(b->kernel >= 0 && b->kernel <= 3, "unknown kernel id");
+  REQUIRE(b->D >= 1 && b->D <= GPSAT_MAX_DIMS, "D out of range [1, 6]");
+  REQUIRE(b->E >= 0, "E < 0");
+  REQUIRE(b->off_n != nullptr, "off_n is NULL");
+  REQUIRE(b->E == 0 || (b->X != nullptr && b->y != nullptr), "X / y is NULL");
+  for (int64_t e = 0; e < b->E; ++e) {
+    REQUIRE(b->off_n[e + 1] >= b->off_n[e], "off_n must be non-decreasing");
+    REQUIRE(b->off_n[e + 1] - b->off_n[e] >= 1, "every expert needs at least one observation");
+    REQUIRE(b->off_n[e + 1] - b->off_n[e] < (1 << 20), "expert too large");
+  }
+  if (need_pred) {
+    REQUIRE(b->off_m != nullptr, "off_m is NULL");
+    REQUIRE(b->off_m[b->E] == 0 || b->Xs != nullptr, "Xs is NULL");
+    for (int64_t e = 0; e < b->E; ++e) REQUIRE(b->off_m[e + 1] >= b->off_m[e], "off_m must be non-decreasing");
+  }
+  return 0;
+}
+
+// Bring the batch to the device (or adopt device pointers) and build the size-sorted order.
+static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with_pred, BatchDev& out) {
+  const int64_t E = b->E;
+  const int D = b->D;
+  g.hn.resize(E); g.hm.assign(E, 0);
+  int64_t nmax = 0;
+  for (int64_t e = 0; e < E; ++e) { g.hn[e] = b->off_n[e + 1] - b->off_n[e]; nmax = std::max(nmax, g.hn[e]); }
+  if (with_pred) for (int64_t e = 0; e < E; ++e) g.hm[e] = b->off_m[e + 1] - b->off_m[e];
+  g.order.resize(E);
+  std::iota(g.order.begin(), g.order.end(), 0);
+  std::stable_sort(g.order.begin(), g.order.end(), [&](int a, int c) { return g.hn[a] > g.hn[c]; });
+  g.Tmax = 0; g.TRmax = 0;
+  for (int64_t e = 0; e < E; ++e) {
+    g.Tmax = std::max(g.Tmax, (int)((g.hn[e] + 1 + NB - 1) / NB));
+    g.TRmax = std::max(g.TRmax, (int)((g.hn[e] + 1 + g.hm[e] + NB - 1) / NB));
+  }
+  const int64_t N = b->off_n[E], M = with_pred ? b->off_m[E] : 0;
+  if (g.boffn.ensure((E + 1) * 8) || g.boffm.ensure((E + 1) * 8) || g.border.ensure(std::max<int64_t>(E, 1) * 4)) return 1;
+  CUDA_TRY(cudaMemcpyAsync(g.boffn.p, b->off_n, (E + 1) * 8, cudaMemcpyHostToDevice, g.stream));
+  if (with_pred) CUDA_TRY(cudaMemcpyAsync(g.boffm.p, b->off_m, (E + 1) * 8, cudaMemcpyHostToDevice, g.stream));
+  CUDA_TRY(cudaMemcpyAsync(g.border.p, g.order.data(), E * 4, cudaMemcpyHostToDevice, g.stream));
+  g.stats.h2d_bytes += (double)(E + 1) * 8 * (with_pred ? 2 : 1) + E * 4;
+  out.kind = b->kernel; out.D = D; out.P = D + 2; out.E = E;
+  out.off_n = g.boffn.as<int64_t>();
+  out.off_m = with_pred ? g.boffm.as<int64_t>() : nullptr;
+  out.order = g.border.as<int>();
+  if (mem == GPSAT_MEM_DEVICE) {
+    out.X = b->X; out.y = b->y; out.Xs = b->Xs;
+  } else {
+    if (g.bX.ensure(std::max<int64_t>(N * D, 1) * 8) || g.by.ensure(std::max<int64_t>(N, 1) * 8)) return 1;
+    CUDA_TRY(cudaMemcpyAsync(g.bX.p, b->X, N * D * 8, cudaMemcpyHostToDevice, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(g.by.p, b->y, N * 8, cudaMemcpyHostToDevice, g.stream));
+    g.stats.h2d_bytes += (double)N * (D + 1) * 8;
+    out.X = g.bX.as<double>(); out.y = g.by.as<double>(); out.Xs = nullptr;
+    if (with_pred && M > 0) {
+      if (g.bXs.ensure(M * D * 8)) return 1;
+      CUDA_TRY(cudaMemcpyAsync(g.bXs.p, b->Xs, M * D * 8, cudaMemcpyHostToDevice, g.stream));
+      g.stats.h2d_bytes += (double)M * D * 8;
+      out.Xs = g.bXs.as<double>();
+    }
+  }
+  return 0;
+}
+
+// Carve per-slot scratch for S slots with `rows` x `ld` matrices.
+static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out) {
+  const int ld = Tmax * NB;
+  const size_t rows = (size_t)TRmax * NB;
+  const size_t a_d = rows * ld;
+  const size_t tile_d = (size_t)Tmax * NB * NB;
+  const size_t ntile = (size_t)Tmax * (Tmax + 1) / 2;
+  size_t side_d = 2 * tile_d + align_up(Tmax, 2) + 2 + ntile * PG + 2;   // Wd, Ld, logdet, quad, gpart, notpd
+  side_d = (side_d + 1) & ~(size_t)1;
+  if (g.bA.ensure(a_d * 8 * S) || g.bside.ensure(side_d * 8 * S) || g.bslots.ensure(sizeof(SlotDesc) * S) ||
+      g.bmems.ensure(sizeof(SlotMem) * S))
+    return 1;
+  std::vector<SlotMem> mems(S);
+  for (int s = 0; s < S; ++s) {
+    double* sd = g.bside.as<double>() + side_d * s;
+    SlotMem& m = mems[s];
+    m.A = g.bA.as<double>() + a_d * s;
+    m.Wd = sd;
+    m.Ld = sd + tile_d;
+    m.logdet = sd + 2 * tile_d;
+    m.quad = m.logdet + align_up(Tmax, 2);
+    m.gpart = m.quad + 2;
+    m.notpd = reinterpret_cast<int*>(m.gpart + ntile * PG);
+  }
+  CUDA_TRY(cudaMemcpyAsync(g.bmems.p, mems.data(), sizeof(SlotMem) * S, cudaMemcpyHostToDevice, g.stream));
+  CUDA_TRY(cudaStreamSynchronize(g.stream));   // `mems` is a stack-lifetime source
+  ld_out = ld;
+  return 0;
+}
+
+static int choose_slots(Engine& g, int64_t E, int Tmax, int TRmax, int max_slots) {
+  size_t free_b = 0, total_b = 0;
+  cudaMemGetInfo(&free_b, &total_b);
+  size_t per = (size_t)TRmax * NB * Tmax * NB * 8 + (size_t)2 * Tmax * NB * NB * 8 + (1 << 16);
+  size_t avail = (size_t)((free_b + g.bA.cap + g.bside.cap) * 0.80);
+  int64_t S = max_slots > 0 ? max_slots : 296;
+  S = std::min<int64_t>(S, E);
+  S = std::min<int64_t>(S, (int64_t)(avail / per));
+  return (int)std::max<int64_t>(S, 1);
+}
+
+// One blocked sweep over all occupied slots.
+static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv) {
+  const SlotDesc* slots = g.bslots.as<SlotDesc>();
+  for (int i = 0; i < Tmax; ++i) {
+    diag_kernel<<<S, GPSAT_THREADS, DIAG_SMEM_BYTES, g.stream>>>(slots, i);
+    g.stats.kernel_launches++;
+    int ntile = (TRmax - 1 - i) + (do_inv ? i : 0);
+    if (ntile > 0) {
+      step_kernel<<<dim3(ntile, S), GPSAT_THREADS, STEP_SMEM_BYTES, g.stream>>>(slots, i, do_inv ? 1 : 0);
+      g.stats.kernel_launches++;
+    }
+  }
+  if (do_inv) {
+    lauum_grad_kernel<<<dim3(Tmax * (Tmax + 1) / 2, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots);
+    g.stats.kernel_launches++;
+  }
+  CUDA_TRY(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace gpsat
+
+#include "engine_api.inl"

@@ -1,0 +1,141 @@
+// lauum_grad_kernel: Ks^-1 = U U^T tile by tile, contracted at once with dKs/dtheta so that the
+// inverse is never written to memory.  Output: per-tile partial sums
+//   gpart[tile][d]     = sum w Q_ab gunit_ab sdiff_d^2      (d < D)       -> d lml/d l_d = var/(2 l_d) * sum
+//   gpart[tile][D]     = sum w Q_ab kunit_ab                               -> d lml/d var = 1/2 * sum
+//   gpart[tile][D + 1] = sum_a Q_aa                                        -> d lml/d s2  = 1/2 * sum
+// with Q = alpha alpha^T - Ks^-1 and w = 2 off the diagonal (lower triangle only), 1 on it.
+// (analytic form of the gradient TensorFlow autodiff produces for training_loss,
+//  GPSat/models/gpflow_models.py:317-321)
+#pragma once
+#include "tiles.cuh"
+
+namespace gpsat {
+
+__global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const SlotDesc* __restrict__ slots) {
+  const SlotDesc& d = slots[blockIdx.y];
+  if (d.expert < 0) return;
+  const int T = d.T;
+  const int t = blockIdx.x;
+  if (t >= T * (T + 1) / 2) return;
+  int i = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+  while (i * (i + 1) / 2 > t) --i;
+  while ((i + 1) * (i + 2) / 2 <= t) ++i;
+  const int j = t - i * (i + 1) / 2;
+
+  extern __shared__ double smem[];
+  double* stages = smem;
+  double* xr = smem + NSTAGE * STAGE_D;
+  double* xc = xr + NB * GPSAT_DMAX;
+  double* ar = xc + NB * GPSAT_DMAX;     // alpha of the row block
+  double* ac = ar + NB;                  // alpha of the column block
+  double* red = ac + NB;                 // [8 warps][8]
+  const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
+  const int lr = lane >> 2, lk = lane & 3;
+  const int n = d.n, ld = d.ld, D = d.D;
+
+  load_block_coords(d, i * NB, xr, ar, tid);      // ar / ac overwritten with alpha below
+  load_block_coords(d, j * NB, xc, ac, tid);
+  __syncthreads();
+  for (int r = tid; r < NB; r += GPSAT_THREADS) {
+    int gi = i * NB + r, gj = j * NB + r;
+    ar[r] = (gi < n) ? -d.A[(size_t)gi * ld + n] : 0.0;
+    ac[r] = (gj < n) ? -d.A[(size_t)gj * ld + n] : 0.0;
+  }
+
+  Acc acc;
+  acc_zero(acc);
+  const int kend = ((n + 1 + KC - 1) / KC) * KC;     // includes column n (the -alpha column)
+  gemm_nt_mainloop(acc, d.A + (size_t)i * NB * ld, d.A + (size_t)j * NB * ld, ld, i * NB, kend, stages, tid);
+  __syncthreads();
+
+  double part[GPSAT_DMAX + 2];
+#pragma unroll
+  for (int p = 0; p < GPSAT_DMAX + 2; ++p) part[p] = 0.0;
+#pragma unroll
+  for (int fm = 0; fm < 8; ++fm)
+#pragma unroll
+    for (int fn = 0; fn < 4; ++fn)
+#pragma unroll
+      for (int e = 0; e < 2; ++e) {
+        int r = wm * 64 + fm * 8 + lr, c = wn * 32 + fn * 8 + 2 * lk + e;
+        int gi = i * NB + r, gj = j * NB + c;
+        if (gi >= n || gj >= n || gj > gi) continue;
+        double aa = ar[r] * ac[c];
+        // acc = Ks^-1 + alpha alpha^T (column n of U is -alpha)
+        double q = aa - (acc.c[fm][fn][e] - aa);
+        double w = (gi == gj) ? 1.0 : 2.0;
+        double r2 = 0.0, sd[GPSAT_DMAX];
+#pragma unroll
+        for (int dd = 0; dd < GPSAT_DMAX; ++dd) {
+          double tdiff = (dd < D) ? xr[r * GPSAT_DMAX + dd] - xc[c * GPSAT_DMAX + dd] : 0.0;
+          sd[dd] = tdiff * tdiff;
+          r2 += sd[dd];
+        }
+        double ku, gu;
+        kunit_gunit_dyn(d.kind, r2, ku, gu);
+        double wq = w * q;
+#pragma unroll
+        for (int dd = 0; dd < GPSAT_DMAX; ++dd) part[dd] += wq * gu * sd[dd];
+        part[GPSAT_DMAX] += wq * ku;
+        if (gi == gj) part[GPSAT_DMAX + 1] += q;
+      }
+  // deterministic block reduction: warp shuffle tree, then warp 0 adds the 8 warp sums in order
+#pragma unroll
+  for (int p = 0; p < GPSAT_DMAX + 2; ++p) {
+    double v = part[p];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (lane == 0) red[warp * 8 + p] = v;
+  }
+  __syncthreads();
+  if (tid < GPSAT_DMAX + 2) {
+    double v = 0.0;
+    for (int w8 = 0; w8 < 8; ++w8) v += red[w8 * 8 + tid];
+    d.gpart[(size_t)t * (GPSAT_DMAX + 2) + tid] = v;
+  }
+}
+
+// predict_reduce_kernel: one warp per prediction row s:  f* = <A_s, a>, f*_var = var - |A_s|^2,
+// y_var = f*_var + s2, with A_s = row n+1+s of the factored matrix (= (L^-1 k_s)^T) and
+// a = row n (= (L^-1 y)^T).   Reference: GPR.predict_f / predict_y called at
+// GPSat/models/gpflow_models.py:229-230.
+__global__ void predict_reduce_kernel(const SlotDesc* __restrict__ slots, const int64_t* __restrict__ off_m,
+                                      double* __restrict__ fmean, double* __restrict__ fvar,
+                                      double* __restrict__ yvar) {
+  const SlotDesc& d = slots[blockIdx.y];
+  if (d.expert < 0) return;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= d.m) return;
+  const int n = d.n, ld = d.ld;
+  const int g = n + 1 + warp;
+  const double* As = d.A + (size_t)g * ld;
+  const double* a = d.A + (size_t)n * ld;
+  // columns of the last factored block: rows of block row T-1 (the y row, and the first few
+  // prediction rows) keep their L entries in the diagonal side buffer, not in the slot matrix
+  const int c0 = (d.T - 1) * NB;
+  const double* Ldt = d.Ld + (size_t)(d.T - 1) * NB * NB;
+  const double* a_last = Ldt + (size_t)(n - c0) * NB;
+  const double* As_last = (g < d.T * NB) ? Ldt + (size_t)(g - c0) * NB : nullptr;
+  double s1 = 0.0, s2 = 0.0;
+  for (int k = lane; k < c0; k += 32) { double v = As[k]; s1 += v * a[k]; s2 += v * v; }
+  for (int k = c0 + lane; k < n; k += 32) {
+    double v = As_last ? As_last[k - c0] : As[k];
+    s1 += v * a_last[k - c0];
+    s2 += v * v;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  }
+  if (lane == 0) {
+    int64_t o = off_m[d.expert] + warp;
+    double fv = d.var - s2;
+    fmean[o] = s1;
+    fvar[o] = fv;
+    yvar[o] = fv + d.noise;
+  }
+}
+
+}  // namespace gpsat

@@ -1,0 +1,239 @@
+"""NumPy / torch facing wrapper around the C ABI (one :class:`Engine` per GPU rank).
+
+``RaggedBatch`` is the on-wire format between the driver and the engine: experts packed back to
+back, described by ``off_n`` / ``off_m`` (see ``include/gpsat_b200.h``).  Host arrays go through
+the library's own host<->device copies (the end-to-end path); torch CUDA tensors are passed as
+device pointers (inputs resident in HBM).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+
+SCIPY_FTOL = 2.220446049250313e-09
+
+
+def _is_torch(x) -> bool:
+    return type(x).__module__.startswith("torch")
+
+
+def _ptr(x):
+    if x is None:
+        return None
+    if _is_torch(x):
+        return C.c_void_p(x.data_ptr())
+    return C.c_void_p(x.ctypes.data)
+
+
+def _f64(x, shape=None):
+    a = np.ascontiguousarray(x, dtype=np.float64)
+    if shape is not None:
+        a = a.reshape(shape)
+    return a
+
+
+@dataclass
+class RaggedBatch:
+    """Packed experts.  ``X`` [N, D], ``y`` [N], ``Xs`` [M, D] are either all NumPy (host) or all
+    torch CUDA float64 tensors (device); ``off_n`` / ``off_m`` are host int64 arrays."""
+    kernel: str
+    D: int
+    off_n: np.ndarray
+    X: object
+    y: object
+    off_m: Optional[np.ndarray] = None
+    Xs: object = None
+    _keep: list = field(default_factory=list, repr=False)
+
+    @property
+    def E(self) -> int:
+        return len(self.off_n) - 1
+
+    @property
+    def on_device(self) -> bool:
+        return _is_torch(self.X)
+
+    @property
+    def n(self) -> np.ndarray:
+        return np.diff(self.off_n)
+
+    @property
+    def m(self) -> np.ndarray:
+        return np.diff(self.off_m) if self.off_m is not None else np.zeros(self.E, np.int64)
+
+    @classmethod
+    def from_lists(cls, kernel: str, Xs_obs: Sequence[np.ndarray], ys: Sequence[np.ndarray],
+                   Xs_pred: Optional[Sequence[np.ndarray]] = None) -> "RaggedBatch":
+        assert len(Xs_obs) == len(ys)
+        E = len(Xs_obs)
+        D = int(np.atleast_2d(Xs_obs[0]).shape[1]) if E else 1
+        off_n = np.zeros(E + 1, np.int64)
+        off_n[1:] = np.cumsum([len(a) for a in Xs_obs])
+        X = _f64(np.concatenate([_f64(a, (-1, D)) for a in Xs_obs], axis=0)) if E else np.zeros((0, D))
+        y = _f64(np.concatenate([_f64(a).ravel() for a in ys])) if E else np.zeros(0)
+        assert len(y) == off_n[-1], "obs / coords length mismatch"
+        off_m, XS = None, None
+        if Xs_pred is not None:
+            assert len(Xs_pred) == E
+            off_m = np.zeros(E + 1, np.int64)
+            off_m[1:] = np.cumsum([len(a) for a in Xs_pred])
+            XS = _f64(np.concatenate([_f64(a, (-1, D)) for a in Xs_pred], axis=0)) if E else np.zeros((0, D))
+        return cls(kernel=kernel, D=D, off_n=off_n, X=X, y=y, off_m=off_m, Xs=XS)
+
+    def to_device(self, device) -> "RaggedBatch":
+        import torch
+        t = lambda a: None if a is None else torch.as_tensor(a, dtype=torch.float64, device=device).contiguous()
+        return RaggedBatch(self.kernel, self.D, self.off_n, t(self.X), t(self.y), self.off_m, t(self.Xs))
+
+    def select(self, idx: Sequence[int]) -> "RaggedBatch":
+        """Host-side sub-batch (used to shard experts across ranks)."""
+        assert not self.on_device
+        idx = list(idx)
+        Xo = [self.X[self.off_n[e]:self.off_n[e + 1]] for e in idx]
+        yo = [self.y[self.off_n[e]:self.off_n[e + 1]] for e in idx]
+        Xp = None
+        if self.off_m is not None:
+            Xp = [self.Xs[self.off_m[e]:self.off_m[e + 1]] for e in idx]
+        if not idx:
+            b = RaggedBatch(self.kernel, self.D, np.zeros(1, np.int64), np.zeros((0, self.D)), np.zeros(0))
+            if self.off_m is not None:
+                b.off_m, b.Xs = np.zeros(1, np.int64), np.zeros((0, self.D))
+            return b
+        return RaggedBatch.from_lists(self.kernel, Xo, yo, Xp)
+
+    def _c(self, with_pred: bool) -> _lib.Batch:
+        b = _lib.Batch()
+        b.kernel = _lib.KERNEL_IDS[self.kernel]
+        b.D = self.D
+        b.E = self.E
+        self.off_n = np.ascontiguousarray(self.off_n, dtype=np.int64)
+        b.off_n = self.off_n.ctypes.data
+        b.X = _ptr(self.X).value if self.X is not None else None
+        b.y = _ptr(self.y).value if self.y is not None else None
+        if with_pred:
+            assert self.off_m is not None, "batch has no prediction locations"
+            self.off_m = np.ascontiguousarray(self.off_m, dtype=np.int64)
+            b.off_m = self.off_m.ctypes.data
+            b.Xs = _ptr(self.Xs).value if self.Xs is not None else None
+        return b
+
+
+@dataclass
+class FitResult:
+    theta: object
+    lml: object
+    n_evals: object
+    n_iters: object
+    status: object
+
+    @property
+    def success(self):
+        return self.status == _lib.STATUS_OK
+
+
+class Engine:
+    """One engine handle = one CUDA device + one stream.  Not thread-safe."""
+
+    def __init__(self, device: int = 0):
+        self._lib = _lib.load()
+        h = C.c_void_p()
+        _lib.check(self._lib.gpsat_engine_create(int(device), C.byref(h)))
+        self._h = h
+        self.device = int(device)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.gpsat_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def stats(self) -> dict:
+        s = _lib.Stats()
+        _lib.check(self._lib.gpsat_engine_stats(self._h, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in s._fields_}
+
+    # -- allocation helper: outputs live where the inputs live --------------------------------
+    def _empty(self, batch: RaggedBatch, shape, dtype):
+        if batch.on_device:
+            import torch
+            td = {np.float64: torch.float64, np.int32: torch.int32}[dtype]
+            return torch.empty(shape, dtype=td, device=batch.X.device)
+        return np.empty(shape, dtype=dtype)
+
+    def _in(self, batch: RaggedBatch, a, dtype, shape):
+        if batch.on_device:
+            import torch
+            td = {np.float64: torch.float64, np.int32: torch.int32, np.uint8: torch.uint8}[dtype]
+            if _is_torch(a):
+                return a.to(device=batch.X.device, dtype=td).reshape(shape).contiguous()
+            return torch.as_tensor(np.ascontiguousarray(a, dtype=dtype).reshape(shape), device=batch.X.device)
+        return np.ascontiguousarray(a, dtype=dtype).reshape(shape)
+
+    def lml_grad(self, batch: RaggedBatch, theta, with_grad: bool = True):
+        E, P = batch.E, batch.D + 2
+        mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
+        th = self._in(batch, theta, np.float64, (E, P))
+        lml = self._empty(batch, (E,), np.float64)
+        grad = self._empty(batch, (E, P), np.float64) if with_grad else None
+        status = self._empty(batch, (E,), np.int32)
+        cb = batch._c(False)
+        _lib.check(self._lib.gpsat_gpr_lml_grad(self._h, C.byref(cb), mem, _ptr(th), _ptr(lml), _ptr(grad), _ptr(status)))
+        return lml, grad, status
+
+    def fit(self, batch: RaggedBatch, theta0, tkind, ta, tb, trainable, *, max_iter: int = 10_000,
+            pgtol: float = 1e-5, ftol: float = SCIPY_FTOL, maxfun: int = 15_000, maxls: int = 20,
+            max_slots: int = 0) -> FitResult:
+        E, P = batch.E, batch.D + 2
+        mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
+        th = self._in(batch, theta0, np.float64, (E, P))
+        th = th.clone() if _is_torch(th) else th.copy()
+        tk = self._in(batch, tkind, np.int32, (E, P))
+        a = self._in(batch, ta, np.float64, (E, P))
+        b = self._in(batch, tb, np.float64, (E, P))
+        tr = self._in(batch, trainable, np.uint8, (E, P))
+        lml = self._empty(batch, (E,), np.float64)
+        nev = self._empty(batch, (E,), np.int32)
+        nit = self._empty(batch, (E,), np.int32)
+        status = self._empty(batch, (E,), np.int32)
+        opt = _lib.FitOptions(pgtol, ftol, int(max_iter), int(maxfun), int(maxls), int(max_slots))
+        cb = batch._c(False)
+        _lib.check(self._lib.gpsat_gpr_fit(self._h, C.byref(cb), mem, _ptr(th), _ptr(tk), _ptr(a), _ptr(b), _ptr(tr),
+                                           C.byref(opt), _ptr(lml), _ptr(nev), _ptr(nit), _ptr(status)))
+        return FitResult(th, lml, nev, nit, status)
+
+    def predict(self, batch: RaggedBatch, theta):
+        E, P = batch.E, batch.D + 2
+        mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
+        M = int(batch.off_m[-1])
+        th = self._in(batch, theta, np.float64, (E, P))
+        fm = self._empty(batch, (M,), np.float64)
+        fv = self._empty(batch, (M,), np.float64)
+        yv = self._empty(batch, (M,), np.float64)
+        lml = self._empty(batch, (E,), np.float64)
+        status = self._empty(batch, (E,), np.int32)
+        cb = batch._c(True)
+        _lib.check(self._lib.gpsat_gpr_predict(self._h, C.byref(cb), mem, _ptr(th), _ptr(fm), _ptr(fv), _ptr(yv),
+                                               _ptr(lml), _ptr(status)))
+        return {"f*": fm, "f*_var": fv, "y_var": yv, "lml": lml, "status": status}
+
+    def factor_debug(self, kernel: str, X, y, theta, want_U: bool = True):
+        X = _f64(X)
+        X = X.reshape(len(X), -1)
+        b = RaggedBatch.from_lists(kernel, [X], [_f64(y)])
+        N = len(X) + 1
+        L = np.empty((N, N))
+        U = np.empty((N, N)) if want_U else None
+        th = _f64(theta)
+        cb = b._c(False)
+        _lib.check(self._lib.gpsat_gpr_factor_debug(self._h, C.byref(cb), _ptr(th), _ptr(L), _ptr(U)))
+        return L, U

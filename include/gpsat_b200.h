@@ -1,0 +1,133 @@
+/* gpsat_b200.h - C ABI of the B200-native local-expert GP engine (libgpsat_b200.so).
+ *
+ * Drop-in boundary for the per-expert hot path of akpetty/GPSat.  The reference is pure Python
+ * and has no FFI of its own; the calls below replace, in batch over E experts, what one
+ * GPSat model instance does per expert through GPflow/TensorFlow:
+ *
+ *   gpsat_gpr_lml_grad  <- GPflowGPRModel.get_objective_function_value
+ *                          (GPSat/models/gpflow_models.py:334-337) and the loss+gradient closure
+ *                          gpflow.optimizers.Scipy evaluates (gpflow_models.py:317-321)
+ *   gpsat_gpr_fit       <- GPflowGPRModel.optimise_parameters (gpflow_models.py:290-329) for the
+ *                          whole loop body of LocalExpertOI.run (GPSat/local_experts.py:1126-1132)
+ *   gpsat_gpr_predict   <- GPflowGPRModel.predict (gpflow_models.py:186-273; predict_y/predict_f
+ *                          at :229-230), called at local_experts.py:1157-1164
+ *   gpsat_sgpr_*        <- GPflowSGPRModel (gpflow_models.py:666-901)
+ *
+ * Conventions
+ *   - all floating point data is float64, C-contiguous; offsets are int64; flags are int32/uint8
+ *   - experts are described raggedly: expert e owns rows off_n[e] .. off_n[e+1] of X / y and
+ *     rows off_m[e] .. off_m[e+1] of Xs and of the prediction outputs
+ *   - X, Xs are the *scaled* coordinates (already divided by coords_scale,
+ *     GPSat/models/base_model.py:243) and y the centred/scaled observations (:244-245)
+ *   - theta layout per expert: [lengthscale_1..lengthscale_D, kernel_variance, likelihood_variance],
+ *     P = D + 2 values, constrained space
+ *   - `mem` says where the data arrays live: GPSAT_MEM_HOST (the engine copies in and out on its
+ *     own stream) or GPSAT_MEM_DEVICE (device pointers of the engine's device; nothing is copied).
+ *     off_n / off_m are always host pointers.
+ *   - every function returns 0 on success, non-zero on API misuse or a CUDA error
+ *     (gpsat_last_error() gives the text); numerical trouble is reported per expert in status[].
+ *   - a handle is bound to one device and one stream and is not thread-safe; use one handle per
+ *     host thread / GPU rank.  No global mutable state besides the last-error string.
+ */
+#ifndef GPSAT_B200_H
+#define GPSAT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GPSAT_MEM_HOST 0
+#define GPSAT_MEM_DEVICE 1
+
+/* kernel ids (gpflow.kernels names accepted by GPflowGPRModel(kernel=...), gpflow_models.py:72-75) */
+#define GPSAT_KERNEL_MATERN12 0
+#define GPSAT_KERNEL_MATERN32 1
+#define GPSAT_KERNEL_MATERN52 2
+#define GPSAT_KERNEL_RBF 3
+
+/* parameter transforms: theta = a + softplus(xi)            (gpflow.utilities.positive(lower=a))
+ *                       theta = a + (b - a) * sigmoid(xi)   (tfp.bijectors.Sigmoid(low=a, high=b),
+ *                                                            gpflow_models.py:490-494)            */
+#define GPSAT_TRANSFORM_SOFTPLUS 0
+#define GPSAT_TRANSFORM_SIGMOID 1
+
+/* per-expert status */
+#define GPSAT_STATUS_OK 0            /* converged (SciPy success == True) / evaluated            */
+#define GPSAT_STATUS_NOT_PD 1        /* K + s2 I not positive definite at the (starting) point    */
+#define GPSAT_STATUS_LINESEARCH 2    /* ABNORMAL_TERMINATION_IN_LNSRCH (success == False)         */
+#define GPSAT_STATUS_MAXITER 3       /* maxiter / maxfun reached (success == False)               */
+#define GPSAT_STATUS_BAD_INPUT 4     /* non-finite input                                          */
+
+#define GPSAT_MAX_DIMS 6
+
+typedef struct gpsat_engine gpsat_engine;
+
+typedef struct {
+  int32_t kernel;          /* GPSAT_KERNEL_*                       */
+  int32_t D;               /* input dimensions, 1..GPSAT_MAX_DIMS  */
+  int64_t E;               /* number of experts                    */
+  const int64_t* off_n;    /* [E+1] host                           */
+  const int64_t* off_m;    /* [E+1] host, may be NULL (no prediction rows) */
+  const double* X;         /* [off_n[E]][D]                        */
+  const double* y;         /* [off_n[E]]                           */
+  const double* Xs;        /* [off_m[E]][D], may be NULL           */
+} gpsat_batch;
+
+typedef struct {
+  double pgtol;            /* SciPy gtol,   default 1e-5                     */
+  double ftol;             /* SciPy ftol,   default 2.220446049250313e-09    */
+  int32_t maxiter;         /* default 10000 (gpflow_models.py:291)           */
+  int32_t maxfun;          /* default 15000                                  */
+  int32_t maxls;           /* default 20                                     */
+  int32_t max_slots;       /* experts in flight per GPU, 0 = automatic       */
+} gpsat_fit_options;
+
+typedef struct {
+  int64_t kernel_launches; /* kernels launched by the last call      */
+  int64_t ticks;           /* batched objective evaluations (sweeps) */
+  int64_t evals;           /* per-expert objective evaluations       */
+  int64_t slots;           /* experts in flight                      */
+  double h2d_bytes;
+  double d2h_bytes;
+  double gpu_ms;           /* CUDA-event time of the last call, copies included */
+  double sweep_flops;      /* sum over evaluations of n^3 (+ n^2 m for predict) */
+} gpsat_stats;
+
+int gpsat_version(void);
+const char* gpsat_last_error(void);
+
+int gpsat_engine_create(int device, gpsat_engine** out);
+int gpsat_engine_destroy(gpsat_engine* eng);
+int gpsat_engine_stats(const gpsat_engine* eng, gpsat_stats* out);
+void gpsat_fit_options_default(gpsat_fit_options* opt);
+
+/* lml[e] = log marginal likelihood, grad[e][P] = d lml / d theta (constrained space). */
+int gpsat_gpr_lml_grad(gpsat_engine* eng, const gpsat_batch* batch, int mem, const double* theta,
+                       double* lml, double* grad, int32_t* status);
+
+/* Batched L-BFGS in unconstrained space.  theta_io: start values in, optimum out.
+ * tkind/ta/tb: transform per parameter; trainable: 1 = optimise, 0 = keep fixed.
+ * lml: value at the optimum; n_evals / n_iters: SciPy nfev / nit equivalents. */
+int gpsat_gpr_fit(gpsat_engine* eng, const gpsat_batch* batch, int mem, double* theta_io,
+                  const int32_t* tkind, const double* ta, const double* tb, const uint8_t* trainable,
+                  const gpsat_fit_options* opt, double* lml, int32_t* n_evals, int32_t* n_iters,
+                  int32_t* status);
+
+/* Predictive mean / variance at batch->Xs for fixed theta: fmean = f*, fvar = f*_var,
+ * yvar = f*_var + likelihood variance; lml[e] as a by-product of the same factorisation. */
+int gpsat_gpr_predict(gpsat_engine* eng, const gpsat_batch* batch, int mem, const double* theta,
+                      double* fmean, double* fvar, double* yvar, double* lml, int32_t* status);
+
+/* Test hook (single expert, host memory): dense factor of the augmented matrix.
+ * Lout [(n+1)*(n+1)] row-major lower: rows < n = chol(K + s2 I), row n = (L^-1 y)^T, 1.
+ * Uout [(n+1)*(n+1)] row-major upper: L_aug^-T (may be NULL). */
+int gpsat_gpr_factor_debug(gpsat_engine* eng, const gpsat_batch* batch, const double* theta,
+                           double* Lout, double* Uout);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GPSAT_B200_H */
