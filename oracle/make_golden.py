@@ -1,0 +1,128 @@
+"""Generate tests/golden/*.npz  (run in the build container, where /root/reference is mounted).
+
+Three independent sources pin the oracle (and through it the CUDA path):
+
+1. ``kat_localexperts.npz`` - the reference's own known-answer vector: the module-level fixture
+   of ``/root/reference/tests/test_localexperts.py:22-49`` re-executed verbatim (sklearn
+   Matern-3/2 fit on 50 points) - optimised lengthscale, LML, predictive mean / std.
+2. ``pure_python_gpr.npz`` - the reference's in-repo NumPy GPR
+   (``/root/reference/GPSat/models/pure_python_gpr.py:378-553``: ``SGPkernel``, ``SMLII_mod``,
+   ``GPR``) executed from the reference tree (functions extracted with ``ast`` because the
+   module's own imports pull in TensorFlow) on seeded 3-D ARD inputs.
+3. ``sklearn_ard.npz`` - scikit-learn ``GaussianProcessRegressor`` LML, gradient and predictions
+   for Matern-1/2, 3/2, 5/2 and RBF with ARD lengthscales (same math, independent code).
+
+Usage:  python oracle/make_golden.py
+"""
+from __future__ import annotations
+
+import ast
+import os
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+OUT = os.path.join(ROOT, "tests", "golden")
+REF = "/root/reference"
+
+
+def kat_localexperts():
+    from sklearn.gaussian_process import GaussianProcessRegressor
+    from sklearn.gaussian_process.kernels import Matern
+
+    # --- verbatim flow of tests/test_localexperts.py:22-49 ---
+    np.random.seed(23435)
+    kernel = Matern(length_scale=0.8, nu=3 / 2)
+    gp = GaussianProcessRegressor(kernel)
+    x = np.linspace(0, 10, 100)[:, None]
+    f = gp.sample_y(x, random_state=0)
+    N = 50
+    eps = 1e-2
+    indices = np.arange(100)
+    np.random.shuffle(indices)
+    x_train = x[indices[:N]]
+    y_train = f[indices[:N]] + eps * np.random.randn(N, 1)
+    gp.alpha = eps ** 2
+    gp.fit(x_train, y_train)
+    ls = gp.kernel_.length_scale
+    ml = gp.log_marginal_likelihood()
+    test_index = np.random.randint(0, 99)
+    x_test = x[[test_index]]
+    pred_mean, pred_std = gp.predict(x_test, return_std=True)
+    np.savez(os.path.join(OUT, "kat_localexperts.npz"), x_train=x_train, y_train=y_train, eps=eps,
+             ls=ls, ml=ml, x_test=x_test, pred_mean=pred_mean, pred_std=pred_std,
+             constraint_low=1e-10, constraint_high=5.0)
+    print("kat:", ls, ml, test_index, pred_mean, pred_std ** 2)
+
+
+def _load_pure_python_functions():
+    """Extract SGPkernel / SMLII_mod / GPR / Nystroem from the reference without importing GPSat."""
+    path = os.path.join(REF, "GPSat", "models", "pure_python_gpr.py")
+    tree = ast.parse(open(path).read())
+    wanted = {"SGPkernel", "SMLII_mod", "GPR", "Nystroem"}
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in wanted]
+    mod = ast.Module(body=body, type_ignores=[])
+    import scipy
+    from numpy.linalg import multi_dot as mdot
+    from scipy.spatial.distance import cdist, pdist, squareform
+    ns = {"np": np, "scipy": scipy, "mdot": mdot, "squareform": squareform, "pdist": pdist, "cdist": cdist}
+    exec(compile(mod, path, "exec"), ns)
+    return ns
+
+
+def pure_python():
+    ns = _load_pure_python_functions()
+    rng = np.random.default_rng(20240517)
+    n, m = 120, 40
+    X = rng.uniform(-3, 3, (n, 3))
+    Xs = rng.uniform(-3, 3, (m, 3))
+    y = np.sin(X[:, 0]) + 0.5 * np.cos(2 * X[:, 1]) + 0.1 * X[:, 2] + 0.1 * rng.standard_normal(n)
+    thetas = np.array([[1.0, 1.0, 1.0, 1.0, 1.0],
+                       [1.7, 0.6, 2.5, 0.8, 0.05],
+                       [0.4, 3.0, 1.2, 2.0, 0.3]])
+    nlz, fs, fvar = [], [], []
+    for th in thetas:
+        nlz.append(ns["SMLII_mod"](hypers=th, x=X, y=y, approx=False, M=None, grad=False))
+        mean, sd = ns["GPR"](x=X, y=y, xs=Xs, ell=th[:3], sf2=th[3], sn2=th[4], mean=0, approx=False, M=None)
+        fs.append(np.asarray(mean).ravel())
+        fvar.append(np.asarray(sd).ravel() ** 2)
+    np.savez(os.path.join(OUT, "pure_python_gpr.npz"), X=X, y=y, Xs=Xs, thetas=thetas,
+             nlZ=np.array(nlz), fmean=np.array(fs), fvar=np.array(fvar))
+    print("pure_python nlZ:", nlz)
+
+
+def sklearn_ard():
+    from sklearn.gaussian_process import GaussianProcessRegressor
+    from sklearn.gaussian_process.kernels import RBF, ConstantKernel, Matern
+
+    rng = np.random.default_rng(77)
+    n, m = 150, 30
+    X = rng.uniform(-4, 4, (n, 3))
+    Xs = rng.uniform(-4, 4, (m, 3))
+    y = np.sin(X[:, 0]) * np.cos(0.5 * X[:, 1]) + 0.2 * X[:, 2] + 0.15 * rng.standard_normal(n)
+    theta = np.array([1.3, 0.7, 2.0, 0.8, 0.1])
+    out = dict(X=X, y=y, Xs=Xs, theta=theta)
+    for name, base in (("Matern12", Matern(length_scale=theta[:3], nu=0.5)),
+                       ("Matern32", Matern(length_scale=theta[:3], nu=1.5)),
+                       ("Matern52", Matern(length_scale=theta[:3], nu=2.5)),
+                       ("RBF", RBF(length_scale=theta[:3]))):
+        k = ConstantKernel(theta[3]) * base
+        gp = GaussianProcessRegressor(k, alpha=theta[4], optimizer=None).fit(X, y)
+        # sklearn theta = log([constant, l1, l2, l3]); gradient is w.r.t. log-parameters
+        lml, g = gp.log_marginal_likelihood(gp.kernel_.theta, eval_gradient=True)
+        mean, sd = gp.predict(Xs, return_std=True)
+        out[f"{name}_lml"] = lml
+        # convert to d/d(constrained): dlml/dp = g / p ; order -> [l1, l2, l3, var]
+        out[f"{name}_grad_ls"] = g[1:4] / theta[:3]
+        out[f"{name}_grad_var"] = g[0] / theta[3]
+        out[f"{name}_fmean"] = mean
+        out[f"{name}_fvar"] = sd ** 2
+        print(name, lml)
+    np.savez(os.path.join(OUT, "sklearn_ard.npz"), **out)
+
+
+if __name__ == "__main__":
+    os.makedirs(OUT, exist_ok=True)
+    kat_localexperts()
+    pure_python()
+    sklearn_ard()

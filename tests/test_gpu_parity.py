@@ -1,0 +1,268 @@
+"""Parity of the CUDA path (through the C ABI) with the CPU oracle.  Needs a B200: -m gpu.
+
+Tolerances (BASELINE.json north_star): relative 1e-8 on LML and predictive mean / variance at
+fixed hyper-parameters; 1e-4 on optimised hyper-parameters and the resulting LML.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import gpr
+
+pytestmark = pytest.mark.gpu
+
+RTOL_FIXED = 1e-8
+RTOL_OPT = 1e-4
+
+
+def _expert(rng, n, D, m=0, noise=0.2):
+    X = rng.uniform(-4, 4, (n, D))
+    K = gpr.kernel_matrix("Matern32", X, None, [2.0, 1.5, 3.0][:D], 0.7)
+    y = np.linalg.cholesky(K + 1e-8 * np.eye(n)) @ rng.standard_normal(n) + noise * rng.standard_normal(n)
+    return X, y, rng.uniform(-4, 4, (m, D))
+
+
+def _batch(kind, experts, with_pred=True):
+    from gpsat_b200.engine import RaggedBatch
+    return RaggedBatch.from_lists(kind, [e[0] for e in experts], [e[1] for e in experts],
+                                  [e[2] for e in experts] if with_pred else None)
+
+
+def _theta(rng, D):
+    return np.concatenate([rng.uniform(0.6, 2.5, D), [rng.uniform(0.3, 1.5)], [rng.uniform(0.02, 0.3)]])
+
+
+@pytest.mark.parametrize("n", [1, 2, 5, 127, 128, 129, 255, 256, 257, 600])
+def test_factor_matches_numpy(engine, n):
+    rng = np.random.default_rng(n)
+    X, y, _ = _expert(rng, n, 3)
+    th = _theta(rng, 3)
+    L, U = engine.factor_debug("Matern32", X, y, th)
+    Ks = gpr.kernel_matrix("Matern32", X, None, th[:3], th[3]) + th[4] * np.eye(n)
+    Lr = np.linalg.cholesky(Ks)
+    a = np.linalg.solve(Lr, y)
+    np.testing.assert_allclose(L[:n, :n], Lr, rtol=0, atol=1e-12 * np.abs(Lr).max())
+    np.testing.assert_allclose(L[n, :n], a, rtol=0, atol=1e-11 * max(1.0, np.abs(a).max()))
+    assert L[n, n] == 1.0
+    # property: L L^T reproduces K + s2 I, U = L_aug^-T
+    np.testing.assert_allclose(L[:n, :n] @ L[:n, :n].T, Ks, rtol=0, atol=1e-12 * np.abs(Ks).max())
+    np.testing.assert_allclose(U.T @ L, np.eye(n + 1), rtol=0, atol=1e-9)
+    assert np.all(np.triu(L, 1) == 0) and np.all(np.tril(U, -1) == 0)
+
+
+@pytest.mark.parametrize("kind", gpr.KERNELS)
+@pytest.mark.parametrize("D", [1, 2, 3])
+def test_lml_grad_predict_ragged(engine, kind, D):
+    rng = np.random.default_rng(100 * D + len(kind))
+    ns = [3, 40, 130, 257, 420, 64]
+    experts = [_expert(rng, n, D, m=7 + n // 3) for n in ns]
+    experts[1] = (experts[1][0], experts[1][1], np.zeros((0, D)))       # an expert without prediction rows
+    b = _batch(kind, experts)
+    theta = np.stack([_theta(rng, D) for _ in ns])
+    lml, grad, status = engine.lml_grad(b, theta)
+    pred = engine.predict(b, theta)
+    assert np.all(status == 0) and np.all(pred["status"] == 0)
+    for e, (X, y, Xs) in enumerate(experts):
+        v, g = gpr.lml_and_grad(kind, X, y, theta[e])
+        assert abs(lml[e] - v) <= RTOL_FIXED * abs(v)
+        assert abs(pred["lml"][e] - v) <= RTOL_FIXED * abs(v)
+        np.testing.assert_allclose(grad[e], g, rtol=1e-7, atol=1e-8 * np.abs(g).max())
+        if len(Xs):
+            p = gpr.predict(kind, X, y, theta[e], Xs)
+            sl = slice(b.off_m[e], b.off_m[e + 1])
+            np.testing.assert_allclose(pred["f*"][sl], p["f*"], rtol=RTOL_FIXED, atol=1e-10)
+            np.testing.assert_allclose(pred["f*_var"][sl], p["f*_var"], rtol=RTOL_FIXED, atol=1e-12)
+            np.testing.assert_allclose(pred["y_var"][sl], p["y_var"], rtol=RTOL_FIXED, atol=1e-12)
+
+
+def test_lml_only_matches(engine):
+    rng = np.random.default_rng(3)
+    experts = [_expert(rng, n, 3) for n in (50, 300)]
+    b = _batch("Matern52", experts, with_pred=False)
+    theta = np.stack([_theta(rng, 3) for _ in experts])
+    a, _, _ = engine.lml_grad(b, theta, with_grad=False)
+    c, _, _ = engine.lml_grad(b, theta, with_grad=True)
+    assert np.array_equal(a, c)
+
+
+def test_golden_pure_python_through_cuda(engine, golden_dir):
+    """Reference's in-repo NumPy GPR (pure_python_gpr.py:439-553) vs the CUDA path."""
+    from gpsat_b200.engine import RaggedBatch
+    g = np.load(os.path.join(golden_dir, "pure_python_gpr.npz"))
+    X, y, Xs = g["X"], g["y"], g["Xs"]
+    k = len(g["thetas"])
+    b = RaggedBatch.from_lists("Matern32", [X] * k, [y] * k, [Xs] * k)
+    pred = engine.predict(b, g["thetas"])
+    for e in range(k):
+        nlz = float(np.ravel(g["nlZ"][e])[0])
+        assert abs(-pred["lml"][e] - nlz) <= RTOL_FIXED * abs(nlz)
+        sl = slice(b.off_m[e], b.off_m[e + 1])
+        np.testing.assert_allclose(pred["f*"][sl], g["fmean"][e], rtol=RTOL_FIXED, atol=1e-10)
+        np.testing.assert_allclose(pred["f*_var"][sl], g["fvar"][e], rtol=1e-7, atol=1e-12)
+
+
+@pytest.mark.parametrize("kind", gpr.KERNELS)
+def test_golden_sklearn_through_cuda(engine, golden_dir, kind):
+    from gpsat_b200.engine import RaggedBatch
+    g = np.load(os.path.join(golden_dir, "sklearn_ard.npz"))
+    b = RaggedBatch.from_lists(kind, [g["X"]], [g["y"]], [g["Xs"]])
+    th = g["theta"][None, :]
+    lml, grad, _ = engine.lml_grad(b, th)
+    pred = engine.predict(b, th)
+    assert abs(lml[0] - float(g[f"{kind}_lml"])) <= RTOL_FIXED * abs(lml[0])
+    np.testing.assert_allclose(grad[0, :3], g[f"{kind}_grad_ls"], rtol=1e-7)
+    np.testing.assert_allclose(grad[0, 3], g[f"{kind}_grad_var"], rtol=1e-7)
+    np.testing.assert_allclose(pred["f*"], g[f"{kind}_fmean"], rtol=RTOL_FIXED, atol=1e-10)
+    np.testing.assert_allclose(pred["f*_var"], g[f"{kind}_fvar"], rtol=1e-7, atol=1e-12)
+
+
+def test_golden_kat_fit_through_cuda(engine, golden_dir):
+    """tests/test_localexperts.py::test_gpflow_gpr of the reference (tolerance 1e-6 there):
+    likelihood variance fixed at eps^2, kernel variance fixed, lengthscale in [1e-10, 5]."""
+    from gpsat_b200.engine import RaggedBatch
+    g = np.load(os.path.join(golden_dir, "kat_localexperts.npz"))
+    eps = float(g["eps"])
+    b = RaggedBatch.from_lists("Matern32", [g["x_train"]], [g["y_train"][:, 0]], [g["x_test"]])
+    res = engine.fit(b, [[1.0, 1.0, eps ** 2]], [[1, 0, 0]], [[1e-10, 0, 1e-6]], [[5.0, 0, 0]], [[1, 0, 0]])
+    assert res.status[0] == 0
+    assert abs(res.theta[0, 0] - float(g["ls"])) < 1e-6
+    assert res.theta[0, 1] == 1.0 and res.theta[0, 2] == eps ** 2
+    assert abs(res.lml[0] - float(g["ml"])) < 1e-6
+    pred = engine.predict(b, res.theta)
+    assert abs(pred["f*"][0] - g["pred_mean"][0]) < 1e-6
+    assert abs(pred["f*_var"][0] - g["pred_std"][0] ** 2) < 1e-6
+
+
+@pytest.mark.parametrize("kind", ["Matern32", "RBF", "Matern12", "Matern52"])
+def test_fit_matches_scipy_lbfgsb(engine, kind):
+    """More experts than slots (max_slots=3) so slots are retired and refilled on the device."""
+    rng = np.random.default_rng(len(kind))
+    ns = [60, 150, 300, 90, 200, 35, 131, 260]
+    experts = [_expert(rng, n, 3) for n in ns]
+    b = _batch(kind, experts, with_pred=False)
+    E = b.E
+    tr = gpr.Transform.gpflow_default(3)
+    tr.set_sigmoid([0, 1, 2], [1e-8] * 3, [12, 12, 9.0])
+    th0 = np.ones((E, 5))
+    res = engine.fit(b, th0, np.tile(tr.kind, (E, 1)), np.tile(tr.a, (E, 1)), np.tile(tr.b, (E, 1)),
+                     np.ones((E, 5), np.uint8), max_slots=3)
+    for e, (X, y, _) in enumerate(experts):
+        th, l, ok, nev = gpr.fit(kind, X, y, th0[e], tr)
+        assert (res.status[e] == 0) == ok
+        assert abs(res.lml[e] - l) <= RTOL_OPT * abs(l)
+        np.testing.assert_allclose(res.theta[e], th, rtol=RTOL_OPT)
+        assert abs(int(res.n_evals[e]) - nev) <= 2      # same optimisation path as SciPy
+
+
+def test_fit_fixed_parameters_and_maxiter(engine):
+    rng = np.random.default_rng(11)
+    experts = [_expert(rng, n, 2) for n in (80, 140)]
+    b = _batch("Matern32", experts, with_pred=False)
+    tr = gpr.Transform.gpflow_default(2)
+    th0 = np.array([[1.0, 1.0, 0.7, 0.04]] * 2)
+    trainable = np.array([[1, 1, 0, 0]] * 2, np.uint8)
+    res = engine.fit(b, th0, np.tile(tr.kind, (2, 1)), np.tile(tr.a, (2, 1)), np.tile(tr.b, (2, 1)), trainable)
+    for e, (X, y, _) in enumerate(experts):
+        th, l, ok, nev = gpr.fit("Matern32", X, y, th0[e], tr, trainable=trainable[e].astype(bool))
+        np.testing.assert_allclose(res.theta[e], th, rtol=RTOL_OPT)
+        assert np.array_equal(res.theta[e, 2:], th0[e, 2:])
+    # maxiter reached => status MAXITER (SciPy success False), iterate equals SciPy's
+    res2 = engine.fit(b, th0, np.tile(tr.kind, (2, 1)), np.tile(tr.a, (2, 1)), np.tile(tr.b, (2, 1)),
+                      np.ones((2, 4), np.uint8), max_iter=3)
+    for e, (X, y, _) in enumerate(experts):
+        th, l, ok, nev = gpr.fit("Matern32", X, y, th0[e], tr, max_iter=3)
+        assert not ok and res2.status[e] == 3 and res2.n_iters[e] == 3
+        np.testing.assert_allclose(res2.theta[e], th, rtol=1e-7)
+
+
+def test_shard_equality_is_bitwise(engine):
+    """Experts never interact: an expert evaluated / optimised alone gives bit-identical results to
+    the same expert inside a batch (what makes 1-GPU and N-GPU runs identical)."""
+    rng = np.random.default_rng(21)
+    experts = [_expert(rng, n, 3, m=20) for n in (70, 190, 310, 129)]
+    b = _batch("Matern32", experts)
+    E = b.E
+    theta = np.stack([_theta(rng, 3) for _ in range(E)])
+    lml, grad, _ = engine.lml_grad(b, theta)
+    pred = engine.predict(b, theta)
+    tr = gpr.Transform.gpflow_default(3)
+    args = lambda k: (np.tile(tr.kind, (k, 1)), np.tile(tr.a, (k, 1)), np.tile(tr.b, (k, 1)), np.ones((k, 5), np.uint8))
+    fit_all = engine.fit(b, np.ones((E, 5)), *args(E), max_iter=6)
+    for e in range(E):
+        sub = b.select([e])
+        l1, g1, _ = engine.lml_grad(sub, theta[e:e + 1])
+        p1 = engine.predict(sub, theta[e:e + 1])
+        assert l1[0] == lml[e] and np.array_equal(g1[0], grad[e])
+        sl = slice(b.off_m[e], b.off_m[e + 1])
+        assert np.array_equal(p1["f*"], pred["f*"][sl]) and np.array_equal(p1["f*_var"], pred["f*_var"][sl])
+        f1 = engine.fit(sub, np.ones((1, 5)), *args(1), max_iter=6)
+        assert np.array_equal(f1.theta[0], fit_all.theta[e]) and f1.lml[0] == fit_all.lml[e]
+
+
+def test_device_pointers_equal_host_path(engine):
+    import torch
+    rng = np.random.default_rng(31)
+    experts = [_expert(rng, n, 3, m=15) for n in (50, 200)]
+    b = _batch("Matern32", experts)
+    theta = np.stack([_theta(rng, 3) for _ in experts])
+    bd = b.to_device("cuda:0")
+    l_h, g_h, _ = engine.lml_grad(b, theta)
+    l_d, g_d, _ = engine.lml_grad(bd, theta)
+    assert isinstance(l_d, torch.Tensor) and l_d.is_cuda
+    assert np.array_equal(l_d.cpu().numpy(), l_h) and np.array_equal(g_d.cpu().numpy(), g_h)
+    p_h, p_d = engine.predict(b, theta), engine.predict(bd, theta)
+    assert np.array_equal(p_d["f*"].cpu().numpy(), p_h["f*"])
+
+
+def test_duplicates_and_not_pd_status(engine):
+    rng = np.random.default_rng(41)
+    X, y, Xs = _expert(rng, 60, 3, m=5)
+    X[10:20] = X[0:10]                       # exact duplicates (binned data has them)
+    b = _batch("Matern12", [(X, y, Xs)])
+    th = np.array([[1.5, 1.0, 2.0, 0.8, 0.05]])
+    lml, grad, st = engine.lml_grad(b, th)
+    v, g = gpr.lml_and_grad("Matern12", X, y, th[0])
+    assert st[0] == 0 and abs(lml[0] - v) <= RTOL_FIXED * abs(v)
+    np.testing.assert_allclose(grad[0], g, rtol=1e-7)
+    th_bad = np.array([[1.5, 1.0, 2.0, 0.8, 0.0]])    # singular: duplicates and no noise
+    lml, grad, st = engine.lml_grad(b, th_bad)
+    assert st[0] == 1 and lml[0] == -np.inf
+    good = _expert(rng, 40, 3, m=5)
+    b2 = _batch("Matern12", [(X, y, Xs), good])       # a bad expert must not poison its neighbour
+    lml2, _, st2 = engine.lml_grad(b2, np.vstack([th_bad, th]))
+    assert list(st2) == [1, 0]
+    assert abs(lml2[1] - gpr.lml("Matern12", good[0], good[1], th[0])) <= RTOL_FIXED * abs(lml2[1])
+
+
+def test_empty_batch_and_api_misuse(engine):
+    from gpsat_b200.engine import RaggedBatch
+    b = RaggedBatch("Matern32", 3, np.zeros(1, np.int64), np.zeros((0, 3)), np.zeros(0),
+                    np.zeros(1, np.int64), np.zeros((0, 3)))
+    lml, grad, st = engine.lml_grad(b, np.zeros((0, 5)))
+    assert lml.shape == (0,)
+    assert engine.predict(b, np.zeros((0, 5)))["f*"].shape == (0,)
+    bad = RaggedBatch("Matern32", 9, np.array([0, 4], np.int64), np.zeros((4, 9)), np.zeros(4))
+    with pytest.raises(RuntimeError, match="D out of range"):
+        engine.lml_grad(bad, np.ones((1, 11)))
+
+
+@pytest.mark.parametrize("n", [2000, 4000])
+def test_full_size_expert(engine, n):
+    """BASELINE config sizes (c3 / north-star): one expert checked directly against LAPACK, plus
+    size-independent properties (symmetric gradient identity, reproducibility)."""
+    from gpsat_b200 import synthetic as syn
+    spec = syn.WorkloadSpec("t", 2, n, n, 64, 64, 400e3, 8, (50e3, 50e3, 1.0), (600e3, 600e3, 16.0))
+    b = syn.make_batch(spec, seed=5)
+    theta = np.tile(np.array([3.0, 3.5, 4.0, 0.06, 0.006]), (2, 1))
+    lml, grad, st = engine.lml_grad(b, theta)
+    pred = engine.predict(b, theta)
+    X, y, Xs = b.X[:n], b.y[:n], b.Xs[:64]
+    v, g = gpr.lml_and_grad("Matern32", X, y, theta[0])
+    assert st[0] == 0 and abs(lml[0] - v) <= RTOL_FIXED * abs(v)
+    np.testing.assert_allclose(grad[0], g, rtol=1e-6, atol=1e-7 * np.abs(g).max())
+    p = gpr.predict("Matern32", X, y, theta[0], Xs)
+    np.testing.assert_allclose(pred["f*"][:64], p["f*"], rtol=RTOL_FIXED, atol=1e-10)
+    np.testing.assert_allclose(pred["f*_var"][:64], p["f*_var"], rtol=RTOL_FIXED, atol=1e-12)
+    lml_b, grad_b, _ = engine.lml_grad(b, theta)
+    assert np.array_equal(lml, lml_b) and np.array_equal(grad, grad_b)

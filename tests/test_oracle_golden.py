@@ -1,0 +1,126 @@
+"""The oracle against the reference's own known answers (CPU only).
+
+Sources of the golden files: oracle/make_golden.py.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import gpr
+
+
+def test_kat_localexperts(golden_dir):
+    """/root/reference/tests/test_localexperts.py:204-227 (test_gpflow_gpr), tolerance 1e-6 there."""
+    g = np.load(os.path.join(golden_dir, "kat_localexperts.npz"))
+    X, y = g["x_train"], g["y_train"][:, 0]
+    eps = float(g["eps"])
+    tr = gpr.Transform.gpflow_default(1)
+    tr.set_sigmoid(0, float(g["constraint_low"]), float(g["constraint_high"]))
+    theta0 = np.array([1.0, 1.0, eps ** 2])
+    th, l, ok, nev = gpr.fit("Matern32", X, y, theta0, tr, trainable=[True, False, False])
+    assert ok
+    assert abs(th[0] - float(g["ls"])) < 1e-6
+    assert abs(l - float(g["ml"])) < 1e-6
+    p = gpr.predict("Matern32", X, y, th, g["x_test"])
+    assert abs(p["f*"][0] - g["pred_mean"][0]) < 1e-6
+    assert abs(p["f*_var"][0] - g["pred_std"][0] ** 2) < 1e-6
+    assert abs(p["y_var"][0] - (p["f*_var"][0] + eps ** 2)) < 1e-15
+
+
+def test_pure_python_gpr(golden_dir):
+    """GPSat/models/pure_python_gpr.py SMLII_mod (nlZ) and GPR (Rasmussen Alg. 2.1), Matern-3/2 ARD."""
+    g = np.load(os.path.join(golden_dir, "pure_python_gpr.npz"))
+    X, y, Xs = g["X"], g["y"], g["Xs"]
+    for k, th in enumerate(g["thetas"]):
+        nlz = float(np.ravel(g["nlZ"][k])[0])
+        assert abs(-gpr.lml("Matern32", X, y, th) - nlz) <= 1e-10 * abs(nlz)
+        p = gpr.predict("Matern32", X, y, th, Xs)
+        np.testing.assert_allclose(p["f*"], g["fmean"][k], rtol=1e-8, atol=1e-10)
+        np.testing.assert_allclose(p["f*_var"], g["fvar"][k], rtol=1e-7, atol=1e-12)
+
+
+@pytest.mark.parametrize("kind", gpr.KERNELS)
+def test_sklearn_ard(golden_dir, kind):
+    g = np.load(os.path.join(golden_dir, "sklearn_ard.npz"))
+    X, y, Xs, th = g["X"], g["y"], g["Xs"], g["theta"]
+    v, grad = gpr.lml_and_grad(kind, X, y, th)
+    assert abs(v - float(g[f"{kind}_lml"])) <= 1e-10 * abs(v)
+    np.testing.assert_allclose(grad[:3], g[f"{kind}_grad_ls"], rtol=1e-8)
+    np.testing.assert_allclose(grad[3], g[f"{kind}_grad_var"], rtol=1e-8)
+    p = gpr.predict(kind, X, y, th, Xs)
+    np.testing.assert_allclose(p["f*"], g[f"{kind}_fmean"], rtol=1e-8, atol=1e-10)
+    np.testing.assert_allclose(p["f*_var"], g[f"{kind}_fvar"], rtol=1e-7, atol=1e-12)
+
+
+@pytest.mark.parametrize("kind", gpr.KERNELS)
+@pytest.mark.parametrize("D", [1, 2, 3])
+def test_analytic_gradient_fd(kind, D):
+    rng = np.random.default_rng(D)
+    n = 40
+    X = rng.uniform(-3, 3, (n, D))
+    y = rng.standard_normal(n)
+    th = np.concatenate([rng.uniform(0.5, 2.5, D), [0.9, 0.2]])
+    v, g = gpr.lml_and_grad(kind, X, y, th)
+    for i in range(D + 2):
+        h = 1e-6 * th[i]
+        tp, tm = th.copy(), th.copy()
+        tp[i] += h
+        tm[i] -= h
+        fd = (gpr.lml(kind, X, y, tp) - gpr.lml(kind, X, y, tm)) / (2 * h)
+        assert abs(g[i] - fd) <= 2e-6 * max(1.0, abs(fd))
+
+
+def test_gradient_matches_torch_autograd():
+    """Independent check of the analytic gradient: reverse-mode autodiff through Cholesky, the way
+    TensorFlow computes it for gpflow.optimizers.Scipy (gpflow_models.py:317-321)."""
+    import torch
+    rng = np.random.default_rng(5)
+    n, D = 60, 3
+    X = rng.uniform(-3, 3, (n, D))
+    y = rng.standard_normal(n)
+    th = np.array([1.4, 0.8, 2.2, 0.7, 0.15])
+    v, g = gpr.lml_and_grad("Matern32", X, y, th)
+    t = torch.tensor(th, dtype=torch.float64, requires_grad=True)
+    Xt, yt = torch.tensor(X), torch.tensor(y)
+    A = Xt / t[:D]
+    r2 = ((A[:, None, :] - A[None, :, :]) ** 2).sum(-1)
+    r = torch.sqrt(torch.clamp(r2, min=1e-36))
+    K = t[D] * (1 + np.sqrt(3.0) * r) * torch.exp(-np.sqrt(3.0) * r) + t[D + 1] * torch.eye(n, dtype=torch.float64)
+    L = torch.linalg.cholesky(K)
+    a = torch.linalg.solve_triangular(L, yt[:, None], upper=False)[:, 0]
+    lml = -0.5 * (a @ a) - torch.log(torch.diagonal(L)).sum() - 0.5 * n * np.log(2 * np.pi)
+    lml.backward()
+    assert abs(float(lml.detach()) - v) < 1e-10
+    np.testing.assert_allclose(t.grad.numpy(), g, rtol=1e-9)
+
+
+def test_gpflow_distance_mode_agrees():
+    """|a|^2+|b|^2-2ab (what GPflow evaluates) vs direct differences: same LML to 1e-8 for the
+    smooth kernels on GPSat-scaled coordinates."""
+    rng = np.random.default_rng(9)
+    X = rng.uniform(-6, 6, (200, 3))
+    y = rng.standard_normal(200)
+    th = np.array([2.0, 3.0, 4.0, 0.5, 0.05])
+    for kind in ("Matern32", "Matern52", "RBF"):
+        a, b = gpr.lml(kind, X, y, th, "direct"), gpr.lml(kind, X, y, th, "gpflow")
+        assert abs(a - b) <= 1e-10 * abs(a)
+
+
+def test_transforms_roundtrip():
+    tr = gpr.Transform.gpflow_default(3)
+    tr.set_sigmoid([0, 1], [1e-8, 0.5], [12.0, 9.0])
+    th = np.array([1.0, 3.0, 2.0, 0.4, 0.003])
+    xi = tr.inverse(th)
+    np.testing.assert_allclose(tr.forward(xi), th, rtol=1e-14)
+    h = 1e-6
+    fd = (tr.forward(xi + h) - tr.forward(xi - h)) / (2 * h)
+    np.testing.assert_allclose(tr.dtheta_dxi(xi), fd, rtol=1e-8)
+    # likelihood variance lower bound 1e-6 (gpflow Gaussian.variance_lower_bound)
+    assert tr.forward(np.array([0, 0, 0, 0, -800.0]))[4] == pytest.approx(1e-6)
+
+
+def test_not_pd_is_minus_inf():
+    X = np.zeros((5, 2))
+    y = np.ones(5)
+    assert gpr.lml("RBF", X, y, np.array([1.0, 1.0, 1.0, 0.0])) == -np.inf
