@@ -1,0 +1,325 @@
+#!/usr/bin/env python
+"""bench.py - local experts/sec (fit + predict, FP64) on N B200s of one node.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload c2]
+
+One "step" = one full pass of the hot path over one batch of synthetic experts: batched
+L-BFGS hyper-parameter fit (every objective evaluation = kernel build + Cholesky + inverse +
+analytic gradient) followed by prediction at the optimised hyper-parameters.
+Workload at N=1: BASELINE.json configs[1] (`configs/example_local_expert_oi.json` shape,
+~500 experts x ~1k observations).  For N>1 every rank gets its own 500-expert shard (weak
+scaling, expert seeds continue across ranks), ranks run independently and rank 0 gathers the
+per-expert results once per step.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "local experts/sec (fit+predict, FP64)"
+UNIT = "experts/s"
+FP64_PEAK_FILE = os.path.join(ROOT, "profiles", "r01_fp64_peak.json")
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="c2", choices=["c1", "c2", "c3", "ns"])
+    ap.add_argument("--experts-per-gpu", type=int, default=0, help="override the workload's expert count")
+    ap.add_argument("--cpu-sample", type=int, default=0, help="experts in the CPU baseline sample (0 = one per core)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def workload_spec(args):
+    from gpsat_b200 import synthetic as syn
+    from dataclasses import replace
+    spec = syn.WORKLOADS[args.workload]
+    if args.experts_per_gpu > 0:
+        spec = replace(spec, E=args.experts_per_gpu)
+    return spec
+
+
+def fp64_peak_tflops():
+    """FP64 pipe peak measured on this pool by tools/fp64_peak.cu (MEASURED_PEAKS.json has no FP64
+    entry and the profiling guide states no FP64 fallback)."""
+    try:
+        d = json.load(open(FP64_PEAK_FILE))
+        return float(d["dmma_m8n8k4_sustained3s_tflops"]), "measured: tools/fp64_peak.cu DMMA m8n8k4 sustained 3 s (profiles/r01_fp64_peak.json)"
+    except Exception:
+        return 37.1, "fallback: 148 SM x 64 FMA/clk x 2 x 1.965 GHz"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.lines, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "200"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+def cpu_jobs(spec, experts, seed=0):
+    from gpsat_b200 import synthetic as syn
+    th0, tk, ta, tb, tr = syn.default_fit_setup(spec, 1)
+    jobs = []
+    for e in experts:
+        X, y, Xs = syn.make_expert(spec, e, seed)
+        jobs.append((spec.kernel, X, y, Xs, th0[0], tk[0], ta[0], tb[0], tr[0], 10_000))
+    return jobs
+
+
+def run_reference(args):
+    """--impl reference: the oracle port of the reference path on all host cores (the reference
+    itself - GPflow/TensorFlow - is not installable here)."""
+    rank = int(os.environ.get("RANK", 0))
+    if rank != 0:
+        return
+    from oracle.cpu_baseline import CpuPool
+    spec = workload_spec(args)
+    cores = os.cpu_count() or 1
+    sample = args.cpu_sample or cores
+    pool = CpuPool(min(cores, sample))
+    times, done = [], 0
+    for s in range(args.warmup + args.steps):
+        experts = [(s * sample + k) % spec.E for k in range(sample)]
+        res, wall = pool.run(cpu_jobs(spec, experts))
+        if s >= args.warmup:
+            times.append(wall); done += len(res)
+    pool.close()
+    total = float(np.sum(times))
+    value = done / total
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * total / max(args.steps, 1),
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": spec.name, "experts_per_step": sample, "kernel": spec.kernel,
+                       "n_obs": [spec.n_lo, spec.n_hi], "n_pred": [spec.m_lo, spec.m_hi], "optimise": True},
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": min(cores, sample), "kind": "port",
+                             "sample": f"{sample} experts of {spec.name} per step, NumPy/SciPy oracle, "
+                                       f"one process per core, 1 BLAS thread each"},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from gpsat_b200 import parallel, synthetic as syn
+    from gpsat_b200.engine import Engine
+
+    rank, world, local = parallel.init_process_group()
+    assert world == args.gpus or world == 1, f"WORLD_SIZE={world} but --gpus {args.gpus}"
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py --impl ours needs a B200: the CUDA path has no CPU fallback")
+    torch.cuda.set_device(local)
+    spec = workload_spec(args)
+    E = spec.E
+    experts = range(rank * E, (rank + 1) * E)          # weak scaling: a fresh shard per rank
+    host = syn.make_batch(spec, seed=0, experts=experts, with_pred=True)
+    th0, tk, ta, tb, tr = syn.default_fit_setup(spec, E)
+
+    # optional CPU baseline (rank 0, N=1 only) - before CUDA is busy, worker processes are spawned
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle.cpu_baseline import CpuPool
+        cores = os.cpu_count() or 1
+        sample = args.cpu_sample or cores
+        pool = CpuPool(min(cores, sample))
+        res, wall = pool.run(cpu_jobs(spec, range(sample)))
+        pool.close()
+        cpu_baseline = {"value": len(res) / wall, "unit": UNIT, "cores": min(cores, sample), "kind": "port",
+                        "sample": f"first {sample} experts of {spec.name}, NumPy/SciPy oracle (SciPy L-BFGS-B + "
+                                  f"LAPACK), one process per core, 1 BLAS thread each, {wall:.1f} s wall",
+                        "mean_evals_per_expert": float(np.mean([r["nev"] for r in res]))}
+        cpu_check = res
+
+    eng = Engine(local)
+    stream = torch.cuda.ExternalStream(eng.stream_ptr, device=f"cuda:{local}")
+    dev = host.to_device(f"cuda:{local}")
+    d_args = [torch.as_tensor(a, device=f"cuda:{local}") for a in (th0, tk, ta, tb, tr)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")   # > 126 MB L2
+
+    def pin(a):
+        return None if a is None else torch.from_numpy(np.ascontiguousarray(a)).pin_memory().numpy()
+
+    host.X, host.y, host.Xs = pin(host.X), pin(host.y), pin(host.Xs)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_device(collect=None):
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        res = eng.fit(dev, *d_args)
+        if collect is not None:
+            s = eng.stats(); collect["fit"].append(s)
+        pred = eng.predict(dev, res.theta)
+        if collect is not None:
+            s = eng.stats(); collect["predict"].append(s)
+        return res, pred
+
+    def step_e2e():
+        res = eng.fit(host, th0, tk, ta, tb, tr)
+        s1 = eng.stats()
+        pred = eng.predict(host, res.theta)
+        s2 = eng.stats()
+        if world > 1:   # the single final gather
+            parallel.gather_results({"theta": res.theta, "lml": res.lml, "status": res.status},
+                                    np.arange(rank * E, (rank + 1) * E), world * E)
+        return res, pred, s1["h2d_bytes"] + s2["h2d_bytes"], s1["d2h_bytes"] + s2["d2h_bytes"]
+
+    # ---- device-resident timing (value) ----
+    for _ in range(args.warmup):
+        step_device()
+    eng.set_profile(True)
+    collect = {"fit": [], "predict": []}
+    barrier()
+    clocks = ClockSampler(local)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(args.steps):
+        res, pred = step_device(collect)
+    e1.record(stream)
+    barrier()
+    clk = clocks.stop()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=f"cuda:{local}")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_total = float(ms.item())
+    eng.set_profile(False)
+    value = world * E * args.steps / (ms_total * 1e-3)
+
+    # ---- per-kernel roofline numbers from the timed region ----
+    n = host.n.astype(np.float64)
+    m = host.m.astype(np.float64)
+    nev = res.n_evals.cpu().numpy().astype(np.float64)
+    # algorithmic FP64 flops of the step kernels: 2 n^3/3 per objective evaluation
+    # (potrf + trtri tiles), n^3/3 + n^2 m per prediction pass
+    flops_step = args.steps * float(np.sum(nev * 2.0 * n ** 3 / 3.0) + np.sum(n ** 3 / 3.0 + n ** 2 * m))
+    ms_step = sum(s["ms_step"] for k in collect for s in collect[k])
+    n_step = sum(s["n_step"] for k in collect for s in collect[k])
+    ms_lauum = sum(s["ms_lauum"] for s in collect["fit"])
+    ms_diag = sum(s["ms_diag"] for k in collect for s in collect[k])
+    ms_opt = sum(s["ms_opt"] for s in collect["fit"])
+    launches = sum(s["kernel_launches"] for k in collect for s in collect[k])
+    peak, peak_src = fp64_peak_tflops()
+    achieved = flops_step / (ms_step * 1e-3) / 1e12
+    total_flops = args.steps * float(np.sum(nev * n ** 3) + np.sum(n ** 3 / 3.0 + n ** 2 * m))
+    roofline = {"bound": "tensor", "kernel": "step_kernel (FP64 DMMA potrf/trtri tiles)", "achieved": achieved,
+                "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "launches": int(n_step), "avg_launch_ms": ms_step / max(n_step, 1),
+                "whole_job_tflops": total_flops / (ms_total * 1e-3) / 1e12,
+                "whole_job_frac": total_flops / (ms_total * 1e-3) / 1e12 / peak,
+                "kernel_share_of_step": {"step_kernel": ms_step / ms_total, "lauum_grad_kernel": ms_lauum / ms_total,
+                                         "diag_kernel": ms_diag / ms_total, "lbfgs_kernel": ms_opt / ms_total}}
+
+    # ---- end to end through the host-facing call ----
+    e2e = None
+    if not args.no_e2e:
+        step_e2e()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(args.steps):
+            res_h, pred_h, h2d, d2h = step_e2e()
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=f"cuda:{local}")
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": world * E * args.steps / float(dt.item()), "unit": UNIT,
+               "h2d_bytes_per_step": float(h2d), "d2h_bytes_per_step": float(d2h)}
+        # device-resident and host paths are the same arithmetic: results must agree bit for bit
+        assert np.array_equal(res_h.theta, res.theta.cpu().numpy())
+
+    if rank == 0:
+        if cpu_baseline is not None:   # the GPU results agree with the CPU sample (checker role of the oracle)
+            th = res.theta.cpu().numpy()
+            lm = res.lml.cpu().numpy()
+            dth, dl = 0.0, 0.0
+            for k, r in enumerate(cpu_check):
+                if r["ok"] and int(res.status[k]) == 0:
+                    dth = max(dth, float(np.max(np.abs(th[k] - r["theta"]) / np.abs(r["theta"]))))
+                    dl = max(dl, abs(lm[k] - r["lml"]) / abs(r["lml"]))
+            cpu_baseline["parity_vs_gpu"] = {"experts": len(cpu_check), "max_rel_theta": dth, "max_rel_lml": dl}
+            assert dl < 1e-4, f"optimised LML differs from the CPU oracle: {dl}"
+        st = np.bincount(res.status.cpu().numpy(), minlength=4)
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "config": {"workload": spec.name, "experts_per_gpu": E, "kernel": spec.kernel,
+                           "n_obs": [spec.n_lo, spec.n_hi], "n_pred": [spec.m_lo, spec.m_hi], "optimise": True,
+                           "parallelism": f"experts sharded x{world}, no collective on the hot path",
+                           "l2": "256 MB flush written between steps; per-step working set "
+                                 f"{eng.stats()['slots']} slot matrices >> 126 MB L2",
+                           "mean_evals_per_expert": float(nev.mean()),
+                           "status_counts": {"ok": int(st[0]), "not_pd": int(st[1]), "linesearch": int(st[2]), "maxiter": int(st[3])}},
+                "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
+                "clocks": clk}
+        print(json.dumps(line))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

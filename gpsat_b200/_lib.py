@@ -23,7 +23,7 @@ STATUS_OK, STATUS_NOT_PD, STATUS_LINESEARCH, STATUS_MAXITER, STATUS_BAD_INPUT = 
 
 EXPORTED_SYMBOLS = (
     "gpsat_version", "gpsat_last_error", "gpsat_engine_create", "gpsat_engine_destroy",
-    "gpsat_engine_stats", "gpsat_fit_options_default", "gpsat_gpr_lml_grad", "gpsat_gpr_fit",
+    "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_fit_options_default", "gpsat_gpr_lml_grad", "gpsat_gpr_fit",
     "gpsat_gpr_predict", "gpsat_gpr_factor_debug",
 )
 
@@ -42,7 +42,11 @@ class FitOptions(C.Structure):
 class Stats(C.Structure):
     _fields_ = [("kernel_launches", C.c_int64), ("ticks", C.c_int64), ("evals", C.c_int64),
                 ("slots", C.c_int64), ("h2d_bytes", C.c_double), ("d2h_bytes", C.c_double),
-                ("gpu_ms", C.c_double), ("sweep_flops", C.c_double)]
+                ("gpu_ms", C.c_double), ("sweep_flops", C.c_double),
+                ("ms_diag", C.c_double), ("ms_step", C.c_double), ("ms_lauum", C.c_double),
+                ("ms_opt", C.c_double), ("ms_reduce", C.c_double),
+                ("n_diag", C.c_int64), ("n_step", C.c_int64), ("n_lauum", C.c_int64),
+                ("n_opt", C.c_int64), ("n_reduce", C.c_int64)]
 
 
 _lib = None
@@ -64,6 +68,9 @@ def load():
     lib.gpsat_engine_create.argtypes = [C.c_int, C.POINTER(vp)]
     lib.gpsat_engine_destroy.argtypes = [vp]
     lib.gpsat_engine_stats.argtypes = [vp, C.POINTER(Stats)]
+    lib.gpsat_engine_stream.argtypes = [vp]
+    lib.gpsat_engine_stream.restype = vp
+    lib.gpsat_engine_set_profile.argtypes = [vp, C.c_int]
     lib.gpsat_fit_options_default.argtypes = [C.POINTER(FitOptions)]
     lib.gpsat_fit_options_default.restype = None
     lib.gpsat_gpr_lml_grad.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp]

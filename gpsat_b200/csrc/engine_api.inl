@@ -8,6 +8,14 @@ extern "C" {
 int gpsat_version(void) { return 100; }
 const char* gpsat_last_error(void) { return g_last_error.c_str(); }
 
+void* gpsat_engine_stream(const gpsat_engine* h) { return h ? (void*)h->e.stream : nullptr; }
+
+int gpsat_engine_set_profile(gpsat_engine* h, int on) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  h->e.profile = on != 0;
+  return 0;
+}
+
 void gpsat_fit_options_default(gpsat_fit_options* o) {
   o->pgtol = 1e-5;
   o->ftol = 2.220446049250313e-09;
@@ -42,6 +50,7 @@ int gpsat_engine_destroy(gpsat_engine* h) {
   Engine& g = h->e;
   cudaSetDevice(g.device);
   cudaStreamSynchronize(g.stream);
+  for (cudaEvent_t ev : g.evpool) cudaEventDestroy(ev);
   for (DevBuf* b : {&g.bX, &g.by, &g.bXs, &g.boffn, &g.boffm, &g.border, &g.btheta, &g.bmisc, &g.bslots,
                     &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout})
     b->release();
@@ -70,6 +79,7 @@ static int stage_in(Engine& g, int mem, const void* src, size_t bytes, void* dev
 static void begin_call(Engine& g) {
   cudaSetDevice(g.device);
   g.stats = gpsat_stats{};
+  g.evtype.clear();
   cudaEventRecord(g.ev0, g.stream);
 }
 static int end_call(Engine& g) {
@@ -78,6 +88,7 @@ static int end_call(Engine& g) {
   float ms = 0.f;
   CUDA_TRY(cudaEventElapsedTime(&ms, g.ev0, g.ev1));
   g.stats.gpu_ms = ms;
+  if (g.profile) prof_collect(g);
   return 0;
 }
 
@@ -170,6 +181,7 @@ int gpsat_gpr_predict(gpsat_engine* h, const gpsat_batch* batch, int mem, const 
     eval_init_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(slots, mems, bd, (const double*)dtheta, (int)b0, S, 1, ld);
     if (launch_sweep(g, S, Tb, TRb, false)) return 1;
     if (mb > 0) {
+      ProfScope ps(g, PROF_REDUCE);
       predict_reduce_kernel<<<dim3((unsigned)((mb * 32 + 255) / 256), S), 256, 0, g.stream>>>(slots, bd.off_m, dfm, dfv, dyv);
       g.stats.kernel_launches++;
     }

@@ -66,7 +66,10 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
     if (occupied == 0) break;
     CUDA_TRY(cudaMemsetAsync(fd.counters + 1, 0, 2 * sizeof(int), g.stream));
     if (launch_sweep(g, S, Tcur, Tcur, true)) return 1;
-    lbfgs_kernel<<<(S + 63) / 64, 64, 0, g.stream>>>(slots, mems, bd, fd, S, ld);
+    {
+      ProfScope ps(g, PROF_OPT);
+      lbfgs_kernel<<<(S + 63) / 64, 64, 0, g.stream>>>(slots, mems, bd, fd, S, ld);
+    }
     g.stats.kernel_launches++;
     g.stats.ticks++;
   }

@@ -33,7 +33,45 @@ struct Engine {
   std::vector<int64_t> hn, hm;
   std::vector<int> order;
   int Tmax = 0, TRmax = 0;
+  // optional per-kernel timing (gpsat_engine_set_profile)
+  bool profile = false;
+  std::vector<cudaEvent_t> evpool;
+  std::vector<int> evtype;          // kernel type of event pair k (events 2k, 2k+1)
 };
+
+enum ProfType : int { PROF_DIAG = 0, PROF_STEP = 1, PROF_LAUUM = 2, PROF_OPT = 3, PROF_REDUCE = 4 };
+
+// Brackets one kernel launch with a pair of events on the engine's stream when profiling is on.
+struct ProfScope {
+  Engine& g;
+  bool on;
+  ProfScope(Engine& g_, int type) : g(g_), on(g_.profile) {
+    if (!on) return;
+    size_t k = g.evtype.size();
+    while (g.evpool.size() < 2 * (k + 1)) {
+      cudaEvent_t e;
+      cudaEventCreate(&e);
+      g.evpool.push_back(e);
+    }
+    g.evtype.push_back(type);
+    cudaEventRecord(g.evpool[2 * k], g.stream);
+  }
+  ~ProfScope() {
+    if (on) cudaEventRecord(g.evpool[2 * g.evtype.size() - 1], g.stream);
+  }
+};
+
+static void prof_collect(Engine& g) {
+  double* ms[5] = {&g.stats.ms_diag, &g.stats.ms_step, &g.stats.ms_lauum, &g.stats.ms_opt, &g.stats.ms_reduce};
+  int64_t* cnt[5] = {&g.stats.n_diag, &g.stats.n_step, &g.stats.n_lauum, &g.stats.n_opt, &g.stats.n_reduce};
+  for (size_t k = 0; k < g.evtype.size(); ++k) {
+    float t = 0.f;
+    cudaEventElapsedTime(&t, g.evpool[2 * k], g.evpool[2 * k + 1]);
+    *ms[g.evtype[k]] += t;
+    *cnt[g.evtype[k]] += 1;
+  }
+  g.evtype.clear();
+}
 
 static int align_up(int v, int a) { return (v + a - 1) / a * a; }
 
@@ -153,15 +191,20 @@ static int choose_slots(Engine& g, int64_t E, int Tmax, int TRmax, int max_slots
 static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv) {
   const SlotDesc* slots = g.bslots.as<SlotDesc>();
   for (int i = 0; i < Tmax; ++i) {
-    diag_kernel<<<S, GPSAT_THREADS, DIAG_SMEM_BYTES, g.stream>>>(slots, i);
+    {
+      ProfScope ps(g, PROF_DIAG);
+      diag_kernel<<<S, GPSAT_THREADS, DIAG_SMEM_BYTES, g.stream>>>(slots, i);
+    }
     g.stats.kernel_launches++;
     int ntile = (TRmax - 1 - i) + (do_inv ? i : 0);
     if (ntile > 0) {
+      ProfScope ps(g, PROF_STEP);
       step_kernel<<<dim3(ntile, S), GPSAT_THREADS, STEP_SMEM_BYTES, g.stream>>>(slots, i, do_inv ? 1 : 0);
       g.stats.kernel_launches++;
     }
   }
   if (do_inv) {
+    ProfScope ps(g, PROF_LAUUM);
     lauum_grad_kernel<<<dim3(Tmax * (Tmax + 1) / 2, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots);
     g.stats.kernel_launches++;
   }

@@ -157,6 +157,15 @@ class Engine:
         except Exception:
             pass
 
+    def set_profile(self, on: bool):
+        """Bracket every kernel launch with CUDA events; per-kernel times appear in :meth:`stats`."""
+        _lib.check(self._lib.gpsat_engine_set_profile(self._h, int(bool(on))))
+
+    @property
+    def stream_ptr(self) -> int:
+        """cudaStream_t of the engine (wrap with torch.cuda.ExternalStream to record events on it)."""
+        return int(self._lib.gpsat_engine_stream(self._h))
+
     def stats(self) -> dict:
         s = _lib.Stats()
         _lib.check(self._lib.gpsat_engine_stats(self._h, C.byref(s)))
@@ -179,6 +188,13 @@ class Engine:
             return torch.as_tensor(np.ascontiguousarray(a, dtype=dtype).reshape(shape), device=batch.X.device)
         return np.ascontiguousarray(a, dtype=dtype).reshape(shape)
 
+    def _pre(self, batch: RaggedBatch):
+        """Device inputs were produced on torch's current stream; the engine runs on its own
+        non-blocking stream, so order the two before handing pointers over."""
+        if batch.on_device:
+            import torch
+            torch.cuda.current_stream(batch.X.device).synchronize()
+
     def lml_grad(self, batch: RaggedBatch, theta, with_grad: bool = True):
         E, P = batch.E, batch.D + 2
         mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
@@ -187,6 +203,7 @@ class Engine:
         grad = self._empty(batch, (E, P), np.float64) if with_grad else None
         status = self._empty(batch, (E,), np.int32)
         cb = batch._c(False)
+        self._pre(batch)
         _lib.check(self._lib.gpsat_gpr_lml_grad(self._h, C.byref(cb), mem, _ptr(th), _ptr(lml), _ptr(grad), _ptr(status)))
         return lml, grad, status
 
@@ -207,6 +224,7 @@ class Engine:
         status = self._empty(batch, (E,), np.int32)
         opt = _lib.FitOptions(pgtol, ftol, int(max_iter), int(maxfun), int(maxls), int(max_slots))
         cb = batch._c(False)
+        self._pre(batch)
         _lib.check(self._lib.gpsat_gpr_fit(self._h, C.byref(cb), mem, _ptr(th), _ptr(tk), _ptr(a), _ptr(b), _ptr(tr),
                                            C.byref(opt), _ptr(lml), _ptr(nev), _ptr(nit), _ptr(status)))
         return FitResult(th, lml, nev, nit, status)
@@ -222,6 +240,7 @@ class Engine:
         lml = self._empty(batch, (E,), np.float64)
         status = self._empty(batch, (E,), np.int32)
         cb = batch._c(True)
+        self._pre(batch)
         _lib.check(self._lib.gpsat_gpr_predict(self._h, C.byref(cb), mem, _ptr(th), _ptr(fm), _ptr(fv), _ptr(yv),
                                                _ptr(lml), _ptr(status)))
         return {"f*": fm, "f*_var": fv, "y_var": yv, "lml": lml, "status": status}

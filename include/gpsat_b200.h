@@ -94,6 +94,10 @@ typedef struct {
   double d2h_bytes;
   double gpu_ms;           /* CUDA-event time of the last call, copies included */
   double sweep_flops;      /* sum over evaluations of n^3 (+ n^2 m for predict) */
+  /* filled when profiling is on (gpsat_engine_set_profile): CUDA-event time per kernel type,
+   * summed over the launches of the last call, and the launch counts */
+  double ms_diag, ms_step, ms_lauum, ms_opt, ms_reduce;
+  int64_t n_diag, n_step, n_lauum, n_opt, n_reduce;
 } gpsat_stats;
 
 int gpsat_version(void);
@@ -102,6 +106,10 @@ const char* gpsat_last_error(void);
 int gpsat_engine_create(int device, gpsat_engine** out);
 int gpsat_engine_destroy(gpsat_engine* eng);
 int gpsat_engine_stats(const gpsat_engine* eng, gpsat_stats* out);
+/* cudaStream_t the engine launches on (so callers can record their own events on it). */
+void* gpsat_engine_stream(const gpsat_engine* eng);
+/* on != 0: bracket every kernel launch with CUDA events and report per-kernel times in stats. */
+int gpsat_engine_set_profile(gpsat_engine* eng, int on);
 void gpsat_fit_options_default(gpsat_fit_options* opt);
 
 /* lml[e] = log marginal likelihood, grad[e][P] = d lml / d theta (constrained space). */

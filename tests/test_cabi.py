@@ -35,7 +35,7 @@ def test_version_and_defaults(built):
 def test_struct_layouts_match_header():
     assert C.sizeof(_lib.Batch) == 56
     assert C.sizeof(_lib.FitOptions) == 32
-    assert C.sizeof(_lib.Stats) == 64
+    assert C.sizeof(_lib.Stats) == 144
 
 
 def test_no_cpu_fallback(built):
