@@ -22,9 +22,9 @@ TRANSFORM_SIGMOID = 1
 STATUS_OK, STATUS_NOT_PD, STATUS_LINESEARCH, STATUS_MAXITER, STATUS_BAD_INPUT = range(5)
 
 EXPORTED_SYMBOLS = (
-    "gpsat_version", "gpsat_last_error", "gpsat_engine_create", "gpsat_engine_destroy",
-    "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_fit_options_default", "gpsat_gpr_lml_grad", "gpsat_gpr_fit",
-    "gpsat_gpr_predict", "gpsat_gpr_factor_debug",
+    "gpsat_version", "gpsat_last_error", "gpsat_device_name", "gpsat_engine_create", "gpsat_engine_destroy",
+    "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_fit_options_default",
+    "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_factor_debug",
 )
 
 
@@ -37,6 +37,10 @@ class Batch(C.Structure):
 class FitOptions(C.Structure):
     _fields_ = [("pgtol", C.c_double), ("ftol", C.c_double), ("maxiter", C.c_int32),
                 ("maxfun", C.c_int32), ("maxls", C.c_int32), ("max_slots", C.c_int32)]
+
+
+class Priors(C.Structure):
+    _fields_ = [("kind", C.c_void_p), ("a", C.c_void_p), ("b", C.c_void_p)]
 
 
 class Stats(C.Structure):
@@ -65,6 +69,7 @@ def load():
     vp = C.c_void_p
     lib.gpsat_version.restype = C.c_int
     lib.gpsat_last_error.restype = C.c_char_p
+    lib.gpsat_device_name.argtypes = [C.c_int, C.c_char_p, C.c_size_t]
     lib.gpsat_engine_create.argtypes = [C.c_int, C.POINTER(vp)]
     lib.gpsat_engine_destroy.argtypes = [vp]
     lib.gpsat_engine_stats.argtypes = [vp, C.POINTER(Stats)]
@@ -75,11 +80,18 @@ def load():
     lib.gpsat_fit_options_default.restype = None
     lib.gpsat_gpr_lml_grad.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp]
     lib.gpsat_gpr_fit.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp,
-                                  C.POINTER(FitOptions), vp, vp, vp, vp]
+                                  C.POINTER(FitOptions), C.POINTER(Priors), vp, vp, vp, vp, vp]
     lib.gpsat_gpr_predict.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp, vp]
     lib.gpsat_gpr_factor_debug.argtypes = [vp, C.POINTER(Batch), vp, vp, vp]
     _lib = lib
     return lib
+
+
+def device_name(device: int = 0) -> str:
+    """Name of CUDA device `device` (raises if the library or the device is missing)."""
+    buf = C.create_string_buffer(256)
+    check(load().gpsat_device_name(int(device), buf, 256))
+    return buf.value.decode()
 
 
 def last_error() -> str:

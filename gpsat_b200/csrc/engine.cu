@@ -64,7 +64,11 @@ struct FitDev {
   const double* ta;
   const double* tb;
   const unsigned char* trainable;
-  double* lml;
+  const int* pkind;         // [E][P] prior family, nullptr = no priors
+  const double* pa;
+  const double* pb;
+  double* objective;        // [E] minimised value at the optimum: -(lml + log prior)
+  double* lml;              // [E] log marginal likelihood at the optimum (may be nullptr)
   int* n_evals;
   int* n_iters;
   int* status;
@@ -99,6 +103,34 @@ __device__ __forceinline__ double transform_inv(int kind, double a, double b, do
 __device__ __forceinline__ double transform_dfwd(int kind, double a, double b, double xi) {
   double s = dev_sigmoid(xi);
   return kind == GPSAT_TRANSFORM_SIGMOID ? (b - a) * s * (1.0 - s) : s;
+}
+
+// log prior density of one trainable parameter in GPflow's convention (gpflow.Parameter.
+// log_prior_density with prior_on = constrained): log p(theta) + log |d theta / d xi|.
+// Returns the value and adds its derivative w.r.t. xi to *dxi.
+__device__ __forceinline__ double log_prior_xi(int pk, double pa, double pb, int tk, double ta, double tb,
+                                               double xi, double th, double* dxi) {
+  if (pk == GPSAT_PRIOR_NONE) return 0.0;
+  const double HALF_LOG2PI = 0.9189385332046727;
+  double lp, dlp;
+  if (pk == GPSAT_PRIOR_NORMAL) {
+    double z = (th - pa) / pb;
+    lp = -0.5 * z * z - log(pb) - HALF_LOG2PI;
+    dlp = -z / pb;
+  } else if (pk == GPSAT_PRIOR_LOGNORMAL) {
+    double lt = log(th), z = (lt - pa) / pb;
+    lp = -lt - log(pb) - HALF_LOG2PI - 0.5 * z * z;
+    dlp = -(1.0 + z / pb) / th;
+  } else {
+    lp = pa * log(pb) - lgamma(pa) + (pa - 1.0) * log(th) - pb * th;
+    dlp = (pa - 1.0) / th - pb;
+  }
+  double s = dev_sigmoid(xi);
+  double ldj, dldj;
+  if (tk == GPSAT_TRANSFORM_SIGMOID) { ldj = log(tb - ta) + log(s) + log1p(-s); dldj = 1.0 - 2.0 * s; }
+  else { ldj = -dev_softplus(-xi); dldj = 1.0 - s; }
+  *dxi += dlp * transform_dfwd(tk, ta, tb, xi) + dldj;
+  return lp + ldj;
 }
 
 __device__ __forceinline__ void slot_set_expert(SlotDesc& d, const SlotMem& mem, const BatchDev& b, int e,
@@ -203,7 +235,21 @@ __global__ void lbfgs_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, F
       }
     }
   }
-  double fval = isfinite(lml) ? -lml : INFINITY;
+  double logprior = 0.0;
+  if (f.pkind) {
+    int k = 0;
+    for (int p = 0; p < P; ++p) {
+      size_t q = (size_t)e * P + p;
+      if (f.trainable[q]) {
+        double dxi = 0.0;
+        logprior += log_prior_xi(f.pkind[q], f.pa[q], f.pb[q], f.tkind[q], f.ta[q], f.tb[q], st.xtrial[k],
+                                 theta[p], &dxi);
+        gxi[k] -= dxi;
+        ++k;
+      }
+    }
+  }
+  double fval = isfinite(lml) ? -lml - logprior : INFINITY;
   atomicAdd(&f.counters[3], 1);
   int rc = lbfgs_step(&st, fval, gxi, &f.opt);
   if (rc != LBFGS_CONTINUE) {
@@ -213,7 +259,22 @@ __global__ void lbfgs_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, F
       size_t q = (size_t)e * P + p;
       if (f.trainable[q]) f.theta[q] = transform_fwd(f.tkind[q], f.ta[q], f.tb[q], st.x[k++]);
     }
-    f.lml[e] = -st.f;
+    f.objective[e] = st.f;
+    if (f.lml) {
+      double lp = 0.0;
+      if (f.pkind) {
+        int kk = 0;
+        for (int p = 0; p < P; ++p) {
+          size_t q = (size_t)e * P + p;
+          if (f.trainable[q]) {
+            double dxi = 0.0;
+            lp += log_prior_xi(f.pkind[q], f.pa[q], f.pb[q], f.tkind[q], f.ta[q], f.tb[q], st.x[kk], f.theta[q], &dxi);
+            ++kk;
+          }
+        }
+      }
+      f.lml[e] = -st.f - lp;
+    }
     f.n_evals[e] = st.nfev;
     f.n_iters[e] = st.iter;
     int status = GPSAT_STATUS_OK;

@@ -25,6 +25,17 @@ void gpsat_fit_options_default(gpsat_fit_options* o) {
   o->max_slots = 0;
 }
 
+int gpsat_device_name(int device, char* buf, size_t len) {
+  REQUIRE(buf != nullptr && len > 0, "buf is NULL");
+  int count = 0;
+  CUDA_TRY(cudaGetDeviceCount(&count));
+  REQUIRE(device >= 0 && device < count, "no such CUDA device");
+  cudaDeviceProp prop;
+  CUDA_TRY(cudaGetDeviceProperties(&prop, device));
+  snprintf(buf, len, "%s", prop.name);
+  return 0;
+}
+
 int gpsat_engine_create(int device, gpsat_engine** out) {
   REQUIRE(out != nullptr, "out is NULL");
   int count = 0;

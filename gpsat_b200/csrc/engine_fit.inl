@@ -3,11 +3,13 @@ extern "C" {
 
 int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* theta_io, const int32_t* tkind,
                   const double* ta, const double* tb, const uint8_t* trainable, const gpsat_fit_options* opt_in,
-                  double* lml, int32_t* n_evals, int32_t* n_iters, int32_t* status) {
+                  const gpsat_priors* priors, double* objective, double* lml, int32_t* n_evals, int32_t* n_iters,
+                  int32_t* status) {
   REQUIRE(h != nullptr, "engine is NULL");
   if (check_batch(batch, false)) return 2;
   REQUIRE(theta_io && tkind && ta && tb && trainable, "theta / transform argument is NULL");
-  REQUIRE(lml && n_evals && n_iters && status, "output argument is NULL");
+  REQUIRE(objective && n_evals && n_iters && status, "output argument is NULL");
+  REQUIRE(!priors || (priors->kind && priors->a && priors->b), "priors has a NULL member");
   gpsat_fit_options opt;
   if (opt_in) opt = *opt_in; else gpsat_fit_options_default(&opt);
   REQUIRE(opt.maxls > 0 && opt.maxiter >= 0 && opt.maxfun >= 0, "bad fit options");
@@ -22,10 +24,12 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   int ld = 0;
   if (engine_alloc_slots(g, S, g.Tmax, g.Tmax, ld)) return 1;
 
-  // per-expert arrays on the device: [theta | ta | tb | lml] doubles, [tkind | nev | nit | status] ints, trainable
+  // per-expert arrays on the device: [theta | ta | tb | pa | pb | lml | obj] doubles,
+  // [tkind | pkind | nev | nit | status] ints, trainable bytes, counters
   const size_t EP = (size_t)E * P;
-  size_t o_theta = 0, o_ta = o_theta + EP * 8, o_tb = o_ta + EP * 8, o_lml = o_tb + EP * 8;
-  size_t o_tk = o_lml + (size_t)E * 8, o_nev = o_tk + EP * 4, o_nit = o_nev + (size_t)E * 4;
+  size_t o_theta = 0, o_ta = o_theta + EP * 8, o_tb = o_ta + EP * 8, o_pa = o_tb + EP * 8, o_pb = o_pa + EP * 8;
+  size_t o_lml = o_pb + EP * 8, o_obj = o_lml + (size_t)E * 8;
+  size_t o_tk = o_obj + (size_t)E * 8, o_pk = o_tk + EP * 4, o_nev = o_pk + EP * 4, o_nit = o_nev + (size_t)E * 4;
   size_t o_st = o_nit + (size_t)E * 4, o_tr = o_st + (size_t)E * 4, o_cnt = (o_tr + EP + 15) & ~(size_t)15;
   if (g.bout.ensure(o_cnt + 16) || g.bstates.ensure(sizeof(LbfgsState) * S)) return 1;
   char* base = g.bout.as<char>();
@@ -42,7 +46,14 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   if (stage_in(g, mem, tb, EP * 8, base + o_tb, &p)) return 1; fd.tb = (const double*)p;
   if (stage_in(g, mem, tkind, EP * 4, base + o_tk, &p)) return 1; fd.tkind = (const int*)p;
   if (stage_in(g, mem, trainable, EP, base + o_tr, &p)) return 1; fd.trainable = (const unsigned char*)p;
-  fd.lml = dev ? lml : reinterpret_cast<double*>(base + o_lml);
+  fd.pkind = nullptr; fd.pa = nullptr; fd.pb = nullptr;
+  if (priors) {
+    if (stage_in(g, mem, priors->kind, EP * 4, base + o_pk, &p)) return 1; fd.pkind = (const int*)p;
+    if (stage_in(g, mem, priors->a, EP * 8, base + o_pa, &p)) return 1; fd.pa = (const double*)p;
+    if (stage_in(g, mem, priors->b, EP * 8, base + o_pb, &p)) return 1; fd.pb = (const double*)p;
+  }
+  fd.objective = dev ? objective : reinterpret_cast<double*>(base + o_obj);
+  fd.lml = lml ? (dev ? lml : reinterpret_cast<double*>(base + o_lml)) : nullptr;
   fd.n_evals = dev ? n_evals : reinterpret_cast<int*>(base + o_nev);
   fd.n_iters = dev ? n_iters : reinterpret_cast<int*>(base + o_nit);
   fd.status = dev ? status : reinterpret_cast<int*>(base + o_st);
@@ -76,11 +87,12 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   g.stats.evals = evals; g.stats.slots = S;
   if (!dev) {
     CUDA_TRY(cudaMemcpyAsync(theta_io, fd.theta, EP * 8, cudaMemcpyDeviceToHost, g.stream));
-    CUDA_TRY(cudaMemcpyAsync(lml, fd.lml, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(objective, fd.objective, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
+    if (lml) CUDA_TRY(cudaMemcpyAsync(lml, fd.lml, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
     CUDA_TRY(cudaMemcpyAsync(n_evals, fd.n_evals, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
     CUDA_TRY(cudaMemcpyAsync(n_iters, fd.n_iters, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
     CUDA_TRY(cudaMemcpyAsync(status, fd.status, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
-    g.stats.d2h_bytes += (double)EP * 8 + (double)E * 20;
+    g.stats.d2h_bytes += (double)EP * 8 + (double)E * (20 + (lml ? 8 : 0));
   }
   CUDA_TRY(cudaGetLastError());
   if (end_call(g)) return 1;

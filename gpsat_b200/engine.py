@@ -126,6 +126,7 @@ class RaggedBatch:
 @dataclass
 class FitResult:
     theta: object
+    objective: object      # minimised value -(lml + log prior): gpflow's training_loss at the optimum
     lml: object
     n_evals: object
     n_iters: object
@@ -209,7 +210,8 @@ class Engine:
 
     def fit(self, batch: RaggedBatch, theta0, tkind, ta, tb, trainable, *, max_iter: int = 10_000,
             pgtol: float = 1e-5, ftol: float = SCIPY_FTOL, maxfun: int = 15_000, maxls: int = 20,
-            max_slots: int = 0) -> FitResult:
+            max_slots: int = 0, priors=None) -> FitResult:
+        """Batched L-BFGS fit.  ``priors``: optional ``(kind[E,P], a[E,P], b[E,P])`` (GPSAT_PRIOR_*)."""
         E, P = batch.E, batch.D + 2
         mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
         th = self._in(batch, theta0, np.float64, (E, P))
@@ -219,6 +221,12 @@ class Engine:
         b = self._in(batch, tb, np.float64, (E, P))
         tr = self._in(batch, trainable, np.uint8, (E, P))
         lml = self._empty(batch, (E,), np.float64)
+        obj = self._empty(batch, (E,), np.float64)
+        pri, keep = None, None
+        if priors is not None:
+            keep = (self._in(batch, priors[0], np.int32, (E, P)), self._in(batch, priors[1], np.float64, (E, P)),
+                    self._in(batch, priors[2], np.float64, (E, P)))
+            pri = _lib.Priors(_ptr(keep[0]).value, _ptr(keep[1]).value, _ptr(keep[2]).value)
         nev = self._empty(batch, (E,), np.int32)
         nit = self._empty(batch, (E,), np.int32)
         status = self._empty(batch, (E,), np.int32)
@@ -226,8 +234,9 @@ class Engine:
         cb = batch._c(False)
         self._pre(batch)
         _lib.check(self._lib.gpsat_gpr_fit(self._h, C.byref(cb), mem, _ptr(th), _ptr(tk), _ptr(a), _ptr(b), _ptr(tr),
-                                           C.byref(opt), _ptr(lml), _ptr(nev), _ptr(nit), _ptr(status)))
-        return FitResult(th, lml, nev, nit, status)
+                                           C.byref(opt), C.byref(pri) if pri is not None else None, _ptr(obj),
+                                           _ptr(lml), _ptr(nev), _ptr(nit), _ptr(status)))
+        return FitResult(th, obj, lml, nev, nit, status)
 
     def predict(self, batch: RaggedBatch, theta):
         E, P = batch.E, batch.D + 2

@@ -63,6 +63,14 @@ extern "C" {
 
 #define GPSAT_MAX_DIMS 6
 
+/* prior families (extension; the reference never sets a prior).  GPflow convention:
+ * training_loss = -(lml + sum_p [log p(theta_p) + log |d theta_p / d xi_p|]) for parameters that
+ * carry a prior on their constrained value. */
+#define GPSAT_PRIOR_NONE 0
+#define GPSAT_PRIOR_NORMAL 1         /* a = mean, b = standard deviation  */
+#define GPSAT_PRIOR_LOGNORMAL 2      /* a = mu,   b = sigma (of log theta) */
+#define GPSAT_PRIOR_GAMMA 3          /* a = shape (concentration), b = rate */
+
 typedef struct gpsat_engine gpsat_engine;
 
 typedef struct {
@@ -86,6 +94,12 @@ typedef struct {
 } gpsat_fit_options;
 
 typedef struct {
+  const int32_t* kind;     /* [E][P] GPSAT_PRIOR_*; same memory space as the other per-expert arrays */
+  const double* a;         /* [E][P] */
+  const double* b;         /* [E][P] */
+} gpsat_priors;
+
+typedef struct {
   int64_t kernel_launches; /* kernels launched by the last call      */
   int64_t ticks;           /* batched objective evaluations (sweeps) */
   int64_t evals;           /* per-expert objective evaluations       */
@@ -103,6 +117,11 @@ typedef struct {
 int gpsat_version(void);
 const char* gpsat_last_error(void);
 
+/* Name of CUDA device `device` (what the reference stores in run_details.device through
+ * BaseGPRModel.gpu_name, GPSat/models/base_model.py:279-300).  Returns 0 and a NUL-terminated
+ * string in buf, non-zero if there is no such device. */
+int gpsat_device_name(int device, char* buf, size_t len);
+
 int gpsat_engine_create(int device, gpsat_engine** out);
 int gpsat_engine_destroy(gpsat_engine* eng);
 int gpsat_engine_stats(const gpsat_engine* eng, gpsat_stats* out);
@@ -118,11 +137,13 @@ int gpsat_gpr_lml_grad(gpsat_engine* eng, const gpsat_batch* batch, int mem, con
 
 /* Batched L-BFGS in unconstrained space.  theta_io: start values in, optimum out.
  * tkind/ta/tb: transform per parameter; trainable: 1 = optimise, 0 = keep fixed.
- * lml: value at the optimum; n_evals / n_iters: SciPy nfev / nit equivalents. */
+ * priors: may be NULL (no priors).  objective: the minimised value -(lml + log prior) at the
+ * optimum, i.e. gpflow's training_loss; lml: the log marginal likelihood alone (may be NULL);
+ * n_evals / n_iters: SciPy nfev / nit equivalents. */
 int gpsat_gpr_fit(gpsat_engine* eng, const gpsat_batch* batch, int mem, double* theta_io,
                   const int32_t* tkind, const double* ta, const double* tb, const uint8_t* trainable,
-                  const gpsat_fit_options* opt, double* lml, int32_t* n_evals, int32_t* n_iters,
-                  int32_t* status);
+                  const gpsat_fit_options* opt, const gpsat_priors* priors, double* objective, double* lml,
+                  int32_t* n_evals, int32_t* n_iters, int32_t* status);
 
 /* Predictive mean / variance at batch->Xs for fixed theta: fmean = f*, fvar = f*_var,
  * yvar = f*_var + likelihood variance; lml[e] as a by-product of the same factorisation. */

@@ -259,11 +259,52 @@ class Transform:
 
 
 # ----------------------------------------------------------------------------------------------
+# priors (gpflow.Parameter.log_prior_density; the reference only ever passes prior=None through,
+# gpflow_models.py:617,624, so this restates GPflow's published convention and is parity-unpinned)
+# ----------------------------------------------------------------------------------------------
+
+PRIOR_NONE, PRIOR_NORMAL, PRIOR_LOGNORMAL, PRIOR_GAMMA = 0, 1, 2, 3
+
+
+def log_prior_xi(pkind, pa, pb, transform, xi, trainable):
+    """sum over trainable parameters with a prior of  log p(theta) + log|d theta/d xi|
+    (prior on the constrained value, GPflow's default ``prior_on``), and its gradient in xi."""
+    import scipy.special as sps
+    xi = np.asarray(xi, float)
+    theta = transform.forward(xi)
+    total, grad = 0.0, np.zeros_like(xi)
+    for p in range(len(xi)):
+        if not trainable[p] or pkind[p] == PRIOR_NONE:
+            continue
+        th, a, b = theta[p], pa[p], pb[p]
+        if pkind[p] == PRIOR_NORMAL:
+            lp = -0.5 * ((th - a) / b) ** 2 - np.log(b) - 0.5 * LOG2PI
+            dlp = -(th - a) / b ** 2
+        elif pkind[p] == PRIOR_LOGNORMAL:
+            lp = -np.log(th) - np.log(b) - 0.5 * LOG2PI - 0.5 * ((np.log(th) - a) / b) ** 2
+            dlp = -1.0 / th - (np.log(th) - a) / (b ** 2 * th)
+        else:
+            lp = a * np.log(b) - sps.gammaln(a) + (a - 1.0) * np.log(th) - b * th
+            dlp = (a - 1.0) / th - b
+        s = float(sigmoid(xi[p]))
+        if transform.kind[p] == TRANSFORM_SIGMOID:
+            ldj = np.log(transform.b[p] - transform.a[p]) + np.log(s) + np.log1p(-s)
+            dldj = 1.0 - 2.0 * s
+        else:
+            ldj = -float(softplus(-xi[p]))
+            dldj = 1.0 - s
+        total += lp + ldj
+        grad[p] = dlp * transform.dtheta_dxi(xi)[p] + dldj
+    return total, grad
+
+
+# ----------------------------------------------------------------------------------------------
 # fit
 # ----------------------------------------------------------------------------------------------
 
-def objective_and_grad_xi(kind, X, y, xi_free, theta0, trainable, transform, mode="direct"):
-    """-lml and its gradient w.r.t. the free unconstrained variables (training_loss + autodiff)."""
+def objective_and_grad_xi(kind, X, y, xi_free, theta0, trainable, transform, mode="direct", priors=None):
+    """-(lml + log prior) and its gradient w.r.t. the free unconstrained variables
+    (training_loss + autodiff)."""
     xi_full = transform.inverse(theta0)
     xi_full[trainable] = xi_free
     theta = np.where(trainable, transform.forward(xi_full), theta0)
@@ -271,11 +312,15 @@ def objective_and_grad_xi(kind, X, y, xi_free, theta0, trainable, transform, mod
     if not np.isfinite(val):
         return np.inf, np.zeros(int(np.sum(trainable)))
     g_xi = -g_theta * transform.dtheta_dxi(xi_full)
+    if priors is not None:
+        lp, glp = log_prior_xi(priors[0], priors[1], priors[2], transform, xi_full, trainable)
+        val += lp
+        g_xi = g_xi - glp
     return -val, g_xi[trainable]
 
 
 def fit(kind, X, y, theta0, transform=None, trainable=None, max_iter=10_000, mode="direct",
-        return_result=False):
+        return_result=False, priors=None):
     """gpflow.optimizers.Scipy().minimize(training_loss, trainable_variables,
     options=dict(maxiter=max_iter))  (reference call: gpflow_models.py:317-321).
 
@@ -290,7 +335,7 @@ def fit(kind, X, y, theta0, transform=None, trainable=None, max_iter=10_000, mod
     xi0 = transform.inverse(theta0)
 
     def fun(xi_free):
-        return objective_and_grad_xi(kind, X, y, xi_free, theta0, trainable, transform, mode)
+        return objective_and_grad_xi(kind, X, y, xi_free, theta0, trainable, transform, mode, priors)
 
     if not trainable.any():
         return theta0, lml(kind, X, y, theta0, mode), True, 0
