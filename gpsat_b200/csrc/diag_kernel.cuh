@@ -1,36 +1,52 @@
 // diag_kernel: in-shared-memory Cholesky + triangular inverse of one 128 x 128 diagonal tile
 // per expert ("batched in-SM Cholesky of K + s2 I" for experts with n < 128, and the panel
 // step of the blocked factorisation for larger ones).
+//
+// Blocked right-looking factorisation with 32-wide panels, all in shared memory:
+//   for p in 0..3:  warp 0 factors the 32 x 32 diagonal block in registers (one row per lane) and
+//                   inverts it (one column per lane);  all warps: rows below *= W_pp^T (DMMA),
+//                   trailing block -= panel panel^T (DMMA, lower fragments only)
+//   then U = L^-T block by block (the 32-granular twin of the trtri tiles of step_kernel).
+// The tile is "augmented": local row ncol (global row n) is the observation row y^T and rides
+// along, later rows are prediction rows / padding.  Columns >= ncol are identity columns.
 #pragma once
 #include "tiles.cuh"
 
 namespace gpsat {
 
-// global-memory variant of tile_value (used for tile (0,0) only)
-__device__ __forceinline__ double tile_value_g(const SlotDesc& d, int gr, int gc) {
-  const int n = d.n;
-  if (gc >= n) return (gr == gc && gr > n) ? 1.0 : 0.0;
-  if (gr == n) return d.y[gc];
-  if (gr >= n + 1 + d.m) return 0.0;
-  const double* pr = (gr < n) ? d.X + (size_t)gr * d.D : d.Xs + (size_t)(gr - n - 1) * d.D;
-  const double* pc = d.X + (size_t)gc * d.D;
-  double r2 = 0.0;
-  for (int dd = 0; dd < d.D; ++dd) {
-    double t = pr[dd] * d.inv_ls[dd] - pc[dd] * d.inv_ls[dd];
-    r2 += t * t;
-  }
-  double v = d.var * kunit_dyn(d.kind, r2);
-  if (gr == gc) v += d.noise;
-  return v;
+constexpr int LDD = NB + 4;                 // tile stride: DMMA fragment loads are conflict-free
+constexpr int PB = 32;                      // panel width
+constexpr int LDP = PB + 4;                 // stride of the 32 x 32 side blocks
+constexpr int DIAG_CS_D = NB * LDD;
+constexpr int DIAG_WP_D = 4 * PB * LDP;     // W_pp, row-major, p = 0..3
+constexpr int DIAG_TT_D = 3 * PB * LDP;     // temporaries of the inverse sweep
+constexpr int DIAG_XY_D = NB * GPSAT_DMAX + NB;
+constexpr int DIAG_SMEM_BYTES = (DIAG_CS_D + DIAG_WP_D + DIAG_TT_D + DIAG_XY_D + NB + 2 * PB + 8) * 8;
+static_assert(LDD == LDC, "add_aug_tile writes with stride LDC");
+
+// One 8 x 8 fragment: c += sa * A[8 rows][4*nk4 k] * B[8 rows][same k]^T (both k-contiguous).
+__device__ __forceinline__ void frag_nt(double& c0, double& c1, const double* A, int lda, const double* B,
+                                        int ldb, int nk4, int lane, double sa) {
+  const double* ap = A + (lane >> 2) * lda + (lane & 3);
+  const double* bp = B + (lane >> 2) * ldb + (lane & 3);
+#pragma unroll 4
+  for (int k4 = 0; k4 < nk4; ++k4) dmma884(c0, c1, sa * ap[4 * k4], bp[4 * k4]);
 }
 
 __global__ void __launch_bounds__(GPSAT_THREADS, 1) diag_kernel(const SlotDesc* __restrict__ slots, int i) {
   const SlotDesc& d = slots[blockIdx.x];
   if (d.expert < 0 || i >= d.T) return;
   extern __shared__ double smem[];
-  double* Cs = smem;                 // [NB][LDD]: lower = S_ii -> L_ii, strict upper = W^T
-  double* wdiag = smem + NB * LDD;   // [NB] 1 / L_cc
+  double* Cs = smem;                        // lower: S_ii -> L_ii;  strict upper: U_ii = W_ii^T
+  double* Wp = Cs + DIAG_CS_D;              // [4][32][LDP]  W_pp (lower triangular, with diagonal)
+  double* Tt = Wp + DIAG_WP_D;              // [3][32][LDP]
+  double* xr = Tt + DIAG_TT_D;              // [DMAX][NB] coordinates (tile (0,0) only)
+  double* yr = xr + NB * GPSAT_DMAX;        // [NB]
+  double* wdiag = yr + NB;                  // [NB] 1 / L_cc
+  double* colb = wdiag + NB;                // [2][32] column broadcast buffer of the panel warp
+  double* misc = colb + 2 * PB;             // [0] log-determinant accumulator
   const int tid = threadIdx.x;
+  const int warp = tid >> 5, lane = tid & 31, lr = lane >> 2, lk = lane & 3;
   const int row0 = i * NB;
   const int n = d.n, ld = d.ld;
   int ncol = n - row0;               // real columns in this tile; local index ncol is the y row
@@ -39,84 +55,181 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) diag_kernel(const SlotDesc* 
 
   // ---- load the running Schur complement (tile (0,0): evaluate the kernel directly) ----
   if (i == 0) {
-    for (int idx = tid; idx < NB * NB; idx += GPSAT_THREADS) {
-      int r = idx >> 7, c = idx & (NB - 1);
-      if (c <= r) Cs[r * LDD + c] = tile_value_g(d, r, c);
-    }
+    load_block_coords(d, 0, xr, yr, tid);
+    for (int idx = tid; idx < NB * LDD; idx += GPSAT_THREADS) Cs[idx] = 0.0;
+    __syncthreads();
+    add_aug_tile(d, 0, 0, xr, xr, yr, Cs, tid, true);
   } else {
     const double* src = d.A + (size_t)row0 * ld + row0;
-    for (int idx = tid; idx < NB * NB; idx += GPSAT_THREADS) {
-      int r = idx >> 7, c = idx & (NB - 1);
-      if (c <= r) Cs[r * LDD + c] = src[(size_t)r * ld + c];
-    }
+    const int c = tid & (NB - 1);
+    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) Cs[r * LDD + c] = (c <= r) ? src[(size_t)r * ld + c] : 0.0;
   }
+  if (tid == 0) misc[0] = 0.0;
   __syncthreads();
 
-  // ---- right-looking Cholesky of the first ncol columns (all 128 rows ride along) ----
-  const int tx = tid & 15, ty = tid >> 4;
   bool bad = false;
-  for (int c = 0; c < ncol; ++c) {
-    double piv = Cs[c * LDD + c];
-    if (!(piv > 0.0) || !isfinite(piv)) { bad = true; piv = 1.0; }
-    double dd = sqrt(piv);
-    __syncthreads();                     // everyone has read the pivot
-    for (int r = c + 1 + tid; r < NB; r += GPSAT_THREADS) Cs[r * LDD + c] /= dd;
-    if (tid == 0) Cs[c * LDD + c] = dd;
-    __syncthreads();
-    for (int r = c + 1 + ty; r < NB; r += 16) {
-      double lr = Cs[r * LDD + c];
-      for (int k = c + 1 + tx; k <= r; k += 16) Cs[r * LDD + k] -= lr * Cs[k * LDD + c];
-    }
-    // the next iteration's pivot read is ordered by the __syncthreads at its top-of-loop below
-    __syncthreads();
-  }
-  if (bad && tid == 0) *d.notpd = 1;
-
-  // ---- quad term, identity on the padding, log-determinant ----
-  if (tid == 0 && ncol < NB) *d.quad = -Cs[ncol * LDD + ncol];
-  __syncthreads();
-  for (int p = ncol + tid; p < NB; p += GPSAT_THREADS) Cs[p * LDD + p] = 1.0;
-  __syncthreads();
-  if (tid < 32) {
-    double s = 0.0;
-    for (int c = tid; c < ncol; c += 32) s += log(Cs[c * LDD + c]);
+  for (int p = 0; p < NB / PB; ++p) {
+    const int c0 = p * PB;
+    int jmax = ncol - c0;
+    if (jmax > PB) jmax = PB;
+    if (jmax < 0) jmax = 0;
+    // ---- (a) warp 0: Cholesky of the 32 x 32 diagonal block, lane = row; then its inverse ----
+    if (warp == 0) {
+      double a[PB];
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    if (tid == 0) d.logdet[i] = s;
-  }
-  for (int c = tid; c < NB; c += GPSAT_THREADS) wdiag[c] = 1.0 / Cs[c * LDD + c];
-  __syncthreads();
-
-  // ---- W = L^-1, column c by forward substitution; two threads per column split the dot ----
-  // W[k][c] (k > c) is kept transposed at Cs[c][k] (strict upper triangle).
-  {
-    const int c = tid >> 1, half = tid & 1;
-    for (int r = 1; r < NB; ++r) {
-      double s = 0.0;
-      if (c < r) {
-        // k runs over [c, r-1]; k == c uses W[c][c] = wdiag[c]
-        for (int k = r - 1 - half; k > c; k -= 2) s += Cs[r * LDD + k] * Cs[c * LDD + k];
-        if (((r - 1 - c) & 1) == half) s += Cs[r * LDD + c] * wdiag[c];
+      for (int k = 0; k < PB; ++k) a[k] = Cs[(c0 + lane) * LDD + c0 + k];
+#pragma unroll
+      for (int j = 0; j < PB; ++j) {
+        if (j < jmax) {
+          double piv = __shfl_sync(0xffffffffu, a[j], j);
+          if (!(piv > 0.0) || !isfinite(piv)) { bad = true; piv = 1.0; }
+          const double dg = sqrt(piv);
+          const double inv = 1.0 / dg;
+          const double v = (lane > j) ? a[j] * inv : (lane == j ? dg : 0.0);
+          a[j] = v;
+          double* cb = colb + (j & 1) * PB;
+          cb[lane] = v;
+          if (lane == 0) wdiag[c0 + j] = inv;
+          __syncwarp();
+          // a[k] -= L[lane][j] * L[k][j]; entries with k > lane are never read, so no predicate
+#pragma unroll
+          for (int k = j + 1; k < PB; ++k) a[k] = fma(-v, cb[k], a[k]);
+        } else {
+          if (j == jmax && lane == j && c0 + j == ncol) *d.quad = -a[j];   // Schur complement at the y row
+          a[j] = (lane == j) ? 1.0 : 0.0;
+          if (lane == 0) wdiag[c0 + j] = 1.0;
+        }
       }
-      s += __shfl_xor_sync(0xffffffffu, s, 1);
-      if (c < r && half == 0) Cs[c * LDD + r] = -s * wdiag[r];
+      // log-determinant: lane l holds L_ll
+      {
+        double dsel = 1.0;          // a[lane] through static indices only (a[] must stay in registers)
+#pragma unroll
+        for (int k = 0; k < PB; ++k) if (k == lane) dsel = a[k];
+        double lg = (lane < jmax) ? log(dsel) : 0.0;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, o);
+        if (lane == 0) misc[0] += lg;
+      }
+#pragma unroll
+      for (int k = 0; k < PB; ++k) if (k <= lane) Cs[(c0 + lane) * LDD + c0 + k] = a[k];
+      __syncwarp();
+      // inverse, lane = column c of W_pp: x[r] = W[r][c]
+      {
+        double x[PB], acc[PB];
+#pragma unroll
+        for (int r = 0; r < PB; ++r) { x[r] = 0.0; acc[r] = 0.0; }
+        const double myinv = wdiag[c0 + lane];
+#pragma unroll
+        for (int r = 0; r < PB; ++r) if (r == lane) x[r] = myinv;
+#pragma unroll
+        for (int k = 0; k < PB - 1; ++k) {
+          const double xk = x[k];
+#pragma unroll
+          for (int r = k + 1; r < PB; ++r) acc[r] = fma(Cs[(c0 + r) * LDD + c0 + k], xk, acc[r]);
+          if (k + 1 > lane) x[k + 1] = -acc[k + 1] * wdiag[c0 + k + 1];
+        }
+        double* W = Wp + p * PB * LDP;
+#pragma unroll
+        for (int r = 0; r < PB; ++r) {
+          W[r * LDP + lane] = x[r];                                  // W_pp[r][c], zero above the diagonal
+          if (r > lane) Cs[(c0 + lane) * LDD + c0 + r] = x[r];      // U_pp = W_pp^T, strict upper
+        }
+      }
+    }
+    __syncthreads();
+    const int nbelow = NB - c0 - PB;          // rows below the diagonal block
+    if (nbelow > 0) {
+      // ---- (b) panel: rows below *= W_pp^T; a warp owns whole 8-row blocks (in-place safe) ----
+      const double* W = Wp + p * PB * LDP;
+      for (int rb = warp; rb < nbelow / 8; rb += GPSAT_THREADS / 32) {
+        double* Arow = Cs + (c0 + PB + rb * 8) * LDD + c0;
+        double c[4][2];
+#pragma unroll
+        for (int f = 0; f < 4; ++f) { c[f][0] = 0.0; c[f][1] = 0.0; }
+#pragma unroll
+        for (int k4 = 0; k4 < PB / 4; ++k4) {
+          const double av = Arow[lr * LDD + 4 * k4 + lk];
+#pragma unroll
+          for (int f = 0; f < 4; ++f)
+            if (8 * f + 7 >= 4 * k4)             // W_pp lower triangular: k <= c
+              dmma884(c[f][0], c[f][1], av, W[(8 * f + lr) * LDP + 4 * k4 + lk]);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int f = 0; f < 4; ++f) {
+          const int cc = c0 + 8 * f + 2 * lk;      // identity columns get zeros
+          double2 v = make_double2(cc < ncol ? c[f][0] : 0.0, cc + 1 < ncol ? c[f][1] : 0.0);
+          *reinterpret_cast<double2*>(Arow + lr * LDD + 8 * f + 2 * lk) = v;
+        }
+      }
+      __syncthreads();
+      // ---- (c) trailing block -= panel panel^T, lower 8 x 8 fragments ----
+      const int nf = nbelow / 8;
+      const double* P0 = Cs + (c0 + PB) * LDD + c0;
+      for (int f = warp; f < nf * (nf + 1) / 2; f += GPSAT_THREADS / 32) {
+        int fr = (int)((sqrtf(8.0f * f + 1.0f) - 1.0f) * 0.5f);
+        while (fr * (fr + 1) / 2 > f) --fr;
+        while ((fr + 1) * (fr + 2) / 2 <= f) ++fr;
+        const int fc = f - fr * (fr + 1) / 2;
+        double* Cg = Cs + (c0 + PB + 8 * fr + lr) * LDD + c0 + PB + 8 * fc + 2 * lk;
+        double2 cv = *reinterpret_cast<double2*>(Cg);
+        frag_nt(cv.x, cv.y, P0 + 8 * fr * LDD, LDD, P0 + 8 * fc * LDD, LDD, PB / 4, lane, -1.0);
+        *reinterpret_cast<double2*>(Cg) = cv;
+      }
       __syncthreads();
     }
+  }
+  if (bad && tid == 0) *d.notpd = 1;     // `bad` is only ever set in warp 0 (all lanes agree)
+  if (tid == 0) d.logdet[i] = misc[0];
+
+  // ---- U = L^-T off-diagonal 32-blocks:  U_ji = -(sum_{j<=k<i} U_jk L_ik^T) W_ii^T ----
+  for (int dlt = 1; dlt < NB / PB; ++dlt) {
+    const int nblk = NB / PB - dlt;
+    // T_b = sum_k U_jk L_ik^T
+    for (int f = warp; f < nblk * 16; f += GPSAT_THREADS / 32) {
+      const int b = f >> 4, fa = (f >> 2) & 3, fc = f & 3;
+      const int j0 = b * PB, i0 = (b + dlt) * PB;
+      double c0v = 0.0, c1v = 0.0;
+      // k = j: U_jj = W_jj^T, read transposed from Wp
+      {
+        const double* Wj = Wp + b * PB * LDP;
+        const double* Lb = Cs + (i0 + 8 * fc + lr) * LDD + j0 + lk;
+#pragma unroll
+        for (int k4 = 0; k4 < PB / 4; ++k4)
+          dmma884(c0v, c1v, Wj[(4 * k4 + lk) * LDP + 8 * fa + lr], Lb[4 * k4]);
+      }
+      if (dlt > 1)
+        frag_nt(c0v, c1v, Cs + (j0 + 8 * fa) * LDD + j0 + PB, LDD, Cs + (i0 + 8 * fc) * LDD + j0 + PB, LDD,
+                (dlt - 1) * PB / 4, lane, 1.0);
+      *reinterpret_cast<double2*>(Tt + b * PB * LDP + (8 * fa + lr) * LDP + 8 * fc + 2 * lk) = make_double2(c0v, c1v);
+    }
+    __syncthreads();
+    for (int f = warp; f < nblk * 16; f += GPSAT_THREADS / 32) {
+      const int b = f >> 4, fa = (f >> 2) & 3, fc = f & 3;
+      const int j0 = b * PB, i0 = (b + dlt) * PB;
+      double c0v = 0.0, c1v = 0.0;
+      frag_nt(c0v, c1v, Tt + b * PB * LDP + 8 * fa * LDP, LDP, Wp + (b + dlt) * PB * LDP + 8 * fc * LDP, LDP,
+              PB / 4, lane, -1.0);
+      *reinterpret_cast<double2*>(Cs + (j0 + 8 * fa + lr) * LDD + i0 + 8 * fc + 2 * lk) = make_double2(c0v, c1v);
+    }
+    __syncthreads();
   }
 
   // ---- write L_ii, W_ii (side buffers) and U_ii = W_ii^T (into the slot matrix) ----
   double* Ld = d.Ld + (size_t)i * NB * NB;
   double* Wd = d.Wd + (size_t)i * NB * NB;
   double* Ut = d.A + (size_t)row0 * ld + row0;
-  for (int idx = tid; idx < NB * NB; idx += GPSAT_THREADS) {
-    int r = idx >> 7, c = idx & (NB - 1);
-    double lv, wv, uv;
-    if (c < r) { lv = Cs[r * LDD + c]; wv = Cs[c * LDD + r]; uv = 0.0; }
-    else if (c == r) { lv = Cs[r * LDD + r]; wv = wdiag[r]; uv = wv; }
-    else { lv = 0.0; wv = 0.0; uv = Cs[r * LDD + c]; }
-    Ld[idx] = lv;
-    Wd[idx] = wv;
-    Ut[(size_t)r * ld + c] = uv;
+  {
+    const int c = tid & (NB - 1);
+    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
+      double lv, wv, uv;
+      if (c < r) { lv = Cs[r * LDD + c]; wv = Cs[c * LDD + r]; uv = 0.0; }
+      else if (c == r) { lv = Cs[r * LDD + r]; wv = wdiag[r]; uv = wv; }
+      else { lv = 0.0; wv = 0.0; uv = Cs[r * LDD + c]; }
+      Ld[r * NB + c] = lv;
+      Wd[r * NB + c] = wv;
+      Ut[(size_t)r * ld + c] = uv;
+    }
   }
 }
 

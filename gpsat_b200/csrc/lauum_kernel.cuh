@@ -11,6 +11,76 @@
 
 namespace gpsat {
 
+// Rolled gradient reduction over one tile of Q = alpha alpha^T - Ks^-1 held in shared memory.
+// Same thread -> element mapping as add_aug_tile_t (column in registers, rows broadcast).
+template <int KIND, int DD>
+__device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c, const double* xr, const double* xc,
+                                            const double* ar, const double* ac, const double* Cs, int tid,
+                                            double* part) {
+  const int n = d.n, D = d.D;
+  const int c = tid & (NB - 1);
+  const int gj = g0c + c;
+  ColCoords<DD> cc;
+  cc.load(xc, c, D);
+  const double acv = ac[c];
+  constexpr int ND = DD > 0 ? DD : GPSAT_DMAX;
+  double pd[ND], pk = 0.0, pn = 0.0;
+#pragma unroll
+  for (int dd = 0; dd < ND; ++dd) pd[dd] = 0.0;
+  if (gj < n) {
+#pragma unroll 2
+    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
+      const int gi = g0r + r;
+      if (gi >= n || gj > gi) continue;
+      const double aa = ar[r] * acv;
+      // the tile holds Ks^-1 + alpha alpha^T (column n of U is -alpha)
+      const double q = aa - (Cs[r * LDC + c] - aa);
+      const double wq = (gi == gj) ? q : 2.0 * q;
+      double sd[ND], r2 = 0.0;
+#pragma unroll
+      for (int dd = 0; dd < ND; ++dd) {
+        double t = (DD > 0 || dd < D) ? xr[dd * NB + r] - cc.x[dd] : 0.0;
+        sd[dd] = t * t;
+        r2 += sd[dd];
+      }
+      double ku, gu;
+      kunit_gunit_of_r2<KIND>(r2, ku, gu);
+      const double wg = wq * gu;
+#pragma unroll
+      for (int dd = 0; dd < ND; ++dd) pd[dd] = fma(wg, sd[dd], pd[dd]);
+      pk = fma(wq, ku, pk);
+      if (gi == gj) pn += q;
+    }
+  }
+#pragma unroll
+  for (int dd = 0; dd < GPSAT_DMAX; ++dd) part[dd] = dd < ND ? pd[dd < ND ? dd : 0] : 0.0;
+  part[GPSAT_DMAX] = pk;
+  part[GPSAT_DMAX + 1] = pn;
+}
+
+__device__ __noinline__ void grad_tile(const SlotDesc& d, int g0r, int g0c, const double* xr, const double* xc,
+                                       const double* ar, const double* ac, const double* Cs, int tid, double* part) {
+  const bool d3 = d.D == 3;
+  switch (d.kind) {
+    case GPSAT_MATERN12:
+      if (d3) grad_tile_t<GPSAT_MATERN12, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      else grad_tile_t<GPSAT_MATERN12, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      break;
+    case GPSAT_MATERN32:
+      if (d3) grad_tile_t<GPSAT_MATERN32, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      else grad_tile_t<GPSAT_MATERN32, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      break;
+    case GPSAT_MATERN52:
+      if (d3) grad_tile_t<GPSAT_MATERN52, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      else grad_tile_t<GPSAT_MATERN52, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      break;
+    default:
+      if (d3) grad_tile_t<GPSAT_RBF, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      else grad_tile_t<GPSAT_RBF, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      break;
+  }
+}
+
 __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const SlotDesc* __restrict__ slots) {
   const SlotDesc& d = slots[blockIdx.y];
   if (d.expert < 0) return;
@@ -23,16 +93,15 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const Slot
   const int j = t - i * (i + 1) / 2;
 
   extern __shared__ double smem[];
-  double* stages = smem;
-  double* xr = smem + NSTAGE * STAGE_D;
+  double* Cs = smem;                     // pipeline stages, then the Q tile
+  double* xr = smem + SM_TILE_D;
   double* xc = xr + NB * GPSAT_DMAX;
   double* ar = xc + NB * GPSAT_DMAX;     // alpha of the row block
   double* ac = ar + NB;                  // alpha of the column block
   double* red = ac + NB;                 // [8 warps][8]
   const int tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
-  const int lr = lane >> 2, lk = lane & 3;
-  const int n = d.n, ld = d.ld, D = d.D;
+  const int warp = tid >> 5, lane = tid & 31;
+  const int n = d.n, ld = d.ld;
 
   load_block_coords(d, i * NB, xr, ar, tid);      // ar / ac overwritten with alpha below
   load_block_coords(d, j * NB, xc, ac, tid);
@@ -42,44 +111,18 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const Slot
     ar[r] = (gi < n) ? -d.A[(size_t)gi * ld + n] : 0.0;
     ac[r] = (gj < n) ? -d.A[(size_t)gj * ld + n] : 0.0;
   }
-
-  Acc acc;
-  acc_zero(acc);
-  const int kend = ((n + 1 + KC - 1) / KC) * KC;     // includes column n (the -alpha column)
-  gemm_nt_mainloop(acc, d.A + (size_t)i * NB * ld, d.A + (size_t)j * NB * ld, ld, i * NB, kend, stages, tid);
+  {
+    Acc acc;
+    acc_zero(acc);
+    const int kend = ((n + 1 + KC - 1) / KC) * KC;     // includes column n (the -alpha column)
+    gemm_nt_mainloop(acc, d.A + (size_t)i * NB * ld, d.A + (size_t)j * NB * ld, ld, i * NB, kend, smem, tid);
+    __syncthreads();
+    acc_to_smem(acc, Cs, tid, 1.0);
+  }
   __syncthreads();
 
   double part[GPSAT_DMAX + 2];
-#pragma unroll
-  for (int p = 0; p < GPSAT_DMAX + 2; ++p) part[p] = 0.0;
-#pragma unroll
-  for (int fm = 0; fm < 8; ++fm)
-#pragma unroll
-    for (int fn = 0; fn < 4; ++fn)
-#pragma unroll
-      for (int e = 0; e < 2; ++e) {
-        int r = wm * 64 + fm * 8 + lr, c = wn * 32 + fn * 8 + 2 * lk + e;
-        int gi = i * NB + r, gj = j * NB + c;
-        if (gi >= n || gj >= n || gj > gi) continue;
-        double aa = ar[r] * ac[c];
-        // acc = Ks^-1 + alpha alpha^T (column n of U is -alpha)
-        double q = aa - (acc.c[fm][fn][e] - aa);
-        double w = (gi == gj) ? 1.0 : 2.0;
-        double r2 = 0.0, sd[GPSAT_DMAX];
-#pragma unroll
-        for (int dd = 0; dd < GPSAT_DMAX; ++dd) {
-          double tdiff = (dd < D) ? xr[r * GPSAT_DMAX + dd] - xc[c * GPSAT_DMAX + dd] : 0.0;
-          sd[dd] = tdiff * tdiff;
-          r2 += sd[dd];
-        }
-        double ku, gu;
-        kunit_gunit_dyn(d.kind, r2, ku, gu);
-        double wq = w * q;
-#pragma unroll
-        for (int dd = 0; dd < GPSAT_DMAX; ++dd) part[dd] += wq * gu * sd[dd];
-        part[GPSAT_DMAX] += wq * ku;
-        if (gi == gj) part[GPSAT_DMAX + 1] += q;
-      }
+  grad_tile(d, i * NB, j * NB, xr, xc, ar, ac, Cs, tid, part);
   // deterministic block reduction: warp shuffle tree, then warp 0 adds the 8 warp sums in order
 #pragma unroll
   for (int p = 0; p < GPSAT_DMAX + 2; ++p) {

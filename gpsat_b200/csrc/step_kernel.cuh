@@ -2,41 +2,44 @@
 //   blockIdx.y = slot, blockIdx.x = tile within the step:
 //     [0, TR-1-i)            potrf tile (r, i), r = i + 1 + x
 //     [TR-1-i, TR-1-i + i)   trtri tile (j, i), j = x - (TR-1-i)      (only when do_inv)
+// Phases of one CTA (256 threads, one 128 x 128 output tile):
+//   1. main loop   acc = sum_k A_rk B_ik^T           2 x 4 warp grid, 3-stage cp.async pipeline
+//   2. C           = K_ri - acc (potrf, covariance evaluated in a rolled per-column loop) | acc
+//   3. out         = C W_ii^T, W_ii lower triangular: strip-mapped DMMA over k <= c only
+//   4. (potrf)     S_rr -= out out^T, lower triangle only, strip-mapped; coalesced update
 #pragma once
 #include "tiles.cuh"
 
 namespace gpsat {
 
-// out = Cs(128 x 128, smem, stride LDC) * W^T, W row-major 128 x 128 in global memory, streamed
-// through two B-only stages.
-__device__ __forceinline__ void gemm_tile_times_Wt(Acc& acc, const double* Cs, const double* Wg,
-                                                   double* wst, int tid) {
-  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
+// acc[strip rows][c] = sum_{k <= c} Cs[row][k] * W[c][k];  W (row-major 128 x 128, global) is
+// streamed through NWSTAGE B-only stages.  Each warp reads only its own strip of Cs.
+__device__ __forceinline__ void wmult_strip(AccStrip& acc, const double* Cs, const double* Wg, double* wst,
+                                            int tid) {
+  const int warp = tid >> 5, lane = tid & 31, lr = lane >> 2, lk = lane & 3;
+  const int strip = strip_of_warp(warp);
   constexpr int NSL = NB / KC;
-  load_slab(wst, Wg, NB, tid);
-  cp_async_commit();
-  for (int s = 0; s < NSL; ++s) {
-    if (s + 1 < NSL) load_slab(wst + ((s + 1) & 1) * NB * LDS_S, Wg + (s + 1) * KC, NB, tid);
+#pragma unroll
+  for (int s = 0; s < NWSTAGE - 1; ++s) {
+    load_slab(wst + s * NB * LDS_S, Wg + s * KC, NB, tid);
     cp_async_commit();
-    cp_async_wait<1>();
+  }
+  const double* ap = Cs + (16 * strip + lr) * LDC + lk;
+#pragma unroll 1
+  for (int s = 0; s < NSL; ++s) {
+    cp_async_wait<NWSTAGE - 2>();
     __syncthreads();
-    mma_slab(acc, Cs + s * KC, LDC, wst + (s & 1) * NB * LDS_S, LDS_S, KC / 4, wm, wn, lane);
-    __syncthreads();
+    const int nx = s + NWSTAGE - 1;
+    if (nx < NSL) load_slab(wst + (nx % NWSTAGE) * NB * LDS_S, Wg + nx * KC, NB, tid);
+    cp_async_commit();
+    const double* bp = wst + (s % NWSTAGE) * NB * LDS_S + lr * LDS_S + lk;
+#pragma unroll
+    for (int kk = 0; kk < KC / 4; ++kk) {
+      const int kb = s * (KC / 4) + kk;
+      mma_strip_k4(acc, ap + kb * 4, LDC, bp + kk * 4, LDS_S, kb >> 1, 16);
+    }
   }
   cp_async_wait<0>();
-}
-
-__device__ __forceinline__ void acc_to_smem(const Acc& acc, double* Cs, int tid, double sign) {
-  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
-  const int lr = lane >> 2, lk = lane & 3;
-#pragma unroll
-  for (int fm = 0; fm < 8; ++fm)
-#pragma unroll
-    for (int fn = 0; fn < 4; ++fn) {
-      int r = wm * 64 + fm * 8 + lr, c = wn * 32 + fn * 8 + 2 * lk;
-      double2 v = make_double2(sign * acc.c[fm][fn][0], sign * acc.c[fm][fn][1]);
-      *reinterpret_cast<double2*>(Cs + r * LDC + c) = v;
-    }
 }
 
 __global__ void __launch_bounds__(GPSAT_THREADS, 1)
@@ -58,8 +61,9 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
   double* yr = xc + NB * GPSAT_DMAX;
   double* yc = yr + NB;
   const int tid = threadIdx.x;
-  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
+  const int warp = tid >> 5, lane = tid & 31;
   const int lr = lane >> 2, lk = lane & 3;
+  const int strip = strip_of_warp(warp);
   const int ld = d.ld;
   const double* Wg = d.Wd + (size_t)i * NB * NB;
 
@@ -68,73 +72,85 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
     load_block_coords(d, i * NB, xc, yc, tid);
   }
 
-  Acc acc;
-  acc_zero(acc);
-  const double* Ag = d.A + (size_t)rowblk * NB * ld;
-  const double* Bg = d.A + (size_t)i * NB * ld;
-  const int kbeg = is_pot ? 0 : rowblk * NB;
-  gemm_nt_mainloop(acc, Ag, Bg, ld, kbeg, i * NB, smem, tid);
-  __syncthreads();   // coords visible; stages free
-
-  // ---- C = K_ri - acc (potrf) or acc (trtri), to shared memory ----
-  if (is_pot) {
-#pragma unroll
-    for (int fm = 0; fm < 8; ++fm)
-#pragma unroll
-      for (int fn = 0; fn < 4; ++fn) {
-        int r = wm * 64 + fm * 8 + lr, c = wn * 32 + fn * 8 + 2 * lk;
-        int gr = rowblk * NB + r, gc = i * NB + c;
-        double v0 = tile_value(d, gr, gc, xr + r * GPSAT_DMAX, xc + c * GPSAT_DMAX, yc[c]);
-        double v1 = tile_value(d, gr, gc + 1, xr + r * GPSAT_DMAX, xc + (c + 1) * GPSAT_DMAX, yc[c + 1]);
-        *reinterpret_cast<double2*>(Cs + r * LDC + c) =
-            make_double2(v0 - acc.c[fm][fn][0], v1 - acc.c[fm][fn][1]);
-      }
-  } else {
-    acc_to_smem(acc, Cs, tid, 1.0);
+  // ---- 1. main loop ----
+  {
+    Acc acc;
+    acc_zero(acc);
+    const double* Ag = d.A + (size_t)rowblk * NB * ld;
+    const double* Bg = d.A + (size_t)i * NB * ld;
+    const int kbeg = is_pot ? 0 : rowblk * NB;
+    gemm_nt_mainloop(acc, Ag, Bg, ld, kbeg, i * NB, smem, tid);
+    __syncthreads();   // coords visible; stages free
+    // ---- 2. C to shared memory ----
+    acc_to_smem(acc, Cs, tid, is_pot ? -1.0 : 1.0);
   }
   __syncthreads();
+  if (is_pot) {
+    add_aug_tile(d, rowblk * NB, i * NB, xr, xc, yc, Cs, tid, false);
+    __syncthreads();
+  }
 
-  // ---- out = C * W_ii^T ----
-  acc_zero(acc);
-  gemm_tile_times_Wt(acc, Cs, Wg, wst, tid);
+  // ---- 3. out = C * W_ii^T ----
+  AccStrip out;
+  acc_zero(out);
+  wmult_strip(out, Cs, Wg, wst, tid);
   const double sign = is_pot ? 1.0 : -1.0;
   {
-    double* Og = d.A + (size_t)rowblk * NB * ld + (size_t)i * NB;
+    double* Og = d.A + ((size_t)rowblk * NB + 16 * strip + lr) * ld + (size_t)i * NB + 2 * lk;
 #pragma unroll
-    for (int fm = 0; fm < 8; ++fm)
+    for (int rf = 0; rf < 2; ++rf)
 #pragma unroll
-      for (int fn = 0; fn < 4; ++fn) {
-        int r = wm * 64 + fm * 8 + lr, c = wn * 32 + fn * 8 + 2 * lk;
-        *reinterpret_cast<double2*>(Og + (size_t)r * ld + c) =
-            make_double2(sign * acc.c[fm][fn][0], sign * acc.c[fm][fn][1]);
-      }
+      for (int cf = 0; cf < 16; ++cf)
+        *reinterpret_cast<double2*>(Og + (size_t)rf * 8 * ld + cf * 8) =
+            make_double2(sign * out.c[rf][cf][0], sign * out.c[rf][cf][1]);
   }
   if (!is_pot || rowblk >= d.T) return;
 
-  // ---- S_rr -= L_ri L_ri^T  (running Schur complement of the diagonal tile of block row r) ----
-  acc_to_smem(acc, Cs, tid, 1.0);     // all warps passed the last barrier of gemm_tile_times_Wt
+  // ---- 4. S_rr -= L_ri L_ri^T  (running Schur complement of the diagonal tile of block row r) ----
+  // every warp read only its own strip of Cs in phase 3, so it may overwrite that strip now
+  {
+    double* Cw = Cs + (16 * strip + lr) * LDC + 2 * lk;
+#pragma unroll
+    for (int rf = 0; rf < 2; ++rf)
+#pragma unroll
+      for (int cf = 0; cf < 16; ++cf)
+        *reinterpret_cast<double2*>(Cw + rf * 8 * LDC + cf * 8) = make_double2(out.c[rf][cf][0], out.c[rf][cf][1]);
+  }
   __syncthreads();
-  acc_zero(acc);
-  mma_slab(acc, Cs, LDC, Cs, LDC, NB / 4, wm, wn, lane);
-  double* Sg = d.A + (size_t)rowblk * NB * ld + (size_t)rowblk * NB;
+  AccStrip sy;
+  acc_zero(sy);
+  {
+    const double* ap = Cs + (16 * strip + lr) * LDC + lk;
+    const double* bp = Cs + lr * LDC + lk;
+    const int cf_hi = 2 * strip + 2;
+#pragma unroll 2
+    for (int kb = 0; kb < NB / 4; ++kb) mma_strip_k4(sy, ap + kb * 4, LDC, bp + kb * 4, LDC, 0, cf_hi);
+  }
+  __syncthreads();   // all warps done reading L_ri from Cs
+  {
+    double* Cw = Cs + (16 * strip + lr) * LDC + 2 * lk;
+    const int cf_hi = 2 * strip + 2;
 #pragma unroll
-  for (int fm = 0; fm < 8; ++fm)
+    for (int rf = 0; rf < 2; ++rf)
 #pragma unroll
-    for (int fn = 0; fn < 4; ++fn) {
-      int r = wm * 64 + fm * 8 + lr, c = wn * 32 + fn * 8 + 2 * lk;
-      if (c > r + 1 && (c >> 3) > (r >> 3)) continue;    // strictly upper fragment: never read
-      double2 base;
-      if (i == 0) {
-        int gr = rowblk * NB + r, gc = rowblk * NB + c;
-        base.x = tile_value(d, gr, gc, xr + r * GPSAT_DMAX, xr + c * GPSAT_DMAX, yr[c]);
-        base.y = tile_value(d, gr, gc + 1, xr + r * GPSAT_DMAX, xr + (c + 1) * GPSAT_DMAX, yr[c + 1]);
-      } else {
-        base = *reinterpret_cast<const double2*>(Sg + (size_t)r * ld + c);
-      }
-      base.x -= acc.c[fm][fn][0];
-      base.y -= acc.c[fm][fn][1];
-      *reinterpret_cast<double2*>(Sg + (size_t)r * ld + c) = base;
+      for (int cf = 0; cf < 16; ++cf)
+        if (cf < cf_hi)
+          *reinterpret_cast<double2*>(Cw + rf * 8 * LDC + cf * 8) = make_double2(-sy.c[rf][cf][0], -sy.c[rf][cf][1]);
+  }
+  __syncthreads();
+  // the two loops below touch element (r, c) from the same thread: no barrier between them
+  if (i == 0) add_aug_tile(d, rowblk * NB, rowblk * NB, xr, xr, yr, Cs, tid, true);
+  {
+    double* Sg = d.A + (size_t)rowblk * NB * ld + (size_t)rowblk * NB;
+    const int c = tid & (NB - 1);
+    if (i == 0) {
+      for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
+        if (c <= r) Sg[(size_t)r * ld + c] = Cs[r * LDC + c];
+    } else {
+      for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
+        if (c <= r) Sg[(size_t)r * ld + c] += Cs[r * LDC + c];
     }
+  }
 }
 
 }  // namespace gpsat

@@ -24,15 +24,16 @@ constexpr int LDS_S = KC + 4;          // padded smem row stride of a slab (conf
 constexpr int LDC = NB + 4;            // padded smem row stride of a full tile
 constexpr int STAGE_D = 2 * NB * LDS_S;     // doubles per stage (A slab + B slab)
 constexpr int NSTAGE = 3;
-constexpr int SM_TILE_D = NB * LDC;         // 16896 doubles
-constexpr int SM_WST_D = 2 * NB * LDS_S;    // two B-only stages for streaming W_ii
+constexpr int SM_TILE_D = NB * LDC;         // 16896 doubles (>= NSTAGE * STAGE_D: the tile aliases the stages)
+constexpr int NWSTAGE = 3;                  // B-only stages for streaming W_ii
+constexpr int SM_WST_D = NWSTAGE * NB * LDS_S;
 constexpr int SM_XY_D = 2 * NB * GPSAT_DMAX + 2 * NB;
 constexpr int STEP_SMEM_BYTES = (SM_TILE_D + SM_WST_D + SM_XY_D) * 8;
-constexpr int LAUUM_SMEM_BYTES = (NSTAGE * STAGE_D + SM_XY_D + 64 * 8) * 8;
-constexpr int LDD = NB + 1;                 // diag kernel smem stride
-constexpr int DIAG_SMEM_BYTES = (NB * LDD + NB) * 8;
+constexpr int LAUUM_SMEM_BYTES = (SM_TILE_D + SM_XY_D + 64 * 8) * 8;
+static_assert(SM_TILE_D >= NSTAGE * STAGE_D, "tile must cover the pipeline stages it aliases");
 
-struct Acc { double c[8][4][2]; };
+struct Acc { double c[8][4][2]; };        // 2 x 4 warp grid: warp tile 64 x 32
+struct AccStrip { double c[2][16][2]; };  // strip mapping: warp tile 16 x 128
 
 __device__ __forceinline__ void acc_zero(Acc& a) {
 #pragma unroll
@@ -40,6 +41,16 @@ __device__ __forceinline__ void acc_zero(Acc& a) {
 #pragma unroll
     for (int j = 0; j < 4; ++j) { a.c[i][j][0] = 0.0; a.c[i][j][1] = 0.0; }
 }
+__device__ __forceinline__ void acc_zero(AccStrip& a) {
+#pragma unroll
+  for (int i = 0; i < 2; ++i)
+#pragma unroll
+    for (int j = 0; j < 16; ++j) { a.c[i][j][0] = 0.0; a.c[i][j][1] = 0.0; }
+}
+
+// Row strip of warp w in the strip mapping.  Warps w and w + 4 share a scheduler (warp id mod 4);
+// pairing strips s and 7 - s balances triangular work between the four schedulers.
+__device__ __forceinline__ int strip_of_warp(int warp) { return warp < 4 ? warp : 11 - warp; }
 
 // acc += A[wm*64 .. +64][k] * B[wn*32 .. +32][k]^T over nk4*4 values of k.  As/Bs point at k = 0
 // of the slab; both are k-contiguous with row strides lda / ldb (strides = 4 mod 16 doubles).
@@ -59,6 +70,22 @@ __device__ __forceinline__ void mma_slab(Acc& acc, const double* As, int lda, co
     for (int fm = 0; fm < 8; ++fm)
 #pragma unroll
       for (int fn = 0; fn < 4; ++fn) dmma884(acc.c[fm][fn][0], acc.c[fm][fn][1], a[fm], b[fn]);
+  }
+}
+
+// Strip mapping, one block of 4 k values: acc[rf][cf] += A[strip rows][k] * B[8cf .. 8cf+8][k]^T for
+// the column fragments cf_lo <= cf < cf_hi (warp-uniform bounds).  ap / bp point at this lane's
+// element of the k block: ap = A + (16*strip + lr) * lda + k + lk,  bp = B + lr * ldb + k + lk.
+__device__ __forceinline__ void mma_strip_k4(AccStrip& acc, const double* ap, int lda, const double* bp, int ldb,
+                                             int cf_lo, int cf_hi) {
+  const double a0 = ap[0], a1 = ap[8 * lda];
+#pragma unroll
+  for (int cf = 0; cf < 16; ++cf) {
+    if (cf >= cf_lo && cf < cf_hi) {
+      const double b = bp[cf * 8 * ldb];
+      dmma884(acc.c[0][cf][0], acc.c[0][cf][1], a0, b);
+      dmma884(acc.c[1][cf][0], acc.c[1][cf][1], a1, b);
+    }
   }
 }
 
@@ -104,8 +131,10 @@ __device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, con
   __syncthreads();
 }
 
-// Row / column coordinates of one 128-block, scaled by 1/lengthscale, into smem [128][DMAX];
-// yv[128] gets the observation values of the block (0 outside [0, n)).
+// Row / column coordinates of one 128-block, scaled by 1/lengthscale, into smem as
+// xs[dim][row] (structure of arrays: a warp reading 32 consecutive rows of one dimension is
+// conflict-free, a warp reading one row is a broadcast); yv[128] gets the observation values of
+// the block (0 outside [0, n)).
 __device__ __forceinline__ void load_block_coords(const SlotDesc& d, int g0, double* xs, double* yv, int tid) {
   const int D = d.D, n = d.n, m = d.m;
   for (int idx = tid; idx < NB * D; idx += GPSAT_THREADS) {
@@ -114,7 +143,7 @@ __device__ __forceinline__ void load_block_coords(const SlotDesc& d, int g0, dou
     double v = 0.0;
     if (g < n) v = d.X[(size_t)g * D + dd] * d.inv_ls[dd];
     else if (g > n && g < n + 1 + m) v = d.Xs[(size_t)(g - n - 1) * D + dd] * d.inv_ls[dd];
-    xs[row * GPSAT_DMAX + dd] = v;
+    xs[dd * NB + row] = v;
   }
   for (int row = tid; row < NB; row += GPSAT_THREADS) {
     int g = g0 + row;
@@ -122,18 +151,90 @@ __device__ __forceinline__ void load_block_coords(const SlotDesc& d, int g0, dou
   }
 }
 
-// Entry (gr, gc) of the augmented matrix  [[K + s2 I], [y^T], [Kxs^T], [0 .. I]]  from smem coords.
-__device__ __forceinline__ double tile_value(const SlotDesc& d, int gr, int gc, const double* xr,
-                                             const double* xc, double yc) {
+// ---- compact (rolled) evaluation of covariance tiles ------------------------------------------
+// Thread t owns column c = t & 127 and the rows r = (t >> 7), (t >> 7) + 2, ...: the column
+// coordinates stay in registers, the row coordinates are warp-wide broadcasts, the tile is
+// touched with unit stride.  DD > 0 fixes the input dimension at compile time (DD = 3: x, y, t).
+template <int DD>
+struct ColCoords {
+  double x[DD > 0 ? DD : GPSAT_DMAX];
+  __device__ __forceinline__ void load(const double* xc, int c, int D) {
+#pragma unroll
+    for (int dd = 0; dd < (DD > 0 ? DD : GPSAT_DMAX); ++dd) x[dd] = (DD > 0 || dd < D) ? xc[dd * NB + c] : 0.0;
+  }
+  __device__ __forceinline__ double r2(const double* xr, int r, int D) const {
+    double s = 0.0;
+#pragma unroll
+    for (int dd = 0; dd < (DD > 0 ? DD : GPSAT_DMAX); ++dd)
+      if (DD > 0 || dd < D) { double t = xr[dd * NB + r] - x[dd]; s = fma(t, t, s); }
+    return s;
+  }
+};
+
+// Entry (gr, gc) of the augmented matrix  [[K + s2 I], [y^T], [Kxs^T], [0 .. I]].
+template <int KIND, int DD>
+__device__ __forceinline__ double aug_value(const SlotDesc& d, int gr, int gc, int r, const double* xr,
+                                            const ColCoords<DD>& cc, double yc) {
   const int n = d.n;
   if (gc >= n) return (gr == gc && gr > n) ? 1.0 : 0.0;
   if (gr == n) return yc;
   if (gr >= n + 1 + d.m) return 0.0;
-  double r2 = 0.0;
-  for (int dd = 0; dd < d.D; ++dd) { double t = xr[dd] - xc[dd]; r2 += t * t; }
-  double v = d.var * kunit_dyn(d.kind, r2);
+  double v = d.var * kunit_of_r2<KIND>(cc.r2(xr, r, d.D));
   if (gr == gc) v += d.noise;
   return v;
+}
+
+// Cs[r][c] += aug(g0r + r, g0c + c) for the whole tile (lower_only: c <= r only).
+template <int KIND, int DD>
+__device__ __forceinline__ void add_aug_tile_t(const SlotDesc& d, int g0r, int g0c, const double* xr,
+                                               const double* xc, const double* yc, double* Cs, int tid,
+                                               bool lower_only) {
+  const int c = tid & (NB - 1);
+  ColCoords<DD> cc;
+  cc.load(xc, c, d.D);
+  const double ycv = yc[c];
+#pragma unroll 4
+  for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
+    if (lower_only && c > r) continue;
+    Cs[r * LDC + c] += aug_value<KIND, DD>(d, g0r + r, g0c + c, r, xr, cc, ycv);
+  }
+}
+
+__device__ __noinline__ void add_aug_tile(const SlotDesc& d, int g0r, int g0c, const double* xr, const double* xc,
+                                          const double* yc, double* Cs, int tid, bool lower_only) {
+  const bool d3 = d.D == 3;
+  switch (d.kind) {
+    case GPSAT_MATERN12:
+      if (d3) add_aug_tile_t<GPSAT_MATERN12, 3>(d, g0r, g0c, xr, xc, yc, Cs, tid, lower_only);
+      else add_aug_tile_t<GPSAT_MATERN12, 0>(d, g0r, g0c, xr, xc, yc, Cs, tid, lower_only);
+      break;
+    case GPSAT_MATERN32:
+      if (d3) add_aug_tile_t<GPSAT_MATERN32, 3>(d, g0r, g0c, xr, xc, yc, Cs, tid, lower_only);
+      else add_aug_tile_t<GPSAT_MATERN32, 0>(d, g0r, g0c, xr, xc, yc, Cs, tid, lower_only);
+      break;
+    case GPSAT_MATERN52:
+      if (d3) add_aug_tile_t<GPSAT_MATERN52, 3>(d, g0r, g0c, xr, xc, yc, Cs, tid, lower_only);
+      else add_aug_tile_t<GPSAT_MATERN52, 0>(d, g0r, g0c, xr, xc, yc, Cs, tid, lower_only);
+      break;
+    default:
+      if (d3) add_aug_tile_t<GPSAT_RBF, 3>(d, g0r, g0c, xr, xc, yc, Cs, tid, lower_only);
+      else add_aug_tile_t<GPSAT_RBF, 0>(d, g0r, g0c, xr, xc, yc, Cs, tid, lower_only);
+      break;
+  }
+}
+
+// Accumulators to a smem tile [128][LDC] (2 x 4 warp grid layout).
+__device__ __forceinline__ void acc_to_smem(const Acc& acc, double* Cs, int tid, double sign) {
+  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
+  const int lr = lane >> 2, lk = lane & 3;
+#pragma unroll
+  for (int fm = 0; fm < 8; ++fm)
+#pragma unroll
+    for (int fn = 0; fn < 4; ++fn) {
+      int r = wm * 64 + fm * 8 + lr, c = wn * 32 + fn * 8 + 2 * lk;
+      double2 v = make_double2(sign * acc.c[fm][fn][0], sign * acc.c[fm][fn][1]);
+      *reinterpret_cast<double2*>(Cs + r * LDC + c) = v;
+    }
 }
 
 }  // namespace gpsat
