@@ -60,9 +60,17 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) diag_kernel(const SlotDesc* 
     __syncthreads();
     add_aug_tile(d, 0, 0, xr, xr, yr, Cs, tid, true);
   } else {
+    // whole tile through cp.async (all requests in flight at once), then clear the strict upper part
     const double* src = d.A + (size_t)row0 * ld + row0;
+    for (int id = tid; id < NB * NB / 2; id += GPSAT_THREADS) {
+      const int r = id >> 6, ch = id & 63;
+      cp_async16(Cs + r * LDD + ch * 2, src + (size_t)r * ld + ch * 2);
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+    __syncthreads();
     const int c = tid & (NB - 1);
-    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) Cs[r * LDD + c] = (c <= r) ? src[(size_t)r * ld + c] : 0.0;
+    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) if (c > r) Cs[r * LDD + c] = 0.0;
   }
   if (tid == 0) misc[0] = 0.0;
   __syncthreads();
@@ -83,8 +91,12 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) diag_kernel(const SlotDesc* 
         if (j < jmax) {
           double piv = __shfl_sync(0xffffffffu, a[j], j);
           if (!(piv > 0.0) || !isfinite(piv)) { bad = true; piv = 1.0; }
-          const double dg = sqrt(piv);
-          const double inv = 1.0 / dg;
+          // 1/sqrt first (one MUFU + Newton), then L_jj = piv * inv with one correction step:
+          // shorter dependent chain than sqrt followed by a division
+          double inv = rsqrt(piv);
+          double dg = piv * inv;
+          dg = fma(fma(-dg, dg, piv), 0.5 * inv, dg);
+          inv = fma(fma(-dg, inv, 1.0), inv, inv);
           const double v = (lane > j) ? a[j] * inv : (lane == j ? dg : 0.0);
           a[j] = v;
           double* cb = colb + (j & 1) * PB;

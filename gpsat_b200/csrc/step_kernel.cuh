@@ -147,8 +147,11 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
       for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
         if (c <= r) Sg[(size_t)r * ld + c] = Cs[r * LDC + c];
     } else {
+      // fire-and-forget reduction at L2 (RED.ADD.F64): no load latency on the CTA's critical path.
+      // Only this CTA touches S_rr during step i, so the result does not depend on timing.
+#pragma unroll 8
       for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
-        if (c <= r) Sg[(size_t)r * ld + c] += Cs[r * LDC + c];
+        if (c <= r) atomicAdd(Sg + (size_t)r * ld + c, Cs[r * LDC + c]);
     }
   }
 }
