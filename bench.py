@@ -302,8 +302,9 @@ def run_ours(args):
                            "n_obs": [spec.n_lo, spec.n_hi], "n_pred": [spec.m_lo, spec.m_hi], "optimise": True,
                            "parallelism": f"experts sharded x{world}, no collective on the hot path",
                            "l2": "256 MB flush written between steps; per-step working set "
-                                 f"{eng.stats()['slots']} slot matrices >> 126 MB L2",
-                           "mean_evals_per_expert": float(nev.mean()),
+                                 f"{int(collect['fit'][-1]['slots'])} slot matrices >> 126 MB L2",
+                           "mean_evals_per_expert": float(nev.mean()), "max_evals_per_expert": int(nev.max()),
+                           "ticks_per_fit": int(collect["fit"][-1]["ticks"]), "slots": int(collect["fit"][-1]["slots"]),
                            "status_counts": {"ok": int(st[0]), "not_pd": int(st[1]), "linesearch": int(st[2]), "maxiter": int(st[3])}},
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clk}

@@ -181,7 +181,7 @@ static int choose_slots(Engine& g, int64_t E, int Tmax, int TRmax, int max_slots
   cudaMemGetInfo(&free_b, &total_b);
   size_t per = (size_t)TRmax * NB * Tmax * NB * 8 + (size_t)2 * Tmax * NB * NB * 8 + (1 << 16);
   size_t avail = (size_t)((free_b + g.bA.cap + g.bside.cap) * 0.80);
-  int64_t S = max_slots > 0 ? max_slots : 296;
+  int64_t S = max_slots > 0 ? max_slots : 592;      // 4 x 148 SMs: amortises the per-step launches
   S = std::min<int64_t>(S, E);
   S = std::min<int64_t>(S, (int64_t)(avail / per));
   return (int)std::max<int64_t>(S, 1);

@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const Slot
     Acc acc;
     acc_zero(acc);
     const int kend = ((n + 1 + KC - 1) / KC) * KC;     // includes column n (the -alpha column)
-    gemm_nt_mainloop(acc, d.A + (size_t)i * NB * ld, d.A + (size_t)j * NB * ld, ld, i * NB, kend, smem, tid);
+    gemm_nt_mainloop(acc, d.A + (size_t)i * NB * ld, d.A + (size_t)j * NB * ld, ld, i * NB, kend, smem, tid, true);
     __syncthreads();
     acc_to_smem(acc, Cs, tid, 1.0);
   }

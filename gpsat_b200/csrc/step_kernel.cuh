@@ -79,7 +79,7 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
     const double* Ag = d.A + (size_t)rowblk * NB * ld;
     const double* Bg = d.A + (size_t)i * NB * ld;
     const int kbeg = is_pot ? 0 : rowblk * NB;
-    gemm_nt_mainloop(acc, Ag, Bg, ld, kbeg, i * NB, smem, tid);
+    gemm_nt_mainloop(acc, Ag, Bg, ld, kbeg, i * NB, smem, tid, !is_pot);   // trtri: U_jj is upper triangular
     __syncthreads();   // coords visible; stages free
     // ---- 2. C to shared memory ----
     acc_to_smem(acc, Cs, tid, is_pot ? -1.0 : 1.0);

@@ -73,6 +73,32 @@ __device__ __forceinline__ void mma_slab(Acc& acc, const double* As, int lda, co
   }
 }
 
+// Same as mma_slab for a slab of an upper-triangular A block (A[a][k] = 0 for k < a, a and k
+// local to the 128-block): fragments whose rows all lie below the slab's k range are skipped.
+// kl0 = local k of the slab's first column.
+__device__ __forceinline__ void mma_slab_tri(Acc& acc, const double* As, int lda, const double* Bs, int ldb,
+                                             int nk4, int wm, int wn, int lane, int kl0) {
+  const int lr = lane >> 2, lk = lane & 3;
+  const double* ap = As + (wm * 64 + lr) * lda + lk;
+  const double* bp = Bs + (wn * 32 + lr) * ldb + lk;
+#pragma unroll
+  for (int k4 = 0; k4 < nk4; ++k4) {
+    const int klast = kl0 + 4 * k4 + 3;
+    if (klast < wm * 64) continue;
+    double b[4];
+#pragma unroll
+    for (int f = 0; f < 4; ++f) b[f] = bp[f * 8 * ldb + k4 * 4];
+#pragma unroll
+    for (int fm = 0; fm < 8; ++fm) {
+      if (klast >= wm * 64 + fm * 8) {
+        const double a = ap[fm * 8 * lda + k4 * 4];
+#pragma unroll
+        for (int fn = 0; fn < 4; ++fn) dmma884(acc.c[fm][fn][0], acc.c[fm][fn][1], a, b[fn]);
+      }
+    }
+  }
+}
+
 // Strip mapping, one block of 4 k values: acc[rf][cf] += A[strip rows][k] * B[8cf .. 8cf+8][k]^T for
 // the column fragments cf_lo <= cf < cf_hi (warp-uniform bounds).  ap / bp point at this lane's
 // element of the k block: ap = A + (16*strip + lr) * lda + k + lk,  bp = B + lr * ldb + k + lk.
@@ -100,8 +126,10 @@ __device__ __forceinline__ void load_slab(double* dst, const double* src, int ld
 }
 
 // acc += sum_{k in [kbeg, kend)} Ag[m][k] * Bg[n][k]   (kbeg, kend multiples of KC)
+// tri_first: the first 128-block of A (k in [kbeg, kbeg + 128)) is upper triangular.
 __device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, const double* Bg, int ldg,
-                                                 int kbeg, int kend, double* stages, int tid) {
+                                                 int kbeg, int kend, double* stages, int tid,
+                                                 bool tri_first = false) {
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
   const int nslab = (kend - kbeg) / KC;
   if (nslab <= 0) return;
@@ -125,7 +153,8 @@ __device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, con
     }
     cp_async_commit();
     const double* st = stages + (s % NSTAGE) * STAGE_D;
-    mma_slab(acc, st, LDS_S, st + NB * LDS_S, LDS_S, KC / 4, wm, wn, lane);
+    if (tri_first && s < NB / KC) mma_slab_tri(acc, st, LDS_S, st + NB * LDS_S, LDS_S, KC / 4, wm, wn, lane, s * KC);
+    else mma_slab(acc, st, LDS_S, st + NB * LDS_S, LDS_S, KC / 4, wm, wn, lane);
   }
   cp_async_wait<0>();
   __syncthreads();

@@ -254,6 +254,9 @@ class Engine:
                                                _ptr(lml), _ptr(status)))
         return {"f*": fm, "f*_var": fv, "y_var": yv, "lml": lml, "status": status}
 
+    def predict_full_cov(self, batch: RaggedBatch, theta):
+        raise NotImplementedError("full_cov=True is not implemented in the engine yet (DESIGN.md section 8)")
+
     def factor_debug(self, kernel: str, X, y, theta, want_U: bool = True):
         X = _f64(X)
         X = X.reshape(len(X), -1)

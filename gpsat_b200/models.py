@@ -313,7 +313,10 @@ class B200GPRModel(BaseGPRModel):
         "f*_cov" and "y_cov".  Values are in scaled-observation units, as in the reference."""
         Xs = self._prep_pred_coords(coords, apply_scale)
         b = self._batch(Xs)
-        out = self.engine.predict(b, self._theta[None, :], full_cov=bool(full_cov))
+        if full_cov:
+            out = self.engine.predict_full_cov(b, self._theta[None, :])
+        else:
+            out = self.engine.predict(b, self._theta[None, :])
         if int(out["status"][0]) != _lib.STATUS_OK:
             raise FloatingPointError("K + likelihood_variance * I is not positive definite at the current parameters")
         res = {"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"]}

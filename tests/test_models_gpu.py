@@ -1,0 +1,140 @@
+"""The plugin surface on a B200, checked like the reference checks GPflowGPRModel
+(/root/reference/tests/test_localexperts.py:204-227) plus the batched entry point and priors."""
+import os
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from oracle import gpr
+
+pytestmark = pytest.mark.gpu
+
+
+def test_b200_gpr_reference_kat(built, golden_dir):
+    """test_gpflow_gpr with B200GPRModel in place of GPflowGPRModel; tolerance 1e-6 as there."""
+    from gpsat_b200.models import B200GPRModel
+    g = np.load(os.path.join(golden_dir, "kat_localexperts.npz"))
+    eps, tol = float(g["eps"]), 1e-6
+    df = pd.DataFrame({"x": g["x_train"][:, 0], "y": g["y_train"][:, 0]})
+    model = B200GPRModel(data=df, obs_col="y", coords_col="x", obs_mean=None)
+    model.set_parameters(likelihood_variance=eps ** 2)
+    model.set_parameter_constraints({"lengthscales": {"low": 1e-10, "high": 5.0}})
+    result = model.optimise_parameters(fixed_params=["likelihood_variance", "kernel_variance"])
+    out = model.predict(coords=g["x_test"])
+    params = model.get_parameters()
+    objfunc = -model.get_objective_function_value()
+    assert result
+    assert np.abs(params["lengthscales"][0] - float(g["ls"])) < tol
+    assert np.abs(objfunc - float(g["ml"])) < tol
+    assert np.abs(out["f*"] - g["pred_mean"]) < tol
+    assert np.abs(out["f*_var"] - g["pred_std"] ** 2) < tol
+    assert np.abs(out["y_var"] - (out["f*_var"] + eps ** 2)) < 1e-14
+    assert set(out) == {"f*", "f*_var", "y_var", "f_bar"} and out["f_bar"].shape == out["f*"].shape
+    assert model.gpu_name is None or "B200" in model.gpu_name
+    with pytest.raises(NotImplementedError):
+        model.predict(coords=g["x_test"], full_cov=True)
+
+
+def _frames(rng, E, D=3):
+    cols = ["x", "y", "t"][:D]
+    out = []
+    for e in range(E):
+        n = int(rng.integers(40, 260))
+        X = rng.uniform(-2e5, 2e5, (n, D))
+        if D == 3:
+            X[:, 2] = rng.integers(-4, 5, n)
+        cs = np.array([5e4, 5e4, 1.0][:D])
+        K = gpr.kernel_matrix("Matern32", X / cs, None, [2.0, 1.5, 3.0][:D], 0.7)
+        y = np.linalg.cholesky(K + 1e-8 * np.eye(n)) @ rng.standard_normal(n) + 0.2 * rng.standard_normal(n) + 3.0
+        df = pd.DataFrame(X, columns=cols)
+        df["obs"] = y
+        out.append(df)
+    return out, cols
+
+
+def test_driver_call_sequence_matches_oracle(built):
+    """The call order of LocalExpertOI.run (local_experts.py:1043-1164) on one expert, against the
+    oracle with the same transforms: constraints with scale=True and tol=1e-2, optimise, objective,
+    parameters, predict on raw coordinates."""
+    from gpsat_b200.models import B200GPRModel
+    rng = np.random.default_rng(5)
+    (df,), cols = _frames(rng, 1)
+    init = {"coords_scale": [5e4, 5e4, 1], "obs_mean": "local", "kernel": "Matern52"}
+    cons = {"lengthscales": {"low": [1e-8] * 3, "high": [6e5, 6e5, 9], "scale": True},
+            "likelihood_variance": {"low": 1e-5, "high": 2.0}}
+    model = B200GPRModel(data=df, obs_col="obs", coords_col=cols, expert_loc=np.zeros(3), **init)
+    model.set_parameter_constraints(cons, move_within_tol=True, tol=1e-2)
+    ok = model.optimise_parameters(max_iter=10_000)
+    obj = model.get_objective_function_value()
+    hyp = model.get_parameters("lengthscales", "kernel_variance", "likelihood_variance")
+    pc = rng.uniform(-1e5, 1e5, (30, 3))
+    pred = model.predict(coords=pc)
+
+    cs = np.array([5e4, 5e4, 1.0])
+    X = df[cols].values / cs
+    y = df["obs"].values - df["obs"].mean()
+    tr = gpr.Transform.gpflow_default(3)
+    tr.set_sigmoid([0, 1, 2], np.array([1e-8] * 3) / cs, np.array([6e5, 6e5, 9]) / cs)
+    tr.set_sigmoid([4], [1e-5], [2.0])
+    th, l, ok_ref, nev = gpr.fit("Matern52", X, y, np.ones(5), tr)
+    assert ok == ok_ref
+    theta = np.concatenate([hyp["lengthscales"], [hyp["kernel_variance"], hyp["likelihood_variance"]]])
+    np.testing.assert_allclose(theta, th, rtol=1e-4)
+    assert abs(obj + l) <= 1e-4 * abs(l)
+    p = gpr.predict("Matern52", X, y, theta, pc / cs)
+    np.testing.assert_allclose(pred["f*"], p["f*"], rtol=1e-8, atol=1e-10)
+    np.testing.assert_allclose(pred["f*_var"], p["f*_var"], rtol=1e-8, atol=1e-12)
+    np.testing.assert_allclose(pred["f_bar"], np.repeat(df["obs"].mean(), 30))
+    assert obj == pytest.approx(-gpr.lml("Matern52", X, y, theta), rel=1e-10)
+
+
+def test_batched_equals_per_instance(built):
+    """fit_predict_models (one engine call for all experts) gives bit-identical parameters and
+    predictions to the per-instance calls the reference driver makes."""
+    from gpsat_b200.models import B200GPRModel, fit_predict_models
+    rng = np.random.default_rng(11)
+    frames, cols = _frames(rng, 5)
+    init = {"coords_scale": [5e4, 5e4, 1], "obs_mean": "local"}
+    cons = {"lengthscales": {"low": [1e-8] * 3, "high": [6e5, 6e5, 9], "scale": True}}
+    pcs = [rng.uniform(-1e5, 1e5, (int(rng.integers(1, 40)), 3)) for _ in frames]
+
+    def make():
+        ms = [B200GPRModel(data=df, obs_col="obs", coords_col=cols, **init) for df in frames]
+        for m in ms:
+            m.set_parameter_constraints(cons, move_within_tol=True, tol=1e-2)
+        return ms
+
+    a = make()
+    succ, obj, preds = fit_predict_models(a, pcs, max_iter=25)
+    b = make()
+    for e, m in enumerate(b):
+        s = m.optimise_parameters(max_iter=25)
+        assert s == succ[e]
+        np.testing.assert_array_equal(m._theta, a[e]._theta)
+        assert m.get_objective_function_value() == obj[e]
+        pr = m.predict(pcs[e])
+        for k in ("f*", "f*_var", "y_var", "f_bar"):
+            np.testing.assert_array_equal(pr[k], preds[e][k])
+
+
+def test_priors_match_oracle(built):
+    """Extension: log prior density (GPflow convention) added to the objective."""
+    from gpsat_b200.models import B200GPRModel
+    rng = np.random.default_rng(3)
+    (df,), cols = _frames(rng, 1, D=2)
+    model = B200GPRModel(data=df, obs_col="obs", coords_col=cols, coords_scale=[5e4, 5e4], obs_mean="local",
+                         priors={"lengthscales": {"family": "gamma", "a": 2.0, "b": 1.5},
+                                 "kernel_variance": {"family": "lognormal", "a": -0.5, "b": 0.8},
+                                 "likelihood_variance": {"family": "normal", "a": 0.05, "b": 0.1}})
+    ok = model.optimise_parameters()
+    X = df[cols].values / np.array([5e4, 5e4])
+    y = df["obs"].values - df["obs"].mean()
+    tr = gpr.Transform.gpflow_default(2)
+    pri = (np.array([3, 3, 2, 1]), np.array([2.0, 2.0, -0.5, 0.05]), np.array([1.5, 1.5, 0.8, 0.1]))
+    th, l, ok_ref, nev, res = gpr.fit("Matern32", X, y, np.ones(4), tr, priors=pri, return_result=True)
+    assert ok == ok_ref
+    np.testing.assert_allclose(model._theta, th, rtol=1e-4)
+    assert model.opt_info["objective"] == pytest.approx(res.fun, rel=1e-6)
+    # the objective value reported to the driver stays the pure -LML (gpflow_models.py:337)
+    assert model.get_objective_function_value() == pytest.approx(-l, rel=1e-6)
