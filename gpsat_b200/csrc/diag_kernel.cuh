@@ -20,9 +20,11 @@ constexpr int LDP = PB + 4;                 // stride of the 32 x 32 side blocks
 constexpr int DIAG_CS_D = NB * LDD;
 constexpr int DIAG_WP_D = 4 * PB * LDP;     // W_pp, row-major, p = 0..3
 constexpr int DIAG_TT_D = 3 * PB * LDP;     // temporaries of the inverse sweep
+constexpr int DIAG_AUX_D = DIAG_WP_D + DIAG_TT_D + NB + 2 * PB + 8;   // scratch of diag_factor_tile
 constexpr int DIAG_XY_D = NB * GPSAT_DMAX + NB;
-constexpr int DIAG_SMEM_BYTES = (DIAG_CS_D + DIAG_WP_D + DIAG_TT_D + DIAG_XY_D + NB + 2 * PB + 8) * 8;
+constexpr int DIAG_SMEM_BYTES = (DIAG_CS_D + DIAG_AUX_D + DIAG_XY_D) * 8;
 static_assert(LDD == LDC, "add_aug_tile writes with stride LDC");
+static_assert(DIAG_AUX_D <= SM_WST_D + SM_XY_D, "step_kernel lends its W stages + coordinate arrays as scratch");
 
 // One 8 x 8 fragment: c += sa * A[8 rows][4*nk4 k] * B[8 rows][same k]^T (both k-contiguous).
 __device__ __forceinline__ void frag_nt(double& c0, double& c1, const double* A, int lda, const double* B,
@@ -33,45 +35,22 @@ __device__ __forceinline__ void frag_nt(double& c0, double& c1, const double* A,
   for (int k4 = 0; k4 < nk4; ++k4) dmma884(c0, c1, sa * ap[4 * k4], bp[4 * k4]);
 }
 
-__global__ void __launch_bounds__(GPSAT_THREADS, 1) diag_kernel(const SlotDesc* __restrict__ slots, int i) {
-  const SlotDesc& d = slots[blockIdx.x];
-  if (d.expert < 0 || i >= d.T) return;
-  extern __shared__ double smem[];
-  double* Cs = smem;                        // lower: S_ii -> L_ii;  strict upper: U_ii = W_ii^T
-  double* Wp = Cs + DIAG_CS_D;              // [4][32][LDP]  W_pp (lower triangular, with diagonal)
+// Factor the diagonal tile i of slot d held in shared memory: on entry the lower triangle of
+// Cs[128][LDD] is the Schur complement S_ii (the strict upper part may hold anything finite); on
+// exit L_ii / W_ii are in the slot's side buffers, U_ii in the slot matrix, logdet[i] (and quad,
+// notpd) are set.  aux: DIAG_AUX_D doubles of scratch.  All 256 threads of the CTA must call it.
+__device__ __noinline__ void diag_factor_tile(const SlotDesc& d, int i, double* Cs, double* aux, int tid) {
+  double* Wp = aux;                         // [4][32][LDP]  W_pp (lower triangular, with diagonal)
   double* Tt = Wp + DIAG_WP_D;              // [3][32][LDP]
-  double* xr = Tt + DIAG_TT_D;              // [DMAX][NB] coordinates (tile (0,0) only)
-  double* yr = xr + NB * GPSAT_DMAX;        // [NB]
-  double* wdiag = yr + NB;                  // [NB] 1 / L_cc
+  double* wdiag = Tt + DIAG_TT_D;           // [NB] 1 / L_cc
   double* colb = wdiag + NB;                // [2][32] column broadcast buffer of the panel warp
   double* misc = colb + 2 * PB;             // [0] log-determinant accumulator
-  const int tid = threadIdx.x;
   const int warp = tid >> 5, lane = tid & 31, lr = lane >> 2, lk = lane & 3;
   const int row0 = i * NB;
   const int n = d.n, ld = d.ld;
   int ncol = n - row0;               // real columns in this tile; local index ncol is the y row
   if (ncol > NB) ncol = NB;
   if (ncol < 0) ncol = 0;
-
-  // ---- load the running Schur complement (tile (0,0): evaluate the kernel directly) ----
-  if (i == 0) {
-    load_block_coords(d, 0, xr, yr, tid);
-    for (int idx = tid; idx < NB * LDD; idx += GPSAT_THREADS) Cs[idx] = 0.0;
-    __syncthreads();
-    add_aug_tile(d, 0, 0, xr, xr, yr, Cs, tid, true);
-  } else {
-    // whole tile through cp.async (all requests in flight at once), then clear the strict upper part
-    const double* src = d.A + (size_t)row0 * ld + row0;
-    for (int id = tid; id < NB * NB / 2; id += GPSAT_THREADS) {
-      const int r = id >> 6, ch = id & 63;
-      cp_async16(Cs + r * LDD + ch * 2, src + (size_t)r * ld + ch * 2);
-    }
-    cp_async_commit();
-    cp_async_wait<0>();
-    __syncthreads();
-    const int c = tid & (NB - 1);
-    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) if (c > r) Cs[r * LDD + c] = 0.0;
-  }
   if (tid == 0) misc[0] = 0.0;
   __syncthreads();
 
@@ -243,6 +222,37 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) diag_kernel(const SlotDesc* 
       Ut[(size_t)r * ld + c] = uv;
     }
   }
+}
+
+// Stand-alone launch: tile (0,0) of every slot (evaluates the covariance itself); the later
+// diagonal tiles are factored inside step_kernel by the CTA that completes their Schur complement.
+__global__ void __launch_bounds__(GPSAT_THREADS, 1) diag_kernel(const SlotDesc* __restrict__ slots, int i) {
+  const SlotDesc& d = slots[blockIdx.x];
+  if (d.expert < 0 || i >= d.T) return;
+  extern __shared__ double smem[];
+  double* Cs = smem;
+  double* aux = Cs + DIAG_CS_D;
+  double* xr = aux + DIAG_AUX_D;            // [DMAX][NB] coordinates (tile (0,0) only)
+  double* yr = xr + NB * GPSAT_DMAX;        // [NB]
+  const int tid = threadIdx.x;
+  if (i == 0) {
+    load_block_coords(d, 0, xr, yr, tid);
+    for (int idx = tid; idx < NB * LDD; idx += GPSAT_THREADS) Cs[idx] = 0.0;
+    __syncthreads();
+    add_aug_tile(d, 0, 0, xr, xr, yr, Cs, tid, true);
+  } else {
+    // whole tile through cp.async (all requests in flight at once)
+    const int row0 = i * NB, ld = d.ld;
+    const double* src = d.A + (size_t)row0 * ld + row0;
+    for (int id = tid; id < NB * NB / 2; id += GPSAT_THREADS) {
+      const int r = id >> 6, ch = id & 63;
+      cp_async16(Cs + r * LDD + ch * 2, src + (size_t)r * ld + ch * 2);
+    }
+    cp_async_commit();
+    cp_async_wait<0>();
+  }
+  __syncthreads();
+  diag_factor_tile(d, i, Cs, aux, tid);
 }
 
 }  // namespace gpsat

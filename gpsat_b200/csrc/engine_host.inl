@@ -190,16 +190,17 @@ static int choose_slots(Engine& g, int64_t E, int Tmax, int TRmax, int max_slots
 // One blocked sweep over all occupied slots.
 static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv) {
   const SlotDesc* slots = g.bslots.as<SlotDesc>();
+  {
+    ProfScope ps(g, PROF_DIAG);
+    diag_kernel<<<S, GPSAT_THREADS, DIAG_SMEM_BYTES, g.stream>>>(slots, 0);
+  }
+  g.stats.kernel_launches++;
   for (int i = 0; i < Tmax; ++i) {
-    {
-      ProfScope ps(g, PROF_DIAG);
-      diag_kernel<<<S, GPSAT_THREADS, DIAG_SMEM_BYTES, g.stream>>>(slots, i);
-    }
-    g.stats.kernel_launches++;
+    // step i factors block column i and, in its (i+1, i) tile, the diagonal tile i+1
     int ntile = (TRmax - 1 - i) + (do_inv ? i : 0);
     if (ntile > 0) {
       ProfScope ps(g, PROF_STEP);
-      step_kernel<<<dim3(ntile, S), GPSAT_THREADS, STEP_SMEM_BYTES, g.stream>>>(slots, i, do_inv ? 1 : 0);
+      step_kernel<<<dim3(S, ntile), GPSAT_THREADS, STEP_SMEM_BYTES, g.stream>>>(slots, i, do_inv ? 1 : 0);
       g.stats.kernel_launches++;
     }
   }

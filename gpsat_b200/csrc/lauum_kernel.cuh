@@ -27,7 +27,27 @@ __device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c,
   double pd[ND], pk = 0.0, pn = 0.0;
 #pragma unroll
   for (int dd = 0; dd < ND; ++dd) pd[dd] = 0.0;
-  if (gj < n) {
+  if (g0r + NB <= n && g0r > g0c) {
+    // interior off-diagonal tile: every element counts twice, no bounds, no diagonal
+#pragma unroll 4
+    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
+      const double aa = ar[r] * acv;
+      const double wq = 2.0 * (aa - (Cs[r * LDC + c] - aa));
+      double sd[ND], r2 = 0.0;
+#pragma unroll
+      for (int dd = 0; dd < ND; ++dd) {
+        double t = (DD > 0 || dd < D) ? xr[dd * NB + r] - cc.x[dd] : 0.0;
+        sd[dd] = t * t;
+        r2 += sd[dd];
+      }
+      double ku, gu;
+      kunit_gunit_of_r2<KIND>(r2, ku, gu);
+      const double wg = wq * gu;
+#pragma unroll
+      for (int dd = 0; dd < ND; ++dd) pd[dd] = fma(wg, sd[dd], pd[dd]);
+      pk = fma(wq, ku, pk);
+    }
+  } else if (gj < n) {
 #pragma unroll 2
     for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
       const int gi = g0r + r;
@@ -103,6 +123,8 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const Slot
   const int warp = tid >> 5, lane = tid & 31;
   const int n = d.n, ld = d.ld;
 
+  const int kend = ((n + 1 + KC - 1) / KC) * KC;     // includes column n (the -alpha column)
+  gemm_nt_prologue(d.A + (size_t)i * NB * ld, d.A + (size_t)j * NB * ld, ld, i * NB, kend, smem, tid);
   load_block_coords(d, i * NB, xr, ar, tid);      // ar / ac overwritten with alpha below
   load_block_coords(d, j * NB, xc, ac, tid);
   __syncthreads();
@@ -114,7 +136,6 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const Slot
   {
     Acc acc;
     acc_zero(acc);
-    const int kend = ((n + 1 + KC - 1) / KC) * KC;     // includes column n (the -alpha column)
     gemm_nt_mainloop(acc, d.A + (size_t)i * NB * ld, d.A + (size_t)j * NB * ld, ld, i * NB, kend, smem, tid, true);
     __syncthreads();
     acc_to_smem(acc, Cs, tid, 1.0);

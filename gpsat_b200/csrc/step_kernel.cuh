@@ -1,5 +1,6 @@
 // step_kernel(i): all off-diagonal work of block column i for every expert in flight.
-//   blockIdx.y = slot, blockIdx.x = tile within the step:
+//   blockIdx.x = slot, blockIdx.y = tile within the step (x fastest: the tile-0 CTAs of all slots,
+//   which also factor the next diagonal tile, are dispatched first):
 //     [0, TR-1-i)            potrf tile (r, i), r = i + 1 + x
 //     [TR-1-i, TR-1-i + i)   trtri tile (j, i), j = x - (TR-1-i)      (only when do_inv)
 // Phases of one CTA (256 threads, one 128 x 128 output tile):
@@ -7,23 +8,30 @@
 //   2. C           = K_ri - acc (potrf, covariance evaluated in a rolled per-column loop) | acc
 //   3. out         = C W_ii^T, W_ii lower triangular: strip-mapped DMMA over k <= c only
 //   4. (potrf)     S_rr -= out out^T, lower triangle only, strip-mapped; coalesced update
+//   5. (tile (i+1, i) only)  S_{i+1,i+1} is now final: factor it in place (diag_factor_tile), so the
+//                  serial diagonal factorisation overlaps the other tiles of the step
 #pragma once
 #include "tiles.cuh"
+#include "diag_kernel.cuh"
 
 namespace gpsat {
 
 // acc[strip rows][c] = sum_{k <= c} Cs[row][k] * W[c][k];  W (row-major 128 x 128, global) is
 // streamed through NWSTAGE B-only stages.  Each warp reads only its own strip of Cs.
-__device__ __forceinline__ void wmult_strip(AccStrip& acc, const double* Cs, const double* Wg, double* wst,
-                                            int tid) {
-  const int warp = tid >> 5, lane = tid & 31, lr = lane >> 2, lk = lane & 3;
-  const int strip = strip_of_warp(warp);
-  constexpr int NSL = NB / KC;
+__device__ __forceinline__ void wmult_prefetch(const double* Wg, double* wst, int tid) {
 #pragma unroll
   for (int s = 0; s < NWSTAGE - 1; ++s) {
     load_slab(wst + s * NB * LDS_S, Wg + s * KC, NB, tid);
     cp_async_commit();
   }
+}
+
+// after wmult_prefetch(Wg, wst)
+__device__ __forceinline__ void wmult_strip(AccStrip& acc, const double* Cs, const double* Wg, double* wst,
+                                            int tid) {
+  const int warp = tid >> 5, lane = tid & 31, lr = lane >> 2, lk = lane & 3;
+  const int strip = strip_of_warp(warp);
+  constexpr int NSL = NB / KC;
   const double* ap = Cs + (16 * strip + lr) * LDC + lk;
 #pragma unroll 1
   for (int s = 0; s < NSL; ++s) {
@@ -44,11 +52,11 @@ __device__ __forceinline__ void wmult_strip(AccStrip& acc, const double* Cs, con
 
 __global__ void __launch_bounds__(GPSAT_THREADS, 1)
 step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
-  const SlotDesc& d = slots[blockIdx.y];
+  const SlotDesc& d = slots[blockIdx.x];
   if (d.expert < 0 || i >= d.T) return;
   const int npot = d.TR - 1 - i;
   const int ninv = do_inv ? i : 0;
-  const int x = blockIdx.x;
+  const int x = blockIdx.y;
   if (x >= npot + ninv) return;
   const bool is_pot = x < npot;
   const int rowblk = is_pot ? (i + 1 + x) : (x - npot);   // r (potrf) or j (trtri)
@@ -67,20 +75,21 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
   const int ld = d.ld;
   const double* Wg = d.Wd + (size_t)i * NB * NB;
 
-  if (is_pot) {
-    load_block_coords(d, rowblk * NB, xr, yr, tid);
-    load_block_coords(d, i * NB, xc, yc, tid);
-  }
-
-  // ---- 1. main loop ----
+  // ---- 1. main loop (slab loads first, the coordinate loads hide behind them) ----
   {
     Acc acc;
     acc_zero(acc);
     const double* Ag = d.A + (size_t)rowblk * NB * ld;
     const double* Bg = d.A + (size_t)i * NB * ld;
     const int kbeg = is_pot ? 0 : rowblk * NB;
+    gemm_nt_prologue(Ag, Bg, ld, kbeg, i * NB, smem, tid);
+    if (is_pot) {
+      load_block_coords(d, rowblk * NB, xr, yr, tid);
+      load_block_coords(d, i * NB, xc, yc, tid);
+    }
     gemm_nt_mainloop(acc, Ag, Bg, ld, kbeg, i * NB, smem, tid, !is_pot);   // trtri: U_jj is upper triangular
     __syncthreads();   // coords visible; stages free
+    wmult_prefetch(Wg, wst, tid);      // W_ii streams in under the epilogue
     // ---- 2. C to shared memory ----
     acc_to_smem(acc, Cs, tid, is_pot ? -1.0 : 1.0);
   }
@@ -138,11 +147,22 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
           *reinterpret_cast<double2*>(Cw + rf * 8 * LDC + cf * 8) = make_double2(-sy.c[rf][cf][0], -sy.c[rf][cf][1]);
   }
   __syncthreads();
-  // the two loops below touch element (r, c) from the same thread: no barrier between them
+  // the loops below touch element (r, c) from the same thread: no barrier between them
   if (i == 0) add_aug_tile(d, rowblk * NB, rowblk * NB, xr, xr, yr, Cs, tid, true);
   {
     double* Sg = d.A + (size_t)rowblk * NB * ld + (size_t)rowblk * NB;
     const int c = tid & (NB - 1);
+    if (x == 0) {
+      // ---- 5. rowblk == i + 1: the Schur complement is complete; factor the next diagonal tile ----
+      if (i > 0) {
+#pragma unroll 16
+        for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
+          if (c <= r) Cs[r * LDC + c] += Sg[(size_t)r * ld + c];
+      }
+      __syncthreads();
+      diag_factor_tile(d, rowblk, Cs, wst, tid);    // scratch: the W stages + coordinate arrays
+      return;
+    }
     if (i == 0) {
       for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
         if (c <= r) Sg[(size_t)r * ld + c] = Cs[r * LDC + c];

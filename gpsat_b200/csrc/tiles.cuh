@@ -126,13 +126,11 @@ __device__ __forceinline__ void load_slab(double* dst, const double* src, int ld
 }
 
 // acc += sum_{k in [kbeg, kend)} Ag[m][k] * Bg[n][k]   (kbeg, kend multiples of KC)
-// tri_first: the first 128-block of A (k in [kbeg, kbeg + 128)) is upper triangular.
-__device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, const double* Bg, int ldg,
-                                                 int kbeg, int kend, double* stages, int tid,
-                                                 bool tri_first = false) {
-  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
+// Pipeline prologue of gemm_nt_mainloop: issue the first NSTAGE-1 slab loads.  Split out so that
+// callers can put other global loads (coordinates) behind it instead of in front of it.
+__device__ __forceinline__ void gemm_nt_prologue(const double* Ag, const double* Bg, int ldg, int kbeg, int kend,
+                                                 double* stages, int tid) {
   const int nslab = (kend - kbeg) / KC;
-  if (nslab <= 0) return;
 #pragma unroll
   for (int s = 0; s < NSTAGE - 1; ++s) {
     if (s < nslab) {
@@ -142,6 +140,16 @@ __device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, con
     }
     cp_async_commit();
   }
+}
+
+// acc += sum_{k in [kbeg, kend)} Ag[m][k] * Bg[n][k]   (kbeg, kend multiples of KC), after
+// gemm_nt_prologue with the same arguments.  tri_first: the first 128-block of A
+// (k in [kbeg, kbeg + 128)) is upper triangular.
+__device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, const double* Bg, int ldg,
+                                                 int kbeg, int kend, double* stages, int tid,
+                                                 bool tri_first = false) {
+  const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
+  const int nslab = (kend - kbeg) / KC;
   for (int s = 0; s < nslab; ++s) {
     cp_async_wait<NSTAGE - 2>();
     __syncthreads();
@@ -214,15 +222,36 @@ __device__ __forceinline__ double aug_value(const SlotDesc& d, int gr, int gc, i
 }
 
 // Cs[r][c] += aug(g0r + r, g0c + c) for the whole tile (lower_only: c <= r only).
+// Tiles whose rows are all observation rows (or all prediction rows) and whose columns are all
+// observation columns take a branch-free path: var * k(r2) (+ noise on the global diagonal).
 template <int KIND, int DD>
 __device__ __forceinline__ void add_aug_tile_t(const SlotDesc& d, int g0r, int g0c, const double* xr,
                                                const double* xc, const double* yc, double* Cs, int tid,
                                                bool lower_only) {
   const int c = tid & (NB - 1);
+  const int n = d.n;
   ColCoords<DD> cc;
   cc.load(xc, c, d.D);
-  const double ycv = yc[c];
+  const bool rows_plain = (g0r + NB <= n) || (g0r > n && g0r + NB <= n + 1 + d.m);
+  if (rows_plain && g0c + NB <= n) {
+    const double var = d.var;
+    if (g0r != g0c) {
 #pragma unroll 4
+      for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
+        Cs[r * LDC + c] += var * kunit_of_r2<KIND>(cc.r2(xr, r, d.D));
+    } else {
+      const double noise = d.noise;
+#pragma unroll 4
+      for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
+        if (lower_only && c > r) continue;
+        double v = var * kunit_of_r2<KIND>(cc.r2(xr, r, d.D));
+        Cs[r * LDC + c] += (r == c) ? v + noise : v;
+      }
+    }
+    return;
+  }
+  const double ycv = yc[c];
+#pragma unroll 2
   for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
     if (lower_only && c > r) continue;
     Cs[r * LDC + c] += aug_value<KIND, DD>(d, g0r + r, g0c + c, r, xr, cc, ycv);
