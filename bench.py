@@ -258,8 +258,15 @@ def run_ours(args):
     peak, peak_src = fp64_peak_tflops()
     achieved = flops_step / (ms_step * 1e-3) / 1e12
     total_flops = args.steps * float(np.sum(nev * n ** 3) + np.sum(n ** 3 / 3.0 + n ** 2 * m))
-    roofline = {"bound": "tensor", "kernel": "step_kernel (FP64 DMMA potrf/trtri tiles)", "achieved": achieved,
-                "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+    traffic, traffic_src = None, None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], tj["source"]
+    except Exception:
+        pass
+    roofline = {"bound": "tensor", "kernel": "step_kernel (FP64 DMMA potrf/trtri tiles + fused diagonal factorisation)",
+                "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": traffic_src, "peak_source": peak_src,
                 "launches": int(n_step), "avg_launch_ms": ms_step / max(n_step, 1),
                 "whole_job_tflops": total_flops / (ms_total * 1e-3) / 1e12,
                 "whole_job_frac": total_flops / (ms_total * 1e-3) / 1e12 / peak,
