@@ -24,7 +24,7 @@ STATUS_OK, STATUS_NOT_PD, STATUS_LINESEARCH, STATUS_MAXITER, STATUS_BAD_INPUT = 
 EXPORTED_SYMBOLS = (
     "gpsat_version", "gpsat_last_error", "gpsat_device_name", "gpsat_engine_create", "gpsat_engine_destroy",
     "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_fit_options_default",
-    "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_factor_debug",
+    "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
 )
 
 
@@ -82,6 +82,7 @@ def load():
     lib.gpsat_gpr_fit.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp,
                                   C.POINTER(FitOptions), C.POINTER(Priors), vp, vp, vp, vp, vp]
     lib.gpsat_gpr_predict.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp, vp]
+    lib.gpsat_gpr_predict_cov.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp, vp, vp]
     lib.gpsat_gpr_factor_debug.argtypes = [vp, C.POINTER(Batch), vp, vp, vp]
     _lib = lib
     return lib

@@ -63,7 +63,7 @@ int gpsat_engine_destroy(gpsat_engine* h) {
   cudaStreamSynchronize(g.stream);
   for (cudaEvent_t ev : g.evpool) cudaEventDestroy(ev);
   for (DevBuf* b : {&g.bX, &g.by, &g.bXs, &g.boffn, &g.boffm, &g.border, &g.btheta, &g.bmisc, &g.bslots,
-                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout})
+                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov})
     b->release();
   if (g.h_counters) cudaFreeHost(g.h_counters);
   cudaEventDestroy(g.ev0); cudaEventDestroy(g.ev1);
@@ -151,8 +151,10 @@ int gpsat_gpr_lml_grad(gpsat_engine* h, const gpsat_batch* batch, int mem, const
 }
 
 // ---- prediction at fixed theta --------------------------------------------------------------
-int gpsat_gpr_predict(gpsat_engine* h, const gpsat_batch* batch, int mem, const double* theta, double* fmean,
-                      double* fvar, double* yvar, double* lml, int32_t* status) {
+}  // extern "C"
+
+static int predict_impl(gpsat_engine* h, const gpsat_batch* batch, int mem, const double* theta, double* fmean,
+                        double* fvar, double* yvar, double* fcov, double* lml, int32_t* status) {
   REQUIRE(h != nullptr, "engine is NULL");
   if (check_batch(batch, true)) return 2;
   REQUIRE(theta && fmean && fvar && yvar, "theta / output is NULL");
@@ -179,6 +181,24 @@ int gpsat_gpr_predict(gpsat_engine* h, const gpsat_batch* batch, int mem, const 
   double* dfm = dev ? fmean : reinterpret_cast<double*>(base + o_pred);
   double* dfv = dev ? fvar : dfm + M;
   double* dyv = dev ? yvar : dfv + M;
+  // full covariance blocks: expert e owns m_e x m_e doubles at off_c[e]
+  double* dcov = nullptr;
+  int64_t* doffc = nullptr;
+  int64_t ctotal = 0;
+  if (fcov) {
+    std::vector<int64_t> offc(E + 1, 0);
+    for (int64_t e = 0; e < E; ++e) offc[e + 1] = offc[e] + g.hm[e] * g.hm[e];
+    ctotal = offc[E];
+    if (g.bmisc.ensure((E + 1) * 8)) return 1;
+    doffc = g.bmisc.as<int64_t>();
+    CUDA_TRY(cudaMemcpyAsync(doffc, offc.data(), (E + 1) * 8, cudaMemcpyHostToDevice, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));    // offc is a stack-lifetime source
+    if (dev) dcov = fcov;
+    else {
+      if (g.bcov.ensure(std::max<int64_t>(ctotal, 1) * 8)) return 1;
+      dcov = g.bcov.as<double>();
+    }
+  }
   SlotDesc* slots = g.bslots.as<SlotDesc>();
   const SlotMem* mems = g.bmems.as<SlotMem>();
   for (int64_t b0 = 0; b0 < E; b0 += S) {
@@ -195,6 +215,11 @@ int gpsat_gpr_predict(gpsat_engine* h, const gpsat_batch* batch, int mem, const 
       ProfScope ps(g, PROF_REDUCE);
       predict_reduce_kernel<<<dim3((unsigned)((mb * 32 + 255) / 256), S), 256, 0, g.stream>>>(slots, bd.off_m, dfm, dfv, dyv);
       g.stats.kernel_launches++;
+      if (fcov) {
+        const unsigned nt = (unsigned)((mb + 63) / 64);
+        predict_cov_kernel<<<dim3(nt, nt, S), 256, 0, g.stream>>>(slots, doffc, dcov);
+        g.stats.kernel_launches++;
+      }
     }
     eval_finish_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(slots, bd, (const double*)dtheta, dlml, nullptr, dstatus, S);
     g.stats.kernel_launches += 2;
@@ -213,10 +238,24 @@ int gpsat_gpr_predict(gpsat_engine* h, const gpsat_batch* batch, int mem, const 
     }
     if (lml) CUDA_TRY(cudaMemcpyAsync(lml, dlml, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
     if (status) CUDA_TRY(cudaMemcpyAsync(status, dstatus, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
-    g.stats.d2h_bytes += (double)M * 24 + (double)E * 12;
+    if (fcov && ctotal > 0) CUDA_TRY(cudaMemcpyAsync(fcov, dcov, (size_t)ctotal * 8, cudaMemcpyDeviceToHost, g.stream));
+    g.stats.d2h_bytes += (double)M * 24 + (double)E * 12 + (fcov ? (double)ctotal * 8 : 0.0);
   }
   CUDA_TRY(cudaGetLastError());
   return end_call(g);
+}
+
+extern "C" {
+
+int gpsat_gpr_predict(gpsat_engine* h, const gpsat_batch* batch, int mem, const double* theta, double* fmean,
+                      double* fvar, double* yvar, double* lml, int32_t* status) {
+  return predict_impl(h, batch, mem, theta, fmean, fvar, yvar, nullptr, lml, status);
+}
+
+int gpsat_gpr_predict_cov(gpsat_engine* h, const gpsat_batch* batch, int mem, const double* theta, double* fmean,
+                          double* fvar, double* yvar, double* fcov, double* lml, int32_t* status) {
+  REQUIRE(fcov != nullptr, "fcov is NULL");
+  return predict_impl(h, batch, mem, theta, fmean, fvar, yvar, fcov, lml, status);
 }
 
 }  // extern "C"

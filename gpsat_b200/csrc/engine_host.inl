@@ -27,7 +27,7 @@ struct Engine {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int* h_counters = nullptr;          // pinned [4]
-  DevBuf bX, by, bXs, boffn, boffm, border, btheta, bmisc, bslots, bmems, bA, bside, bstates, bout;
+  DevBuf bX, by, bXs, boffn, boffm, border, btheta, bmisc, bslots, bmems, bA, bside, bstates, bout, bcov;
   gpsat_stats stats{};
   // host copy of the current batch shape
   std::vector<int64_t> hn, hm;

@@ -202,4 +202,68 @@ __global__ void predict_reduce_kernel(const SlotDesc* __restrict__ slots, const 
   }
 }
 
+// predict_cov_kernel: full posterior covariance of the prediction rows of one slot,
+//   cov[s][t] = k(xs_s, xs_t) - <A_s, A_t>,   A_s = row n+1+s of the factored matrix (columns < n),
+// written as a dense m x m block at fcov + off_c[expert] (GPR.predict_f(full_cov=True), called at
+// GPSat/models/gpflow_models.py:230).  64 x 64 output tile per CTA, 4 x 4 per thread, plain DFMA:
+// this is an occasional diagnostic output, not part of the timed hot path.
+__device__ __forceinline__ double factor_entry(const SlotDesc& d, int g, int k) {
+  const int c0 = (d.T - 1) * NB;
+  if (g < d.T * NB && k >= c0) return d.Ld[(size_t)(d.T - 1) * NB * NB + (size_t)(g - c0) * NB + (k - c0)];
+  return d.A[(size_t)g * d.ld + k];
+}
+
+__global__ void __launch_bounds__(256) predict_cov_kernel(const SlotDesc* __restrict__ slots,
+                                                          const int64_t* __restrict__ off_c, double* __restrict__ fcov) {
+  const SlotDesc& d = slots[blockIdx.z];
+  if (d.expert < 0) return;
+  const int m = d.m, n = d.n, D = d.D;
+  const int s0 = blockIdx.y * 64, t0 = blockIdx.x * 64;
+  if (s0 >= m || t0 >= m || t0 > s0) return;          // lower tiles; mirrored on store
+  __shared__ double As[64][17], Bs[64][17];
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  double acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+  for (int k0 = 0; k0 < n; k0 += 16) {
+    for (int idx = tid; idx < 64 * 16; idx += 256) {
+      const int r = idx >> 4, k = idx & 15;
+      As[r][k] = (s0 + r < m && k0 + k < n) ? factor_entry(d, n + 1 + s0 + r, k0 + k) : 0.0;
+      Bs[r][k] = (t0 + r < m && k0 + k < n) ? factor_entry(d, n + 1 + t0 + r, k0 + k) : 0.0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      double av[4], bv[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) av[a] = As[ty * 4 + a][k];
+#pragma unroll
+      for (int b = 0; b < 4; ++b) bv[b] = Bs[tx * 4 + b][k];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = fma(av[a], bv[b], acc[a][b]);
+    }
+    __syncthreads();
+  }
+  double* out = fcov + off_c[d.expert];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int s = s0 + ty * 4 + a, t = t0 + tx * 4 + b;
+      if (s >= m || t >= m || t > s) continue;
+      double r2 = 0.0;
+      for (int dd = 0; dd < D; ++dd) {
+        double df = (d.Xs[(size_t)s * D + dd] - d.Xs[(size_t)t * D + dd]) * d.inv_ls[dd];
+        r2 += df * df;
+      }
+      const double v = d.var * kunit_dyn(d.kind, r2) - acc[a][b];
+      out[(size_t)s * m + t] = v;
+      out[(size_t)t * m + s] = v;
+    }
+}
+
 }  // namespace gpsat

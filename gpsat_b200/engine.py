@@ -255,7 +255,23 @@ class Engine:
         return {"f*": fm, "f*_var": fv, "y_var": yv, "lml": lml, "status": status}
 
     def predict_full_cov(self, batch: RaggedBatch, theta):
-        raise NotImplementedError("full_cov=True is not implemented in the engine yet (DESIGN.md section 8)")
+        """:meth:`predict` plus ``"f*_cov"``: a list with one dense [m_e, m_e] block per expert."""
+        E, P = batch.E, batch.D + 2
+        mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
+        M = int(batch.off_m[-1])
+        msz = batch.m.astype(np.int64)
+        off_c = np.concatenate([[0], np.cumsum(msz * msz)])
+        th = self._in(batch, theta, np.float64, (E, P))
+        fm, fv, yv = (self._empty(batch, (M,), np.float64) for _ in range(3))
+        cov = self._empty(batch, (int(off_c[-1]),), np.float64)
+        lml = self._empty(batch, (E,), np.float64)
+        status = self._empty(batch, (E,), np.int32)
+        cb = batch._c(True)
+        self._pre(batch)
+        _lib.check(self._lib.gpsat_gpr_predict_cov(self._h, C.byref(cb), mem, _ptr(th), _ptr(fm), _ptr(fv), _ptr(yv),
+                                                   _ptr(cov), _ptr(lml), _ptr(status)))
+        blocks = [cov[int(off_c[e]):int(off_c[e + 1])].reshape(int(msz[e]), int(msz[e])) for e in range(E)]
+        return {"f*": fm, "f*_var": fv, "y_var": yv, "f*_cov": blocks, "lml": lml, "status": status}
 
     def factor_debug(self, kernel: str, X, y, theta, want_U: bool = True):
         X = _f64(X)

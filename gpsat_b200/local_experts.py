@@ -1,0 +1,243 @@
+"""Batched local-expert driver: the loop body of ``LocalExpertOI.run`` for all experts at once.
+
+The reference processes experts serially (``GPSat/local_experts.py:930-1260``): select local data,
+build a model, apply constraints, optimise, read the objective and the hyper-parameters, predict,
+append rows to result tables.  Experts are independent, so this driver runs the same steps in
+three phases:
+
+* phase A (host): per expert, the reference's selection semantics -
+  ``DataLoader.local_data_select`` (``GPSat/dataloader.py:2354-2447``: column-wise comparisons
+  against ``reference_location[col] + val`` and KD-tree ball queries for multi-column entries) and
+  the ``max_dist`` radius filter of ``PredictionLocations`` (``GPSat/prediction_locations.py:18-43,
+  208-273``, missing coordinate columns filled from the expert location); experts with fewer than
+  ``min_obs`` observations get a NaN ``run_details`` row (``local_experts.py:988-1012``), experts
+  without prediction locations are skipped (``:962-965``);
+* phase B (device): one ``gpsat_gpr_fit`` + one ``gpsat_gpr_predict`` call for all remaining
+  experts (:func:`gpsat_b200.models.fit_predict_models`);
+* phase C (host): the same tables the reference writes - ``preds``, ``run_details`` and one table
+  per hyper-parameter, indexed by the expert location (``dict_of_array_to_table``,
+  ``local_experts.py:691-747``; ``lengthscales`` carries a ``_dim_0`` column,
+  ``GPSat/utils.py:1437-1497``), returned as pandas DataFrames and appended to an HDF5 store when
+  ``store_path`` is given and PyTables is importable.
+
+Only what sits on either side of the engine is restated here; config parsing, data loading from
+files, resume logic and plotting stay in GPSat (out of scope).
+"""
+from __future__ import annotations
+
+import time
+from typing import Dict, List, Optional
+
+import numpy as np
+import pandas as pd
+from scipy.spatial import cKDTree
+
+from .models import B200GPRModel, fit_predict_models
+
+_COMPS = {">=": np.greater_equal, ">": np.greater, "==": np.equal, "<": np.less, "<=": np.less_equal}
+
+
+def local_data_select(df: pd.DataFrame, reference_location: dict, local_select: List[dict],
+                      kdtree: Optional[list] = None) -> pd.DataFrame:
+    """Rows of ``df`` that satisfy every entry of ``local_select`` relative to the expert location
+    (same semantics as ``DataLoader.local_data_select``, ``GPSat/dataloader.py:2403-2447``)."""
+    select = np.ones(len(df), dtype=bool)
+    for idx, ls in enumerate(local_select):
+        col, comp = ls["col"], ls["comp"]
+        if isinstance(col, str):
+            assert col in df, f"col: {col} is not in data - {df.columns}"
+            assert col in reference_location, f"col: {col} is not in reference_location - {reference_location.keys()}"
+            assert comp in _COMPS, f"comp: {comp} is not valid"
+            select &= _COMPS[comp](df[col].values, reference_location[col] + ls["val"])
+        else:
+            assert comp in ["<", "<="], "for multi dimensional values only less than comparison handled"
+            for c in col:
+                assert c in df, f"column: {c} is not in df.columns: {df.columns}"
+                assert c in reference_location, f"col: {col} is not in reference_location - {reference_location.keys()}"
+            kdt = None
+            if kdtree is not None:
+                kdt = kdtree[idx] if isinstance(kdtree, list) else kdtree
+            if kdt is None:
+                kdt = cKDTree(df.loc[:, col].values)
+            in_ids = kdt.query_ball_point(x=[reference_location[c] for c in col], r=ls["val"])
+            tmp = np.zeros(len(df), dtype=bool)
+            tmp[in_ids] = True
+            select &= tmp
+    return df.loc[select, :]
+
+
+def prediction_coords_for(pred_df: Optional[pd.DataFrame], expert_loc: dict, coords_col: List[str],
+                          max_dist: Optional[float] = None, tree: Optional[cKDTree] = None,
+                          tree_cols: Optional[List[str]] = None) -> np.ndarray:
+    """Prediction coordinates of one expert: ``pred_df`` rows within ``max_dist`` of the expert
+    (Euclidean over the columns ``pred_df`` shares with ``coords_col``), columns missing from
+    ``pred_df`` filled with the expert's own value; ``pred_df=None`` predicts at the expert
+    location itself (``GPSat/prediction_locations.py:208-273``)."""
+    if pred_df is None:
+        return np.array([[expert_loc[c] for c in coords_col]], dtype=np.float64)
+    shared = tree_cols if tree_cols is not None else [c for c in coords_col if c in pred_df]
+    sel = pred_df
+    if max_dist is not None:
+        if tree is None:
+            tree = cKDTree(pred_df[shared].values)
+        ref = np.array([expert_loc[c] for c in shared], dtype=np.float64)
+        ids = np.array(sorted(tree.query_ball_point(ref, r=max_dist)), dtype=np.int64)
+        if len(ids):     # the reference keeps d^2 < max_dist^2, strictly (prediction_locations.py:31-43)
+            d2 = np.sum((pred_df[shared].values[ids] - ref) ** 2, axis=1)
+            ids = ids[d2 < max_dist * max_dist]
+        sel = pred_df.iloc[ids]
+    out = np.empty((len(sel), len(coords_col)), dtype=np.float64)
+    for k, c in enumerate(coords_col):
+        out[:, k] = sel[c].values if c in sel else expert_loc[c]
+    return out
+
+
+def dict_to_tables(x: dict, ref_loc: dict, table: Optional[str] = None) -> Dict[str, pd.DataFrame]:
+    """``dict_of_array_to_table`` of the reference (``local_experts.py:691-747``) for the shapes this
+    path produces: scalars and equal-length 1-d arrays are concatenated column-wise into one frame
+    named ``table``; with ``table=None`` every entry becomes its own frame, 1-d arrays with a
+    ``_dim_0`` column (``GPSat/utils.py:1437-1497``).  Frames are indexed by the expert location."""
+    names = list(ref_loc.keys())
+    vals = tuple(ref_loc.values())
+
+    def index(nrow):
+        if len(names) == 1:
+            return pd.Index([vals[0]] * nrow, name=names[0])
+        return pd.MultiIndex.from_tuples([vals] * nrow, names=names)
+
+    if len(x) == 0:
+        return {}
+    if table is not None:
+        cols = {k: np.atleast_1d(v) for k, v in x.items()}
+        nrow = max(len(v) for v in cols.values())
+        df = pd.DataFrame({k: (v if len(v) == nrow else np.repeat(v, nrow)) for k, v in cols.items()})
+        df.index = index(len(df))
+        return {table: df}
+    out = {}
+    for k, v in x.items():
+        v = np.asarray(v)
+        if v.ndim == 0:
+            df = pd.DataFrame({k: [v.item()]})
+        else:
+            df = pd.DataFrame({"_dim_0": np.arange(len(v)), k: v})
+        df.index = index(len(df))
+        out[k] = df
+    return out
+
+
+class LocalExpertOI:
+    """Batched counterpart of ``GPSat.local_experts.LocalExpertOI`` for in-memory data.
+
+    ``expert_locs``: DataFrame with (at least) the coordinate columns; ``data``: DataFrame of
+    observations; the config dicts use the reference's keys - ``data_config``: ``obs_col``,
+    ``coords_col``, ``local_select``; ``model_config``: ``init_params``, ``constraints``,
+    ``optim_kwargs``, ``pred_kwargs``, ``params_to_store``; ``pred_loc_config``: ``df`` (or ``None``
+    to predict at the expert location) and ``max_dist`` (``config_dataclasses.py:9-509``).
+    """
+
+    def __init__(self, expert_locs: pd.DataFrame, data: pd.DataFrame, data_config: dict,
+                 model_config: Optional[dict] = None, pred_loc_config: Optional[dict] = None):
+        self.expert_locs = expert_locs.reset_index(drop=True)
+        self.data = data
+        self.obs_col = data_config["obs_col"]
+        self.coords_col = list(data_config["coords_col"])
+        self.local_select = data_config["local_select"]
+        mc = dict(model_config or {})
+        oi_model = mc.get("oi_model", "B200GPRModel")
+        assert oi_model in ("B200GPRModel", B200GPRModel), "the batched driver runs B200GPRModel experts"
+        self.init_params = dict(mc.get("init_params") or {})
+        self.constraints = mc.get("constraints")
+        self.optim_kwargs = dict(mc.get("optim_kwargs") or {})
+        self.pred_kwargs = dict(mc.get("pred_kwargs") or {})
+        pts = mc.get("params_to_store", "all")
+        self.params_to_store = None if pts == "all" else pts
+        pc = dict(pred_loc_config or {})
+        self.pred_df = pc.get("df")
+        self.max_dist = pc.get("max_dist")
+
+    def _constraints_for_model(self):
+        """The driver forces ``scale=True`` on the lengthscale bounds when ``coords_scale`` is given
+        (``local_experts.py:1110-1114``)."""
+        if self.constraints is None:
+            return None
+        cons = {k: dict(v) for k, v in self.constraints.items()}
+        if "coords_scale" in self.init_params and "lengthscales" in cons:
+            cons["lengthscales"]["scale"] = True
+        return cons
+
+    def run(self, store_path: Optional[str] = None, optimise: bool = True, predict: bool = True,
+            min_obs: int = 3, table_suffix: str = "", config_id: int = 1) -> Dict[str, pd.DataFrame]:
+        """All experts: select, fit, predict, tabulate.  Returns ``{table name: DataFrame}`` with the
+        reference's tables (``preds``, ``run_details``, one per stored hyper-parameter), each name
+        extended by ``table_suffix``."""
+        t0 = time.time()
+        coords_col = self.coords_col
+        # phase A: selection (KD-trees are built once, as the reference caches them per global select)
+        kdtrees = [cKDTree(self.data.loc[:, ls["col"]].values) if not isinstance(ls["col"], str) else None
+                   for ls in self.local_select]
+        pred_tree, pred_cols = None, None
+        if self.pred_df is not None and self.max_dist is not None:
+            pred_cols = [c for c in coords_col if c in self.pred_df]
+            pred_tree = cKDTree(self.pred_df[pred_cols].values)
+        cons = self._constraints_for_model()
+        models, pcs, refs, skipped = [], [], [], []
+        for _, rl in self.expert_locs.iterrows():
+            ref = {c: rl[c] for c in coords_col}
+            pc = prediction_coords_for(self.pred_df, ref, coords_col, self.max_dist, pred_tree, pred_cols)
+            if len(pc) == 0:
+                continue                                   # local_experts.py:962-965
+            df_local = local_data_select(self.data, ref, self.local_select, kdtrees)
+            if len(df_local) < min_obs:
+                skipped.append((ref, len(df_local)))       # local_experts.py:988-1012
+                continue
+            m = B200GPRModel(data=df_local, obs_col=self.obs_col, coords_col=coords_col,
+                             expert_loc=np.array([ref[c] for c in coords_col]), verbose=False, **self.init_params)
+            if cons is not None:
+                m.set_parameter_constraints(cons, move_within_tol=True, tol=1e-2)
+            models.append(m); pcs.append(pc); refs.append(ref)
+        # phase B: one fit call + one predict call for every expert
+        opt_kwargs = dict(self.optim_kwargs)
+        t_sel = time.time()
+        if models:
+            success, objective, preds = fit_predict_models(
+                models, pcs if predict else None, optimise=optimise, max_iter=opt_kwargs.pop("max_iter", 10_000),
+                fixed_params=opt_kwargs.pop("fixed_params", None),
+                apply_scale=self.pred_kwargs.get("apply_scale", True), **opt_kwargs)
+        t_fit = time.time()
+        # phase C: tables
+        frames: Dict[str, List[pd.DataFrame]] = {}
+
+        def add(tabs):
+            for k, v in tabs.items():
+                frames.setdefault(k + table_suffix, []).append(v)
+
+        model_name = f"{B200GPRModel.__module__}.{B200GPRModel.__name__}"[:64]
+        for ref, nobs in skipped:
+            add(dict_to_tables({"num_obs": nobs, "run_time": np.nan, "objective_value": np.nan,
+                                "parameters_optimised": optimise, "optimise_success": False, "model": model_name,
+                                "device": "", "config_id": config_id}, ref, "run_details"))
+        per_expert = (t_fit - t_sel) / max(len(models), 1)
+        for e, m in enumerate(models):
+            device = m.cpu_name if m.gpu_name is None else m.gpu_name
+            add(dict_to_tables({"num_obs": len(m.obs), "run_time": per_expert, "objective_value": float(objective[e]),
+                                "parameters_optimised": optimise, "optimise_success": bool(success[e]) if optimise else False,
+                                "model": model_name, "device": str(device)[:64], "config_id": config_id},
+                               refs[e], "run_details"))
+            if predict:
+                pred = dict(preds[e])
+                for ci, c in enumerate(coords_col):
+                    pred[f"pred_loc_{c}"] = pcs[e][:, ci]
+                add(dict_to_tables(pred, refs[e], "preds"))
+            hypes = m.get_parameters(*(self.params_to_store or m.param_names))
+            add(dict_to_tables(hypes, refs[e], None))
+        tables = {k: pd.concat(v) for k, v in frames.items()}
+        self.timings = {"select_s": t_sel - t0, "engine_s": t_fit - t_sel, "tables_s": time.time() - t_fit}
+        if store_path is not None:
+            try:
+                with pd.HDFStore(store_path, mode="a") as store:     # needs PyTables, like the reference
+                    for k, v in tables.items():
+                        store.append(k, v, data_columns=True)
+            except ImportError as exc:
+                raise ImportError("writing result tables to HDF5 needs PyTables; call run(store_path=None) "
+                                  "to get the tables as DataFrames") from exc
+        return tables

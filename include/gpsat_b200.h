@@ -150,6 +150,13 @@ int gpsat_gpr_fit(gpsat_engine* eng, const gpsat_batch* batch, int mem, double* 
 int gpsat_gpr_predict(gpsat_engine* eng, const gpsat_batch* batch, int mem, const double* theta,
                       double* fmean, double* fvar, double* yvar, double* lml, int32_t* status);
 
+/* Same, plus the full posterior covariance of every expert's prediction points
+ * (GPR.predict_f(full_cov=True), gpflow_models.py:230, 245-263): expert e owns a dense row-major
+ * m_e x m_e block at fcov + sum_{e' < e} m_e'^2.  y_cov = f_cov + likelihood_variance * I. */
+int gpsat_gpr_predict_cov(gpsat_engine* eng, const gpsat_batch* batch, int mem, const double* theta,
+                          double* fmean, double* fvar, double* yvar, double* fcov, double* lml,
+                          int32_t* status);
+
 /* Test hook (single expert, host memory): dense factor of the augmented matrix.
  * Lout [(n+1)*(n+1)] row-major lower: rows < n = chol(K + s2 I), row n = (L^-1 y)^T, 1.
  * Uout [(n+1)*(n+1)] row-major upper: L_aug^-T (may be NULL). */

@@ -32,8 +32,6 @@ def test_b200_gpr_reference_kat(built, golden_dir):
     assert np.abs(out["y_var"] - (out["f*_var"] + eps ** 2)) < 1e-14
     assert set(out) == {"f*", "f*_var", "y_var", "f_bar"} and out["f_bar"].shape == out["f*"].shape
     assert model.gpu_name is None or "B200" in model.gpu_name
-    with pytest.raises(NotImplementedError):
-        model.predict(coords=g["x_test"], full_cov=True)
 
 
 def _frames(rng, E, D=3):
@@ -138,3 +136,76 @@ def test_priors_match_oracle(built):
     assert model.opt_info["objective"] == pytest.approx(res.fun, rel=1e-6)
     # the objective value reported to the driver stays the pure -LML (gpflow_models.py:337)
     assert model.get_objective_function_value() == pytest.approx(-l, rel=1e-6)
+
+
+@pytest.mark.parametrize("n,m", [(60, 5), (127, 70), (200, 130), (300, 64)])
+def test_full_cov(built, n, m):
+    """predict(full_cov=True): f*_cov / y_cov as gpflow_models.py:245-263 builds them."""
+    from gpsat_b200.models import B200GPRModel
+    rng = np.random.default_rng(n + m)
+    X = rng.uniform(-3, 3, (n, 2))
+    y = np.sin(X[:, 0]) + 0.1 * rng.standard_normal(n)
+    model = B200GPRModel(coords=X.copy(), obs=y.copy(), kernel="Matern52",
+                         kernel_kwargs={"lengthscales": [1.3, 0.8], "variance": 0.9}, noise_variance=0.05)
+    Xs = rng.uniform(-3, 3, (m, 2))
+    out = model.predict(Xs, full_cov=True)
+    ref = gpr.predict("Matern52", X, y, model._theta, Xs, full_cov=True)
+    scale = np.abs(ref["f*_cov"]).max()
+    np.testing.assert_allclose(out["f*_cov"], ref["f*_cov"], rtol=0, atol=1e-10 * scale)
+    np.testing.assert_allclose(out["y_cov"], ref["y_cov"], rtol=0, atol=1e-10 * scale)
+    np.testing.assert_allclose(out["f*_var"], np.diag(ref["f*_cov"]), rtol=1e-8, atol=1e-12)
+    np.testing.assert_allclose(out["f*"], ref["f*"], rtol=1e-8, atol=1e-10)
+    assert np.array_equal(out["f*_cov"], out["f*_cov"].T)
+    assert set(out) == {"f*", "f*_var", "y_var", "f*_cov", "y_cov", "f_bar"}
+
+
+def test_batched_driver_equals_reference_loop(built):
+    """gpsat_b200.local_experts.LocalExpertOI.run == the reference's per-expert loop
+    (local_experts.py:930-1260) executed with B200GPRModel instances, table by table."""
+    from gpsat_b200.local_experts import LocalExpertOI, local_data_select, prediction_coords_for
+    from gpsat_b200.models import B200GPRModel
+    rng = np.random.default_rng(21)
+    n = 2500
+    data = pd.DataFrame({"x": rng.uniform(-4e5, 4e5, n), "y": rng.uniform(-4e5, 4e5, n),
+                         "t": rng.integers(-6, 7, n).astype(float)})
+    data["obs"] = np.sin(data.x / 1.5e5) + np.cos(data.y / 1e5) + 0.1 * data.t + 0.1 * rng.standard_normal(n)
+    locs = pd.DataFrame({"x": [-1e5, 0.0, 1.5e5, 3.9e5, 9e5], "y": [0.0, 1e5, -1e5, 3.9e5, 9e5], "t": [0.0] * 5})
+    grid = pd.DataFrame({"x": np.repeat(np.linspace(-4e5, 4e5, 33), 33), "y": np.tile(np.linspace(-4e5, 4e5, 33), 33)})
+    data_cfg = {"obs_col": "obs", "coords_col": ["x", "y", "t"],
+                "local_select": [{"col": "t", "comp": "<=", "val": 4}, {"col": "t", "comp": ">=", "val": -4},
+                                 {"col": ["x", "y"], "comp": "<", "val": 1.5e5}]}
+    model_cfg = {"oi_model": "B200GPRModel", "init_params": {"coords_scale": [5e4, 5e4, 1], "obs_mean": "local"},
+                 "constraints": {"lengthscales": {"low": [1e-8] * 3, "high": [6e5, 6e5, 9]}},
+                 "optim_kwargs": {"max_iter": 40}}
+    oi = LocalExpertOI(locs, data, data_cfg, model_cfg, {"df": grid, "max_dist": 1e5})
+    tabs = oi.run(min_obs=100)
+    assert set(tabs) == {"run_details", "preds", "lengthscales", "kernel_variance", "likelihood_variance"}
+    rd = tabs["run_details"]
+    assert len(rd) == 4                      # the last expert has no prediction location in range: skipped
+    assert rd["num_obs"].min() < 100 and np.isnan(rd.loc[rd["num_obs"] < 100, "objective_value"]).all()
+    # the reference loop, one model at a time
+    cons = {"lengthscales": {"low": [1e-8] * 3, "high": [6e5, 6e5, 9], "scale": True}}
+    k = 0
+    for _, rl in locs.iterrows():
+        ref = {c: rl[c] for c in ["x", "y", "t"]}
+        pc = prediction_coords_for(grid, ref, ["x", "y", "t"], 1e5)
+        df_local = local_data_select(data, ref, data_cfg["local_select"])
+        if len(pc) == 0 or len(df_local) < 100:
+            continue
+        m = B200GPRModel(data=df_local, obs_col="obs", coords_col=["x", "y", "t"], **model_cfg["init_params"])
+        m.set_parameter_constraints(cons, move_within_tol=True, tol=1e-2)
+        ok = m.optimise_parameters(max_iter=40)
+        obj = m.get_objective_function_value()
+        pr = m.predict(pc)
+        key = (ref["x"], ref["y"], ref["t"])
+        row = rd.loc[[key]]
+        assert bool(row["optimise_success"].iloc[0]) == ok and row["objective_value"].iloc[0] == obj
+        assert row["num_obs"].iloc[0] == len(df_local)
+        p = tabs["preds"].loc[[key]]
+        np.testing.assert_array_equal(p["f*"].values, pr["f*"])
+        np.testing.assert_array_equal(p["f*_var"].values, pr["f*_var"])
+        np.testing.assert_array_equal(p["pred_loc_x"].values, pc[:, 0])
+        np.testing.assert_array_equal(tabs["lengthscales"].loc[[key]]["lengthscales"].values, m.get_lengthscales())
+        assert tabs["kernel_variance"].loc[[key]]["kernel_variance"].iloc[0] == m.get_kernel_variance()
+        k += 1
+    assert k == 3
