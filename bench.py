@@ -313,6 +313,7 @@ def run_ours(args):
                            "mean_evals_per_expert": float(nev.mean()), "max_evals_per_expert": int(nev.max()),
                            "ticks_per_fit": int(collect["fit"][-1]["ticks"]), "slots": int(collect["fit"][-1]["slots"]),
                            "status_counts": {"ok": int(st[0]), "not_pd": int(st[1]), "linesearch": int(st[2]), "maxiter": int(st[3])}},
+                "lml_grad_evals_per_s": world * float(nev.sum()) * args.steps / (ms_total * 1e-3),
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clk}
         print(json.dumps(line))

@@ -266,3 +266,45 @@ def test_full_size_expert(engine, n):
     np.testing.assert_allclose(pred["f*_var"][:64], p["f*_var"], rtol=RTOL_FIXED, atol=1e-12)
     lml_b, grad_b, _ = engine.lml_grad(b, theta)
     assert np.array_equal(lml, lml_b) and np.array_equal(grad, grad_b)
+
+
+def test_bitwise_repeatable_and_order_independent(engine):
+    """Race / ordering proxy (compute-sanitizer is closed on this pool): every reduction in the sweep
+    has a fixed order, so repeated calls and a permuted batch give bit-identical results."""
+    rng = np.random.default_rng(77)
+    ns = [517, 130, 700, 64, 385, 257, 1030]
+    experts = [_expert(rng, n, 3, m=20 + n // 7) for n in ns]
+    theta = np.stack([_theta(rng, 3) for _ in ns])
+    b = _batch("Matern52", experts)
+    l1, g1, _ = engine.lml_grad(b, theta)
+    p1 = engine.predict(b, theta)
+    for _ in range(2):
+        l2, g2, _ = engine.lml_grad(b, theta)
+        p2 = engine.predict(b, theta)
+        assert np.array_equal(l1, l2) and np.array_equal(g1, g2)
+        assert np.array_equal(p1["f*"], p2["f*"]) and np.array_equal(p1["f*_var"], p2["f*_var"])
+    perm = [3, 6, 0, 5, 1, 4, 2]
+    bp = _batch("Matern52", [experts[k] for k in perm])
+    lp, gp, _ = engine.lml_grad(bp, theta[perm])
+    assert np.array_equal(lp, l1[perm]) and np.array_equal(gp, g1[perm])
+
+
+@pytest.mark.parametrize("n", [2000, 3100])
+def test_full_size_expert(engine, n):
+    """One expert at the sizes of configs c3 / north star (BASELINE.json): LML, gradient and
+    predictions against the oracle (LAPACK) at the fixed-theta tolerance."""
+    rng = np.random.default_rng(n)
+    X = rng.uniform(-8, 8, (n, 3))
+    f = np.sin(X[:, 0]) * np.cos(0.7 * X[:, 1]) + 0.3 * np.sin(0.5 * X[:, 2])
+    y = f + 0.1 * rng.standard_normal(n)
+    Xs = rng.uniform(-8, 8, (300, 3))
+    th = np.array([[1.7, 2.1, 3.0, 0.6, 0.02]])
+    b = _batch("Matern32", [(X, y, Xs)])
+    lml, grad, st = engine.lml_grad(b, th)
+    pred = engine.predict(b, th)
+    v, g = gpr.lml_and_grad("Matern32", X, y, th[0])
+    assert st[0] == 0 and abs(lml[0] - v) <= RTOL_FIXED * abs(v)
+    np.testing.assert_allclose(grad[0], g, rtol=1e-7, atol=1e-8 * np.abs(g).max())
+    p = gpr.predict("Matern32", X, y, th[0], Xs)
+    np.testing.assert_allclose(pred["f*"], p["f*"], rtol=RTOL_FIXED, atol=1e-9)
+    np.testing.assert_allclose(pred["f*_var"], p["f*_var"], rtol=RTOL_FIXED, atol=1e-11)

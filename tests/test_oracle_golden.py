@@ -124,3 +124,41 @@ def test_not_pd_is_minus_inf():
     X = np.zeros((5, 2))
     y = np.ones(5)
     assert gpr.lml("RBF", X, y, np.array([1.0, 1.0, 1.0, 0.0])) == -np.inf
+
+
+def test_sgpr_kat_localexperts(golden_dir):
+    """/root/reference/tests/test_localexperts.py:229-251 (test_gpflow_sgpr, M = N = 50), tol 1e-4 there."""
+    from oracle import sgpr
+    g = np.load(os.path.join(golden_dir, "kat_localexperts.npz"))
+    X, y = g["x_train"], g["y_train"][:, 0]
+    eps = float(g["eps"])
+    tr = gpr.Transform.gpflow_default(1)
+    tr.set_sigmoid(0, float(g["constraint_low"]), float(g["constraint_high"]))
+    th, l, ok, nev = sgpr.fit("Matern32", X, y, X.copy(), np.array([1.0, 1.0, eps ** 2]), tr,
+                              trainable=[True, False, False])
+    assert ok
+    assert abs(th[0] - float(g["ls"])) < 1e-4
+    p = sgpr.predict("Matern32", X, y, X.copy(), th, g["x_test"])
+    assert abs(p["f*"][0] - g["pred_mean"][0]) < 1e-4
+    assert abs(p["f*_var"][0] - g["pred_std"][0] ** 2) < 1e-4
+
+
+@pytest.mark.parametrize("kind", gpr.KERNELS)
+def test_sgpr_gradient_fd_and_tight_bound(kind):
+    from oracle import sgpr
+    rng = np.random.default_rng(4)
+    n, M, D = 120, 25, 3
+    X = rng.uniform(-3, 3, (n, D))
+    y = np.sin(X[:, 0]) + 0.3 * np.cos(X[:, 1]) + 0.1 * rng.standard_normal(n)
+    Z = X[rng.permutation(n)[:M]].copy()
+    th = np.array([1.3, 0.9, 2.0, 0.8, 0.05])
+    v, g = sgpr.elbo_and_grad(kind, X, y, Z, th)
+    for i in range(5):
+        e = np.zeros(5)
+        e[i] = 1e-6 * th[i]
+        fd = (sgpr.elbo(kind, X, y, Z, th + e) - sgpr.elbo(kind, X, y, Z, th - e)) / (2 * e[i])
+        assert abs(fd - g[i]) <= 1e-6 * max(1.0, abs(g[i]))
+    # the bound never exceeds the exact log marginal likelihood and is tight (up to the jitter) for Z = X
+    exact = gpr.lml(kind, X, y, th)
+    assert v <= exact + 1e-9
+    assert abs(sgpr.elbo(kind, X, y, X.copy(), th) - exact) < 1e-2
