@@ -17,7 +17,8 @@
 #define GPSAT_DMAX 6          // max input dimensions
 #define GPSAT_THREADS 256     // threads per CTA for the tile kernels (8 warps, 2 x 4)
 
-enum GpsatKernelKind : int { GPSAT_MATERN12 = 0, GPSAT_MATERN32 = 1, GPSAT_MATERN52 = 2, GPSAT_RBF = 3 };
+enum GpsatKernelKind : int { GPSAT_MATERN12 = 0, GPSAT_MATERN32 = 1, GPSAT_MATERN52 = 2, GPSAT_RBF = 3,
+                             GPSAT_PRECOMPUTED = 4 };   // matrix entries read from SlotDesc::pre (SGPR B matrix)
 
 // One expert in flight.  Written by the scheduler / optimiser kernel, read by the tile kernels.
 struct SlotDesc {
@@ -39,6 +40,8 @@ struct SlotDesc {
   double* quad;          // [1] |L^-1 y|^2
   double* gpart;         // [T*(T+1)/2][GPSAT_DMAX + 2] gradient partial sums per lauum tile
   int* notpd;            // [1] set to 1 when a pivot is not positive
+  const double* pre;     // kind == GPSAT_PRECOMPUTED: dense symmetric matrix (lower part read), else unused
+  int ldpre;
   double inv_ls[GPSAT_DMAX];
   double var;            // kernel variance
   double noise;          // likelihood variance

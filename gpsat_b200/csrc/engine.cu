@@ -23,6 +23,7 @@
 #include "diag_kernel.cuh"
 #include "step_kernel.cuh"
 #include "lauum_kernel.cuh"
+#include "sgpr_kernels.cuh"
 
 namespace gpsat {
 
@@ -149,6 +150,7 @@ __device__ __forceinline__ void slot_set_expert(SlotDesc& d, const SlotMem& mem,
   d.Xs = (m > 0) ? b.Xs + b.off_m[e] * b.D : nullptr;
   d.A = mem.A; d.Wd = mem.Wd; d.Ld = mem.Ld; d.logdet = mem.logdet; d.quad = mem.quad;
   d.gpart = mem.gpart; d.notpd = mem.notpd;
+  d.pre = nullptr; d.ldpre = 0;
   *d.notpd = 0;
   *d.quad = 0.0;
 }

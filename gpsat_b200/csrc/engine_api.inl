@@ -63,7 +63,7 @@ int gpsat_engine_destroy(gpsat_engine* h) {
   cudaStreamSynchronize(g.stream);
   for (cudaEvent_t ev : g.evpool) cudaEventDestroy(ev);
   for (DevBuf* b : {&g.bX, &g.by, &g.bXs, &g.boffn, &g.boffm, &g.border, &g.btheta, &g.bmisc, &g.bslots,
-                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov})
+                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov, &g.bZ, &g.bsg})
     b->release();
   if (g.h_counters) cudaFreeHost(g.h_counters);
   cudaEventDestroy(g.ev0); cudaEventDestroy(g.ev1);

@@ -130,3 +130,5 @@ int gpsat_gpr_factor_debug(gpsat_engine* h, const gpsat_batch* batch, const doub
 }
 
 }  // extern "C"
+
+#include "engine_sgpr.inl"

@@ -27,7 +27,7 @@ struct Engine {
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int* h_counters = nullptr;          // pinned [4]
-  DevBuf bX, by, bXs, boffn, boffm, border, btheta, bmisc, bslots, bmems, bA, bside, bstates, bout, bcov;
+  DevBuf bX, by, bXs, boffn, boffm, border, btheta, bmisc, bslots, bmems, bA, bside, bstates, bout, bcov, bZ, bsg;
   gpsat_stats stats{};
   // host copy of the current batch shape
   std::vector<int64_t> hn, hm;
@@ -79,6 +79,7 @@ static int engine_setup_kernels() {
   CUDA_TRY(cudaFuncSetAttribute(diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DIAG_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STEP_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(sgpr_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SGPR_GEMM_SMEM_BYTES));
   return 0;
 }
 
@@ -188,8 +189,9 @@ static int choose_slots(Engine& g, int64_t E, int Tmax, int TRmax, int max_slots
 }
 
 // One blocked sweep over all occupied slots.
-static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv) {
-  const SlotDesc* slots = g.bslots.as<SlotDesc>();
+static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, const SlotDesc* slots = nullptr,
+                        bool with_lauum = true) {
+  if (!slots) slots = g.bslots.as<SlotDesc>();
   {
     ProfScope ps(g, PROF_DIAG);
     diag_kernel<<<S, GPSAT_THREADS, DIAG_SMEM_BYTES, g.stream>>>(slots, 0);
@@ -204,7 +206,7 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv) {
       g.stats.kernel_launches++;
     }
   }
-  if (do_inv) {
+  if (do_inv && with_lauum) {
     ProfScope ps(g, PROF_LAUUM);
     lauum_grad_kernel<<<dim3(Tmax * (Tmax + 1) / 2, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots);
     g.stats.kernel_launches++;

@@ -258,8 +258,27 @@ __device__ __forceinline__ void add_aug_tile_t(const SlotDesc& d, int g0r, int g
   }
 }
 
+// Precomputed matrix instead of a covariance function (the B matrix of sparse GPR): same augmented
+// layout, entries below row n come from d.pre.
+__device__ __forceinline__ void add_pre_tile(const SlotDesc& d, int g0r, int g0c, const double* yc, double* Cs,
+                                             int tid, bool lower_only) {
+  const int c = tid & (NB - 1), gc = g0c + c, n = d.n;
+  const double ycv = yc[c];
+#pragma unroll 4
+  for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
+    if (lower_only && c > r) continue;
+    const int gr = g0r + r;
+    double v;
+    if (gc >= n) v = (gr == gc && gr > n) ? 1.0 : 0.0;
+    else if (gr == n) v = ycv;
+    else v = (gr < n) ? d.pre[(size_t)gr * d.ldpre + gc] : 0.0;
+    Cs[r * LDC + c] += v;
+  }
+}
+
 __device__ __noinline__ void add_aug_tile(const SlotDesc& d, int g0r, int g0c, const double* xr, const double* xc,
                                           const double* yc, double* Cs, int tid, bool lower_only) {
+  if (d.kind == GPSAT_PRECOMPUTED) { add_pre_tile(d, g0r, g0c, yc, Cs, tid, lower_only); return; }
   const bool d3 = d.D == 3;
   switch (d.kind) {
     case GPSAT_MATERN12:

@@ -273,6 +273,47 @@ class Engine:
         blocks = [cov[int(off_c[e]):int(off_c[e + 1])].reshape(int(msz[e]), int(msz[e])) for e in range(E)]
         return {"f*": fm, "f*_var": fv, "y_var": yv, "f*_cov": blocks, "lml": lml, "status": status}
 
+    # ---- sparse GPR (GPflowSGPRModel, gpflow_models.py:666-901) ------------------------------------
+    def _inducing(self, batch: RaggedBatch, Z):
+        """Z: one [M_e, D] array per expert -> (host off_z, packed Z on the batch's memory)."""
+        Zl = [np.asarray(z.cpu() if _is_torch(z) else z, dtype=np.float64).reshape(-1, batch.D) for z in Z]
+        if len(Zl) != batch.E:
+            raise ValueError(f"need one inducing-point array per expert: got {len(Zl)} for {batch.E} experts")
+        off_z = np.zeros(batch.E + 1, dtype=np.int64)
+        off_z[1:] = np.cumsum([len(z) for z in Zl])
+        Zp = np.ascontiguousarray(np.concatenate(Zl, axis=0)) if Zl else np.zeros((0, batch.D))
+        return off_z, self._in(batch, Zp, np.float64, Zp.shape)
+
+    def sgpr_elbo(self, batch: RaggedBatch, Z, theta):
+        """ELBO of ``gpflow.models.SGPR`` per expert at fixed theta.  Returns (elbo, status)."""
+        E, P = batch.E, batch.D + 2
+        mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
+        off_z, Zp = self._inducing(batch, Z)
+        th = self._in(batch, theta, np.float64, (E, P))
+        elbo = self._empty(batch, (E,), np.float64)
+        status = self._empty(batch, (E,), np.int32)
+        cb = batch._c(False)
+        self._pre(batch)
+        _lib.check(self._lib.gpsat_sgpr_elbo(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, _ptr(th), _ptr(elbo),
+                                             _ptr(status)))
+        return elbo, status
+
+    def sgpr_predict(self, batch: RaggedBatch, Z, theta):
+        """``SGPR.predict_f`` / ``predict_y`` (full_cov=False) per expert at fixed theta."""
+        E, P = batch.E, batch.D + 2
+        mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
+        M = int(batch.off_m[-1])
+        off_z, Zp = self._inducing(batch, Z)
+        th = self._in(batch, theta, np.float64, (E, P))
+        fm, fv, yv = (self._empty(batch, (M,), np.float64) for _ in range(3))
+        elbo = self._empty(batch, (E,), np.float64)
+        status = self._empty(batch, (E,), np.int32)
+        cb = batch._c(True)
+        self._pre(batch)
+        _lib.check(self._lib.gpsat_sgpr_predict(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, _ptr(th), _ptr(fm),
+                                                _ptr(fv), _ptr(yv), _ptr(elbo), _ptr(status)))
+        return {"f*": fm, "f*_var": fv, "y_var": yv, "elbo": elbo, "status": status}
+
     def factor_debug(self, kernel: str, X, y, theta, want_U: bool = True):
         X = _f64(X)
         X = X.reshape(len(X), -1)

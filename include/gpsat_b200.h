@@ -157,6 +157,23 @@ int gpsat_gpr_predict_cov(gpsat_engine* eng, const gpsat_batch* batch, int mem, 
                           double* fmean, double* fvar, double* yvar, double* fcov, double* lml,
                           int32_t* status);
 
+/* ---- sparse GPR (Titsias 2009): GPflowSGPRModel, GPSat/models/gpflow_models.py:666-901 ----------
+ * Inducing points are ragged like the observations: expert e owns rows off_z[e] .. off_z[e+1] of
+ * Z ([sum M_e][D], divided by coords_scale like X).  off_z is always a HOST array; Z and theta follow
+ * `mem`.  theta layout as for GPR: [lengthscales (D), kernel variance, likelihood variance].
+ *
+ * gpsat_sgpr_elbo: elbo[e] = gpflow.models.SGPR.elbo() (jitter 1e-6 on Kuu) — the value behind
+ * GPflowSGPRModel.get_objective_function_value (gpflow_models.py:860-862, which reports +elbo).
+ * status[e] = 1 when Kuu + jitter I or B is not positive definite (elbo = -inf). */
+int gpsat_sgpr_elbo(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,
+                    int mem, const double* theta, double* elbo, int32_t* status);
+
+/* SGPR.predict_f / predict_y (full_cov = False) at batch->Xs, as GPflowSGPRModel.predict uses them
+ * (gpflow_models.py:229-230 inherited); elbo (may be NULL) comes out of the same factorisation. */
+int gpsat_sgpr_predict(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,
+                       int mem, const double* theta, double* fmean, double* fvar, double* yvar,
+                       double* elbo, int32_t* status);
+
 /* Test hook (single expert, host memory): dense factor of the augmented matrix.
  * Lout [(n+1)*(n+1)] row-major lower: rows < n = chol(K + s2 I), row n = (L^-1 y)^T, 1.
  * Uout [(n+1)*(n+1)] row-major upper: L_aug^-T (may be NULL). */
