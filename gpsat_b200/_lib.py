@@ -25,7 +25,7 @@ EXPORTED_SYMBOLS = (
     "gpsat_version", "gpsat_last_error", "gpsat_device_name", "gpsat_engine_create", "gpsat_engine_destroy",
     "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_fit_options_default",
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
-    "gpsat_sgpr_elbo", "gpsat_sgpr_predict",
+    "gpsat_sgpr_elbo", "gpsat_sgpr_predict", "gpsat_sgpr_fit",
 )
 
 
@@ -85,7 +85,9 @@ def load():
     lib.gpsat_gpr_predict.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp, vp]
     lib.gpsat_gpr_predict_cov.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp, vp, vp]
     lib.gpsat_gpr_factor_debug.argtypes = [vp, C.POINTER(Batch), vp, vp, vp]
-    lib.gpsat_sgpr_elbo.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp]
+    lib.gpsat_sgpr_elbo.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp]
+    lib.gpsat_sgpr_fit.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp, vp,
+                                   C.POINTER(FitOptions), C.POINTER(Priors), vp, vp, vp, vp, vp]
     lib.gpsat_sgpr_predict.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp, vp, vp]
     _lib = lib
     return lib

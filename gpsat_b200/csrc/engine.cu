@@ -23,7 +23,6 @@
 #include "diag_kernel.cuh"
 #include "step_kernel.cuh"
 #include "lauum_kernel.cuh"
-#include "sgpr_kernels.cuh"
 
 namespace gpsat {
 
@@ -82,6 +81,10 @@ struct FitDev {
 struct SlotMem {
   double* A; double* Wd; double* Ld; double* logdet; double* quad; double* gpart; int* notpd;
 };
+
+}  // namespace gpsat
+#include "sgpr_kernels.cuh"
+namespace gpsat {
 
 // ---- transforms (gpflow.utilities.positive / tfp.bijectors.Sigmoid) -------------------------
 __device__ __forceinline__ double dev_sigmoid(double x) {
@@ -208,25 +211,22 @@ __global__ void fit_init_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b
   }
 }
 
-// One optimiser step for every occupied slot (one thread per slot).
-__global__ void lbfgs_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, FitDev f, int S, int ld) {
-  int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= S) return;
-  SlotDesc& d = slots[s];
-  if (d.expert < 0) return;
-  const int P = b.P;
-  LbfgsState& st = f.states[s];
-  int e = d.expert;
-  double theta[GPSAT_PMAX], gtheta[GPSAT_PMAX], gxi[GPSAT_PMAX];
-  // theta at the evaluated point
-  {
-    int k = 0;
-    for (int p = 0; p < P; ++p) {
-      size_t q = (size_t)e * P + p;
-      theta[p] = f.trainable[q] ? transform_fwd(f.tkind[q], f.ta[q], f.tb[q], st.xtrial[k++]) : f.theta[q];
-    }
+// theta at the optimiser's current trial point (fixed parameters keep their input value)
+__device__ __forceinline__ void fit_theta_trial(const FitDev& f, const LbfgsState& st, int e, int P, double* theta) {
+  int k = 0;
+  for (int p = 0; p < P; ++p) {
+    size_t q = (size_t)e * P + p;
+    theta[p] = f.trainable[q] ? transform_fwd(f.tkind[q], f.ta[q], f.tb[q], st.xtrial[k++]) : f.theta[q];
   }
-  double lml = slot_finish_eval(d, theta, gtheta, true);
+}
+
+// Feed one evaluation (val = lml or elbo at theta, gtheta = its gradient w.r.t. theta) to the
+// optimiser of expert e: chain rule to xi, priors, L-BFGS step.  When the optimiser stops the
+// per-expert outputs are written (theta at the accepted iterate, objective, ...).  Returns the
+// lbfgs_step code.
+__device__ int fit_advance(const FitDev& f, LbfgsState& st, int e, int P, double val, const double* theta,
+                           const double* gtheta) {
+  double gxi[GPSAT_PMAX];
   {
     int k = 0;
     for (int p = 0; p < P; ++p) {
@@ -251,48 +251,61 @@ __global__ void lbfgs_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, F
       }
     }
   }
-  double fval = isfinite(lml) ? -lml - logprior : INFINITY;
+  double fval = isfinite(val) ? -val - logprior : INFINITY;
   atomicAdd(&f.counters[3], 1);
   int rc = lbfgs_step(&st, fval, gxi, &f.opt);
-  if (rc != LBFGS_CONTINUE) {
-    // retire: theta at the accepted iterate
-    int k = 0;
-    for (int p = 0; p < P; ++p) {
-      size_t q = (size_t)e * P + p;
-      if (f.trainable[q]) f.theta[q] = transform_fwd(f.tkind[q], f.ta[q], f.tb[q], st.x[k++]);
-    }
-    f.objective[e] = st.f;
-    if (f.lml) {
-      double lp = 0.0;
-      if (f.pkind) {
-        int kk = 0;
-        for (int p = 0; p < P; ++p) {
-          size_t q = (size_t)e * P + p;
-          if (f.trainable[q]) {
-            double dxi = 0.0;
-            lp += log_prior_xi(f.pkind[q], f.pa[q], f.pb[q], f.tkind[q], f.ta[q], f.tb[q], st.x[kk], f.theta[q], &dxi);
-            ++kk;
-          }
+  if (rc == LBFGS_CONTINUE) return rc;
+  // retire: theta at the accepted iterate
+  int k = 0;
+  for (int p = 0; p < P; ++p) {
+    size_t q = (size_t)e * P + p;
+    if (f.trainable[q]) f.theta[q] = transform_fwd(f.tkind[q], f.ta[q], f.tb[q], st.x[k++]);
+  }
+  f.objective[e] = st.f;
+  if (f.lml) {
+    double lp = 0.0;
+    if (f.pkind) {
+      int kk = 0;
+      for (int p = 0; p < P; ++p) {
+        size_t q = (size_t)e * P + p;
+        if (f.trainable[q]) {
+          double dxi = 0.0;
+          lp += log_prior_xi(f.pkind[q], f.pa[q], f.pb[q], f.tkind[q], f.ta[q], f.tb[q], st.x[kk], f.theta[q], &dxi);
+          ++kk;
         }
       }
-      f.lml[e] = -st.f - lp;
     }
-    f.n_evals[e] = st.nfev;
-    f.n_iters[e] = st.iter;
-    int status = GPSAT_STATUS_OK;
-    if (rc == LBFGS_STOP_MAXITER || rc == LBFGS_STOP_MAXFUN) status = GPSAT_STATUS_MAXITER;
-    else if (rc == LBFGS_ABNORMAL) status = GPSAT_STATUS_LINESEARCH;
-    else if (rc == LBFGS_NOT_FINITE) status = GPSAT_STATUS_NOT_PD;
-    f.status[e] = status;
+    f.lml[e] = -st.f - lp;
+  }
+  f.n_evals[e] = st.nfev;
+  f.n_iters[e] = st.iter;
+  int status = GPSAT_STATUS_OK;
+  if (rc == LBFGS_STOP_MAXITER || rc == LBFGS_STOP_MAXFUN) status = GPSAT_STATUS_MAXITER;
+  else if (rc == LBFGS_ABNORMAL) status = GPSAT_STATUS_LINESEARCH;
+  else if (rc == LBFGS_NOT_FINITE) status = GPSAT_STATUS_NOT_PD;
+  f.status[e] = status;
+  return rc;
+}
+
+// One optimiser step for every occupied slot (one thread per slot).
+__global__ void lbfgs_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, FitDev f, int S, int ld) {
+  int s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= S) return;
+  SlotDesc& d = slots[s];
+  if (d.expert < 0) return;
+  const int P = b.P;
+  LbfgsState& st = f.states[s];
+  int e = d.expert;
+  double theta[GPSAT_PMAX], gtheta[GPSAT_PMAX];
+  fit_theta_trial(f, st, e, P, theta);
+  double lml = slot_finish_eval(d, theta, gtheta, true);
+  int rc = fit_advance(f, st, e, P, lml, theta, gtheta);
+  if (rc != LBFGS_CONTINUE) {
     int idx = atomicAdd(&f.counters[0], 1);
     if (idx < b.E) fit_begin_expert(d, mems[s], st, b, f, b.order[idx], ld);
     else d.expert = -1;
   } else {
-    int k = 0;
-    for (int p = 0; p < P; ++p) {
-      size_t q = (size_t)e * P + p;
-      theta[p] = f.trainable[q] ? transform_fwd(f.tkind[q], f.ta[q], f.tb[q], st.xtrial[k++]) : f.theta[q];
-    }
+    fit_theta_trial(f, st, e, P, theta);
     slot_set_theta(d, theta);
     *d.notpd = 0;
     *d.quad = 0.0;
@@ -352,6 +365,8 @@ __global__ void debug_extract_kernel(const SlotDesc* slots, double* Lout, double
     if (Uout) Uout[idx] = uv;
   }
 }
+
+#include "sgpr_fit.cuh"
 
 }  // namespace gpsat
 

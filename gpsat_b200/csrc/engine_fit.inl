@@ -1,29 +1,10 @@
 // gpsat_gpr_fit and the factor test hook.  Included at the end of engine_api.inl.
-extern "C" {
-
-int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* theta_io, const int32_t* tkind,
-                  const double* ta, const double* tb, const uint8_t* trainable, const gpsat_fit_options* opt_in,
-                  const gpsat_priors* priors, double* objective, double* lml, int32_t* n_evals, int32_t* n_iters,
-                  int32_t* status) {
-  REQUIRE(h != nullptr, "engine is NULL");
-  if (check_batch(batch, false)) return 2;
-  REQUIRE(theta_io && tkind && ta && tb && trainable, "theta / transform argument is NULL");
-  REQUIRE(objective && n_evals && n_iters && status, "output argument is NULL");
-  REQUIRE(!priors || (priors->kind && priors->a && priors->b), "priors has a NULL member");
-  gpsat_fit_options opt;
-  if (opt_in) opt = *opt_in; else gpsat_fit_options_default(&opt);
-  REQUIRE(opt.maxls > 0 && opt.maxiter >= 0 && opt.maxfun >= 0, "bad fit options");
-  Engine& g = h->e;
-  begin_call(g);
-  const int64_t E = batch->E;
-  if (E == 0) return end_call(g);
-  const int P = batch->D + 2;
-  BatchDev bd;
-  if (engine_load_batch(g, batch, mem, false, bd)) return 1;
-  const int S = choose_slots(g, E, g.Tmax, g.Tmax, opt.max_slots);
-  int ld = 0;
-  if (engine_alloc_slots(g, S, g.Tmax, g.Tmax, ld)) return 1;
-
+// Stage the per-expert optimiser inputs on the device (or adopt device pointers) and point the
+// outputs at device memory.  Uses g.bout and g.bstates.
+static int fit_stage(Engine& g, int mem, int64_t E, int P, int S, double* theta_io, const int32_t* tkind,
+                     const double* ta, const double* tb, const uint8_t* trainable, const gpsat_fit_options& opt,
+                     const gpsat_priors* priors, double* objective, double* lml, int32_t* n_evals, int32_t* n_iters,
+                     int32_t* status, FitDev& fd) {
   // per-expert arrays on the device: [theta | ta | tb | pa | pb | lml | obj] doubles,
   // [tkind | pkind | nev | nit | status] ints, trainable bytes, counters
   const size_t EP = (size_t)E * P;
@@ -34,7 +15,6 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   if (g.bout.ensure(o_cnt + 16) || g.bstates.ensure(sizeof(LbfgsState) * S)) return 1;
   char* base = g.bout.as<char>();
   const bool dev = mem == GPSAT_MEM_DEVICE;
-  FitDev fd;
   const void* p = nullptr;
   if (dev) fd.theta = theta_io;
   else {
@@ -61,6 +41,57 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   fd.counters = reinterpret_cast<int*>(base + o_cnt);
   fd.opt = LbfgsOptions{opt.pgtol, opt.ftol, opt.maxiter, opt.maxfun, opt.maxls};
 
+  return 0;
+}
+
+static int fit_fetch(Engine& g, int mem, int64_t E, int P, const FitDev& fd, double* theta_io, double* objective,
+                     double* lml, int32_t* n_evals, int32_t* n_iters, int32_t* status) {
+  const bool dev = mem == GPSAT_MEM_DEVICE;
+  const size_t EP = (size_t)E * P;
+  if (!dev) {
+    CUDA_TRY(cudaMemcpyAsync(theta_io, fd.theta, EP * 8, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(objective, fd.objective, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
+    if (lml) CUDA_TRY(cudaMemcpyAsync(lml, fd.lml, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(n_evals, fd.n_evals, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(n_iters, fd.n_iters, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(status, fd.status, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
+    g.stats.d2h_bytes += (double)EP * 8 + (double)E * (20 + (lml ? 8 : 0));
+  }
+  return 0;
+}
+
+extern "C" {
+
+int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* theta_io, const int32_t* tkind,
+                  const double* ta, const double* tb, const uint8_t* trainable, const gpsat_fit_options* opt_in,
+                  const gpsat_priors* priors, double* objective, double* lml, int32_t* n_evals, int32_t* n_iters,
+                  int32_t* status) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  if (check_batch(batch, false)) return 2;
+  REQUIRE(theta_io && tkind && ta && tb && trainable, "theta / transform argument is NULL");
+  REQUIRE(objective && n_evals && n_iters && status, "output argument is NULL");
+  REQUIRE(!priors || (priors->kind && priors->a && priors->b), "priors has a NULL member");
+  gpsat_fit_options opt;
+  if (opt_in) opt = *opt_in; else gpsat_fit_options_default(&opt);
+  REQUIRE(opt.maxls > 0 && opt.maxiter >= 0 && opt.maxfun >= 0, "bad fit options");
+  Engine& g = h->e;
+  begin_call(g);
+  const int64_t E = batch->E;
+  if (E == 0) return end_call(g);
+  const int P = batch->D + 2;
+  BatchDev bd;
+  if (engine_load_batch(g, batch, mem, false, bd)) return 1;
+  const int S = choose_slots(g, E, g.Tmax, g.Tmax, opt.max_slots);
+  int ld = 0;
+  if (engine_alloc_slots(g, S, g.Tmax, g.Tmax, ld)) return 1;
+
+  FitDev fd;
+  if (fit_stage(g, mem, E, P, S, theta_io, tkind, ta, tb, trainable, opt, priors, objective, lml, n_evals, n_iters,
+                status, fd))
+    return 1;
+  const bool dev = mem == GPSAT_MEM_DEVICE;
+  const size_t EP = (size_t)E * P;
+
   SlotDesc* slots = g.bslots.as<SlotDesc>();
   const SlotMem* mems = g.bmems.as<SlotMem>();
   // counters: [0] next queue position, [1] occupied, [2] max T, [3] evaluations
@@ -85,15 +116,7 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
     g.stats.ticks++;
   }
   g.stats.evals = evals; g.stats.slots = S;
-  if (!dev) {
-    CUDA_TRY(cudaMemcpyAsync(theta_io, fd.theta, EP * 8, cudaMemcpyDeviceToHost, g.stream));
-    CUDA_TRY(cudaMemcpyAsync(objective, fd.objective, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
-    if (lml) CUDA_TRY(cudaMemcpyAsync(lml, fd.lml, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
-    CUDA_TRY(cudaMemcpyAsync(n_evals, fd.n_evals, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
-    CUDA_TRY(cudaMemcpyAsync(n_iters, fd.n_iters, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
-    CUDA_TRY(cudaMemcpyAsync(status, fd.status, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
-    g.stats.d2h_bytes += (double)EP * 8 + (double)E * (20 + (lml ? 8 : 0));
-  }
+  if (fit_fetch(g, mem, E, P, fd, theta_io, objective, lml, n_evals, n_iters, status)) return 1;
   CUDA_TRY(cudaGetLastError());
   if (end_call(g)) return 1;
   // flops: n^3 per evaluation (needs per-expert counts, which are on the host only in HOST mode)

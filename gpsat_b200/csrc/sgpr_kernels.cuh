@@ -1,21 +1,35 @@
 // Sparse GPR (Titsias) on the same tile machinery: the reference's GPflowSGPRModel
-// (GPSat/models/gpflow_models.py:666-901 -> gpflow.models.SGPR.elbo / predict_f).
+// (GPSat/models/gpflow_models.py:666-901 -> gpflow.models.SGPR.elbo / predict_f, Z fixed :896-897).
 //
+// Forward (ELBO):
 //   Kuu = k(Z,Z) + jitter I = L L^T         sweep of the "K slot" (M inducing points as observations)
-//   W   = L^-1                               transpose of U = L^-T produced by the trtri tiles
+//   W   = L^-1, U = W^T                      transpose of the trtri tiles
 //   Ct  = Kuf^T  [n][Mp]                     kuf_build_kernel (column M carries y, see below)
-//   A'  = W Ct^T / sigma  [Mp][npad]         gemm_nt_kernel; row M of A' comes out as y^T / sigma
-//   B'  = A' A'^T (+ I)   [Mp][Mp]           gemm_nt_kernel (split-K) + splitk_reduce_kernel:
+//   A'  = W Ct^T / sigma                     GEMM; row M of A' comes out as y^T / sigma; stored as
+//                                            Aq [Mp][npad] and At [npad][Mp]
+//   B'  = A' A'^T (+ I)   [Mp][Mp]           split-K SYRK + ordered reduce:
 //                                            B'[u][v] = B, B'[M][u] = (A y)_u / sigma, B'[M][M] = y'y / s2
 //   chol(B') with row M riding along         sweep of the "B slot" on the precomputed matrix:
 //                                            log|LB|, c = LB^-1 A y / sigma, quad = c'c
-//   predict: T1 = Kus^T W^T, T2 = T1 WB^T, mean = T2 c, var = k** + |T2_s|^2 - |T1_s|^2
+// Prediction: T1 = Kus^T W^T, T2 = T1 WB^T, mean = T2 c, var = k** + |T2_s|^2 - |T1_s|^2
+//
+// Gradient w.r.t. theta (analytic form of what TensorFlow autodiff gives for -elbo; derivation and
+// the NumPy statement in oracle/sgpr.py:elbo_and_grad).  With WB = LB^-1, UB = WB^T, gamma = UB c,
+// r = y - sigma A^T gamma:
+//   G_C^T = [ (At - At WB^T UB^T) / sigma + r gamma^T / s2 ] U^T        [n][M]
+//   G_K   = 1/2 U [ 2 I - B - B^-1 - gamma gamma^T ] U^T,   B^-1 = UB UB^T
+//   d elbo / d l_d = var / l_d * ( sum G_C gunit sd_d + sum G_K gunit sd_d )
+//   d elbo / d var = sum G_C kunit + sum G_K kunit - n / (2 s2)
+//   d elbo / d s2  = -n / (2 s2) + [ r'r + n var - s2 (tr B - 2 M + tr B^-1) ] / (2 s2^2)
+// G_C and G_K are never written: the GEMM epilogues contract each 128 x 128 tile with the kernel
+// derivatives and keep [D + 1] partial sums per tile.
 #pragma once
 #include "tiles.cuh"
 
 namespace gpsat {
 
 constexpr double SGPR_JITTER = 1e-6;     // gpflow.config.default_jitter()
+constexpr int SGPR_RES_ROWS = 64;        // rows of the residual kernel per CTA
 
 struct SgprDesc {
   int expert;            // -1 = idle
@@ -24,16 +38,92 @@ struct SgprDesc {
   const double* X; const double* y; const double* Z; const double* Xs;
   double inv_ls[GPSAT_DMAX];
   double var, noise;
-  double* Ct;            // [npad][Mp]
-  double* Aq;            // [Mp][npad]
-  double* W;             // [Mp][Mp]  L^-1
-  double* WB;            // [Mp][Mp]  LB^-1
-  double* Bm;            // [Mp][Mp]
+  double* Ct;            // [npad][Mp]   Kuf^T | y        (dead after A'; reused as Ht)
+  double* Aq;            // [Mp][npad]   A'               (dead after the SYRK; reused as Vt)
+  double* At;            // [npad][Mp]   A'^T             (gradient only)
+  double* W;             // [Mp][Mp]     L^-1
+  double* U;             // [Mp][Mp]     L^-T             (gradient only)
+  double* WB;            // [Mp][Mp]     LB^-1
+  double* UB;            // [Mp][Mp]     LB^-T            (gradient only)
+  double* Bm;            // [Mp][Mp]     B' (lower tiles)
+  double* Binv;          // [Mp][Mp]     B^-1 (lower tiles)
+  double* Q;             // [Mp][Mp]     2I - B - B^-1 - gamma gamma^T (full, zero outside [0,M)^2)
+  double* TT;            // [Mp][Mp]     U Q
   double* part;          // [nsplit][Mp][Mp]
+  double* gam;           // [Mp]
+  double* bid;           // [Mp]         diag(B^-1)
+  double* res;           // [npad]       r
+  double* rrp;           // [npad / 64]  partial sums of r'r
+  double* gpc;           // [npad/128 * Mp/128][8] partial gradient sums of the Kuf term
+  double* gpk;           // [(Mp/128)^2][8]        partial gradient sums of the Kuu term
   double* Cts;           // [mpad][Mp]
   double* T1;            // [mpad][Mp]
   double* T2;            // [mpad][Mp]
 };
+
+// Offsets (in doubles) of one slot's workspace; the same for every slot of a call.
+struct SgprLay {
+  size_t ct, aq, at, w, u, wb, ub, bm, binv, q, tt, part, gam, bid, res, rrp, gpc, gpk, cts, t1, t2, ak, ab,
+      side_k, side_b, total, tile_d;
+  int Tmax, lgd;         // tiles per side of the M x M slots; aligned length of logdet[]
+};
+
+struct SgprIn {
+  const int64_t* off_z;  // device copy
+  const double* Z;
+  const double* zero;    // [Mp] zeros: the "observations" of the K slot
+};
+
+__device__ __forceinline__ void sgpr_fill_slot(SlotDesc& s, int expert, int M, int kind, int D, double* A,
+                                               double* side, const SgprLay& L) {
+  s.expert = expert;
+  s.n = M; s.m = 0;
+  s.T = s.TR = (M + 1 + NB - 1) / NB;
+  s.ld = s.T * NB;
+  s.kind = kind; s.D = D;
+  s.A = A;
+  s.Wd = side; s.Ld = side + L.tile_d; s.logdet = side + 2 * L.tile_d;
+  s.quad = s.logdet + L.lgd;
+  s.gpart = nullptr;
+  s.notpd = reinterpret_cast<int*>(s.quad + 2);
+  s.pre = nullptr; s.ldpre = 0;
+  s.Xs = nullptr;
+}
+
+// Bind expert e to a slot: the SGPR descriptor, the K slot (Kuu + jitter I, y = 0) and the B slot.
+__device__ __forceinline__ void sgpr_set_expert(SgprDesc& d, SlotDesc& k, SlotDesc& b, double* base, const SgprLay& L,
+                                                const BatchDev& bd, const SgprIn& in, int e, int with_pred) {
+  d.expert = e;
+  d.n = (int)(bd.off_n[e + 1] - bd.off_n[e]);
+  d.m = (with_pred && bd.off_m) ? (int)(bd.off_m[e + 1] - bd.off_m[e]) : 0;
+  d.M = (int)(in.off_z[e + 1] - in.off_z[e]);
+  d.D = bd.D; d.kind = bd.kind;
+  d.npad = (d.n + NB - 1) / NB * NB;
+  d.mpad = (max(d.m, 1) + NB - 1) / NB * NB;
+  d.Mp = (d.M + 1 + NB - 1) / NB * NB;
+  d.X = bd.X + bd.off_n[e] * bd.D; d.y = bd.y + bd.off_n[e];
+  d.Z = in.Z + in.off_z[e] * bd.D;
+  d.Xs = d.m > 0 ? bd.Xs + bd.off_m[e] * bd.D : nullptr;
+  d.Ct = base + L.ct; d.Aq = base + L.aq; d.At = base + L.at; d.W = base + L.w; d.U = base + L.u;
+  d.WB = base + L.wb; d.UB = base + L.ub; d.Bm = base + L.bm; d.Binv = base + L.binv; d.Q = base + L.q;
+  d.TT = base + L.tt; d.part = base + L.part; d.gam = base + L.gam; d.bid = base + L.bid; d.res = base + L.res;
+  d.rrp = base + L.rrp; d.gpc = base + L.gpc; d.gpk = base + L.gpk; d.Cts = base + L.cts; d.T1 = base + L.t1;
+  d.T2 = base + L.t2;
+  sgpr_fill_slot(k, e, d.M, d.kind, d.D, base + L.ak, base + L.side_k, L);
+  k.X = d.Z; k.y = in.zero;
+  sgpr_fill_slot(b, e, d.M, GPSAT_PRECOMPUTED, 0, base + L.ab, base + L.side_b, L);
+  b.X = nullptr; b.y = d.Bm + (size_t)d.M * d.Mp;
+  b.var = 0.0; b.noise = 0.0;
+  b.pre = d.Bm; b.ldpre = d.Mp;
+}
+
+__device__ __forceinline__ void sgpr_set_theta(SgprDesc& d, SlotDesc& k, SlotDesc& b, const double* theta) {
+  for (int q = 0; q < d.D; ++q) { d.inv_ls[q] = 1.0 / theta[q]; k.inv_ls[q] = d.inv_ls[q]; }
+  d.var = theta[d.D]; d.noise = theta[d.D + 1];
+  k.var = d.var; k.noise = SGPR_JITTER;
+  *k.quad = 0.0; *k.notpd = 0;
+  *b.quad = 0.0; *b.notpd = 0;
+}
 
 // ---- Ct[i][k] = k(x_i, z_k); column M = y_i (train) or 0; zero padding elsewhere ----------------
 template <int KIND>
@@ -80,97 +170,272 @@ __global__ void __launch_bounds__(GPSAT_THREADS) kuf_build_kernel(const SgprDesc
   }
 }
 
-// ---- W = U^T: dense lower-triangular inverse factor of a slot, row-major [Mp][Mp] ---------------
-// Off-diagonal 128-blocks come from the strict upper block triangle of the slot matrix (U), the
-// diagonal blocks from the W_tt side buffer.  which = 0: descs[].W from slots, 1: descs[].WB.
+// ---- W = L^-1 (dense lower, row-major [Mp][Mp]) and optionally U = W^T from a factored slot ------
+// Off-diagonal 128-blocks come from the strict upper block triangle of the slot matrix (which holds
+// U), the diagonal blocks from the W_tt side buffer.  which = 0: descs[].W / U from the K slots,
+// 1: descs[].WB / UB from the B slots.  One CTA owns the 32 x 32 tile W[u0.., k0..] and its mirror
+// U[k0.., u0..].  U is the transpose of the M x M factor inverse only: its columns >= M (the rows of
+// W that belong to the y row and the padding) are zero, so that products over U / UB see exactly
+// L^-T / LB^-T.
 __global__ void __launch_bounds__(256) transpose_w_kernel(const SgprDesc* __restrict__ descs,
-                                                          const SlotDesc* __restrict__ slots, int which) {
+                                                          const SlotDesc* __restrict__ slots, int which, int with_u) {
   const SgprDesc& d = descs[blockIdx.z];
   if (d.expert < 0) return;
   const SlotDesc& s = slots[blockIdx.z];
   const int Mp = d.Mp;
-  const int u0 = blockIdx.y * 32, k0 = blockIdx.x * 32;       // W tile rows u, cols k
+  const int u0 = blockIdx.y * 32, k0 = blockIdx.x * 32;
   if (u0 >= Mp || k0 >= Mp) return;
   double* W = which ? d.WB : d.W;
+  double* U = with_u ? (which ? d.UB : d.U) : nullptr;
   __shared__ double t[32][33];
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;     // 32 x 8
   const int ub = u0 / NB, kb = k0 / NB;
+  const bool ucol = u0 + tx < d.M;
   if (kb > ub) {
-    for (int r = ty; r < 32; r += 8) W[(size_t)(u0 + r) * Mp + k0 + tx] = 0.0;
+    for (int r = ty; r < 32; r += 8) {
+      W[(size_t)(u0 + r) * Mp + k0 + tx] = 0.0;
+      if (U) U[(size_t)(k0 + r) * Mp + u0 + tx] = 0.0;
+    }
     return;
   }
   if (kb == ub) {
     const double* Wd = s.Wd + (size_t)ub * NB * NB;
-    for (int r = ty; r < 32; r += 8) W[(size_t)(u0 + r) * Mp + k0 + tx] = Wd[(size_t)(u0 - ub * NB + r) * NB + (k0 - kb * NB + tx)];
+    for (int r = ty; r < 32; r += 8) {
+      const double v = Wd[(size_t)(u0 - ub * NB + r) * NB + (k0 - kb * NB + tx)];
+      W[(size_t)(u0 + r) * Mp + k0 + tx] = v;
+      t[r][tx] = v;
+    }
+    if (U) {
+      __syncthreads();
+      for (int r = ty; r < 32; r += 8) U[(size_t)(k0 + r) * Mp + u0 + tx] = ucol ? t[tx][r] : 0.0;
+    }
     return;
   }
-  for (int r = ty; r < 32; r += 8) t[r][tx] = s.A[(size_t)(k0 + r) * s.ld + u0 + tx];    // U[k][u]
+  for (int r = ty; r < 32; r += 8) {
+    const double v = s.A[(size_t)(k0 + r) * s.ld + u0 + tx];    // U[k][u]
+    t[r][tx] = v;
+    if (U) U[(size_t)(k0 + r) * Mp + u0 + tx] = ucol ? v : 0.0;
+  }
   __syncthreads();
   for (int r = ty; r < 32; r += 8) W[(size_t)(u0 + r) * Mp + k0 + tx] = t[tx][r];
 }
 
-// ---- batched NT GEMM on 128 x 128 tiles:  out = alpha * Aop Bop^T  (both operands k-contiguous) ----
+// ---- contraction of one 128 x 128 tile of G (in shared memory) with the kernel derivatives -------
+//   part[d] = sum G_rc gunit(r2_rc) sd_d,   part[DMAX] = sum G_rc kunit(r2_rc)
+// rows r < nr carry the scaled coordinates xr, columns c < nc the scaled coordinates xc.
+template <int KIND>
+__device__ __forceinline__ void cross_grad_tile_t(int D, const double* xr, const double* xc, int nr, int nc,
+                                                  const double* Cs, int tid, double* part) {
+  const int c = tid & (NB - 1);
+  ColCoords<0> cc;
+  cc.load(xc, c, D);
+  double pd[GPSAT_DMAX], pk = 0.0;
+#pragma unroll
+  for (int dd = 0; dd < GPSAT_DMAX; ++dd) pd[dd] = 0.0;
+  if (c < nc) {
+#pragma unroll 2
+    for (int r = tid >> 7; r < nr; r += GPSAT_THREADS / NB) {
+      const double gv = Cs[r * LDC + c];
+      double sd[GPSAT_DMAX], r2 = 0.0;
+#pragma unroll
+      for (int dd = 0; dd < GPSAT_DMAX; ++dd) {
+        const double t = dd < D ? xr[dd * NB + r] - cc.x[dd] : 0.0;
+        sd[dd] = t * t;
+        r2 += sd[dd];
+      }
+      double ku, gu;
+      kunit_gunit_of_r2<KIND>(r2, ku, gu);
+      const double wg = gv * gu;
+#pragma unroll
+      for (int dd = 0; dd < GPSAT_DMAX; ++dd) pd[dd] = fma(wg, sd[dd], pd[dd]);
+      pk = fma(gv, ku, pk);
+    }
+  }
+#pragma unroll
+  for (int dd = 0; dd < GPSAT_DMAX; ++dd) part[dd] = pd[dd];
+  part[GPSAT_DMAX] = pk;
+  part[GPSAT_DMAX + 1] = 0.0;
+}
+
+__device__ __noinline__ void cross_grad_tile(int kind, int D, const double* xr, const double* xc, int nr, int nc,
+                                             const double* Cs, int tid, double* part) {
+  switch (kind) {
+    case GPSAT_MATERN12: cross_grad_tile_t<GPSAT_MATERN12>(D, xr, xc, nr, nc, Cs, tid, part); break;
+    case GPSAT_MATERN32: cross_grad_tile_t<GPSAT_MATERN32>(D, xr, xc, nr, nc, Cs, tid, part); break;
+    case GPSAT_MATERN52: cross_grad_tile_t<GPSAT_MATERN52>(D, xr, xc, nr, nc, Cs, tid, part); break;
+    default: cross_grad_tile_t<GPSAT_RBF>(D, xr, xc, nr, nc, Cs, tid, part); break;
+  }
+}
+
+// scaled coordinates of rows [g0, g0 + 128) of a point set with np valid rows -> xs[dim][row]
+__device__ __forceinline__ void load_scaled_coords(const double* P, int np, int D, const double* inv_ls, int g0,
+                                                   double* xs, int tid) {
+  for (int idx = tid; idx < NB * D; idx += GPSAT_THREADS) {
+    const int row = idx / D, dd = idx - row * D;
+    xs[dd * NB + row] = (g0 + row < np) ? P[(size_t)(g0 + row) * D + dd] * inv_ls[dd] : 0.0;
+  }
+}
+
+// ---- batched NT GEMM on 128 x 128 tiles:  out = Aop Bop^T  (both operands k-contiguous) ----------
 enum SgprGemmMode : int {
-  SGPR_GEMM_A = 0,     // Aq[Mp][npad]  = W  Ct^T / sigma        (W lower triangular: k <= row tile)
-  SGPR_GEMM_SYRK = 1,  // part[split]   = Aq Aq^T over one k range, lower tiles
-  SGPR_GEMM_T1 = 2,    // T1[mpad][Mp]  = Cts W^T                 (k <= column tile)
-  SGPR_GEMM_T2 = 3     // T2[mpad][Mp]  = T1  WB^T                (k <= column tile)
+  SGPR_GEMM_A = 0,     // Aq[Mp][npad] (and At) = W Ct^T / sigma     (W lower triangular: k <= row tile)
+  SGPR_GEMM_SYRK = 1,  // part[split] = Aq Aq^T over one k range, lower tiles
+  SGPR_GEMM_T1 = 2,    // T1[mpad][Mp] = Cts W^T                      (k <= column tile)
+  SGPR_GEMM_T2 = 3,    // T2[mpad][Mp] = T1 WB^T                      (k <= column tile)
+  SGPR_GEMM_V = 4,     // Vt[npad][Mp] = At WB^T                      (k <= column tile)
+  SGPR_GEMM_H = 5,     // Ht[npad][Mp] = (At - Vt UB^T) / sigma + r gamma^T / s2     (k >= column tile)
+  SGPR_GEMM_GC = 6,    // G_C^T tile = Ht U^T, contracted with dKuf/dtheta -> gpc     (k >= column tile)
+  SGPR_GEMM_BINV = 7,  // Binv = UB UB^T, lower tiles                 (k >= row tile)
+  SGPR_GEMM_TT = 8,    // TT = U Q                                    (k >= row tile)
+  SGPR_GEMM_GK = 9     // G_K tile = 1/2 U TT^T, contracted with dKuu/dtheta -> gpk   (k >= row tile)
 };
-constexpr int SGPR_GEMM_SMEM_BYTES = NSTAGE * STAGE_D * 8;
+constexpr int SGPR_GEMM_SMEM_BYTES = (SM_TILE_D + 2 * NB * GPSAT_DMAX + 64) * 8;
+
+__device__ __forceinline__ void tri_tile(int tile, int& rt, int& ct) {
+  rt = (int)((sqrtf(8.0f * tile + 1.0f) - 1.0f) * 0.5f);
+  while (rt * (rt + 1) / 2 > tile) --rt;
+  while ((rt + 1) * (rt + 2) / 2 <= tile) ++rt;
+  ct = tile - rt * (rt + 1) / 2;
+}
 
 __global__ void __launch_bounds__(GPSAT_THREADS, 1)
-sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit) {
+sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit, int with_t) {
   const SgprDesc& d = descs[blockIdx.y];
   if (d.expert < 0) return;
   const int tile = blockIdx.x / nsplit, split = blockIdx.x - tile * nsplit;
   const int Mp = d.Mp, MT = Mp / NB;
   const double *Aop, *Bop;
-  double* out;
-  int ldg, ldo, rt, ct, kbeg = 0, kend;
-  double alpha = 1.0;
-  if (mode == SGPR_GEMM_A) {
-    const int nct = d.npad / NB;
-    if (tile >= MT * nct) return;
-    rt = tile / nct; ct = tile - rt * nct;
-    Aop = d.W; Bop = d.Ct; ldg = Mp; out = d.Aq; ldo = d.npad;
-    kend = (rt + 1) * NB;
-    alpha = rsqrt(d.noise);
-  } else if (mode == SGPR_GEMM_SYRK) {
-    if (tile >= MT * (MT + 1) / 2) return;
-    rt = (int)((sqrtf(8.0f * tile + 1.0f) - 1.0f) * 0.5f);
-    while (rt * (rt + 1) / 2 > tile) --rt;
-    while ((rt + 1) * (rt + 2) / 2 <= tile) ++rt;
-    ct = tile - rt * (rt + 1) / 2;
-    Aop = d.Aq; Bop = d.Aq; ldg = d.npad; out = d.part + (size_t)split * Mp * Mp; ldo = Mp;
-    const int nslab = d.npad / KC, per = (nslab + nsplit - 1) / nsplit;
-    kbeg = split * per * KC;
-    kend = min(d.npad, (split + 1) * per * KC);
-    if (kend < kbeg) kend = kbeg;
-  } else {
-    const int nrt = d.mpad / NB;
-    if (tile >= nrt * MT) return;
-    rt = tile / MT; ct = tile - rt * MT;
-    Aop = (mode == SGPR_GEMM_T1) ? d.Cts : d.T1;
-    Bop = (mode == SGPR_GEMM_T1) ? d.W : d.WB;
-    ldg = Mp; out = (mode == SGPR_GEMM_T1) ? d.T1 : d.T2; ldo = Mp;
-    kend = (ct + 1) * NB;
+  double* out = nullptr;
+  int ldg, ldo = Mp, rt, ct, kbeg = 0, kend = Mp;
+  switch (mode) {
+    case SGPR_GEMM_A: {
+      const int nct = d.npad / NB;
+      if (tile >= MT * nct) return;
+      rt = tile / nct; ct = tile - rt * nct;
+      Aop = d.W; Bop = d.Ct; ldg = Mp; out = d.Aq; ldo = d.npad;
+      kend = (rt + 1) * NB;
+      break;
+    }
+    case SGPR_GEMM_SYRK: {
+      if (tile >= MT * (MT + 1) / 2) return;
+      tri_tile(tile, rt, ct);
+      Aop = d.Aq; Bop = d.Aq; ldg = d.npad; out = d.part + (size_t)split * Mp * Mp;
+      const int nslab = d.npad / KC, per = (nslab + nsplit - 1) / nsplit;
+      kbeg = min(d.npad, split * per * KC);
+      kend = min(d.npad, (split + 1) * per * KC);
+      break;
+    }
+    case SGPR_GEMM_T1: case SGPR_GEMM_T2: case SGPR_GEMM_V: case SGPR_GEMM_H: case SGPR_GEMM_GC: {
+      const int nrt = ((mode == SGPR_GEMM_T1 || mode == SGPR_GEMM_T2) ? d.mpad : d.npad) / NB;
+      if (tile >= nrt * MT) return;
+      rt = tile / MT; ct = tile - rt * MT;
+      ldg = Mp;
+      if (mode == SGPR_GEMM_T1) { Aop = d.Cts; Bop = d.W; out = d.T1; kend = (ct + 1) * NB; }
+      else if (mode == SGPR_GEMM_T2) { Aop = d.T1; Bop = d.WB; out = d.T2; kend = (ct + 1) * NB; }
+      else if (mode == SGPR_GEMM_V) { Aop = d.At; Bop = d.WB; out = d.Aq; kend = (ct + 1) * NB; }
+      else if (mode == SGPR_GEMM_H) { Aop = d.Aq; Bop = d.UB; out = d.Ct; kbeg = ct * NB; }
+      else { Aop = d.Ct; Bop = d.U; kbeg = ct * NB; }
+      break;
+    }
+    case SGPR_GEMM_BINV: {
+      if (tile >= MT * (MT + 1) / 2) return;
+      tri_tile(tile, rt, ct);
+      Aop = d.UB; Bop = d.UB; ldg = Mp; out = d.Binv; kbeg = rt * NB;
+      break;
+    }
+    default: {
+      if (tile >= MT * MT) return;
+      rt = tile / MT; ct = tile - rt * MT;
+      ldg = Mp; kbeg = rt * NB;
+      Aop = d.U;
+      if (mode == SGPR_GEMM_TT) { Bop = d.Q; out = d.TT; }
+      else Bop = d.TT;
+      break;
+    }
   }
   extern __shared__ double smem[];
+  double* Cs = smem;                       // aliases the pipeline stages
+  double* xr = smem + SM_TILE_D;
+  double* xc = xr + NB * GPSAT_DMAX;
+  double* red = xc + NB * GPSAT_DMAX;
   const int tid = threadIdx.x;
   Acc acc;
   acc_zero(acc);
   const double* Ag = Aop + (size_t)rt * NB * ldg;
   const double* Bg = Bop + (size_t)ct * NB * ldg;
   gemm_nt_prologue(Ag, Bg, ldg, kbeg, kend, smem, tid);
+  if (mode == SGPR_GEMM_GC) {
+    load_scaled_coords(d.X, d.n, d.D, d.inv_ls, rt * NB, xr, tid);
+    load_scaled_coords(d.Z, d.M, d.D, d.inv_ls, ct * NB, xc, tid);
+  } else if (mode == SGPR_GEMM_GK) {
+    load_scaled_coords(d.Z, d.M, d.D, d.inv_ls, rt * NB, xr, tid);
+    load_scaled_coords(d.Z, d.M, d.D, d.inv_ls, ct * NB, xc, tid);
+  }
   gemm_nt_mainloop(acc, Ag, Bg, ldg, kbeg, kend, smem, tid);
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3, lr = lane >> 2, lk = lane & 3;
-  double* Og = out + ((size_t)rt * NB + wm * 64 + lr) * ldo + (size_t)ct * NB + wn * 32 + 2 * lk;
+
+  if (mode == SGPR_GEMM_GC || mode == SGPR_GEMM_GK) {
+    // ---- contraction epilogue: the tile of G never leaves the SM ----
+    acc_to_smem(acc, Cs, tid, mode == SGPR_GEMM_GK ? 0.5 : 1.0);
+    __syncthreads();
+    const int nr = min(NB, max(0, (mode == SGPR_GEMM_GC ? d.n : d.M) - rt * NB));
+    const int nc = min(NB, max(0, d.M - ct * NB));
+    double part[GPSAT_DMAX + 2];
+    cross_grad_tile(d.kind, d.D, xr, xc, nr, nc, Cs, tid, part);
+#pragma unroll
+    for (int p = 0; p < GPSAT_DMAX + 2; ++p) {
+      double v = part[p];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) red[warp * 8 + p] = v;
+    }
+    __syncthreads();
+    if (tid < GPSAT_DMAX + 2) {
+      double v = 0.0;
+      for (int w8 = 0; w8 < 8; ++w8) v += red[w8 * 8 + tid];
+      double* gp = (mode == SGPR_GEMM_GC) ? d.gpc : d.gpk;
+      gp[(size_t)(rt * MT + ct) * (GPSAT_DMAX + 2) + tid] = v;
+    }
+    return;
+  }
+
+  const int row0 = rt * NB + wm * 64 + lr, col0 = ct * NB + wn * 32 + 2 * lk;
+  if (mode == SGPR_GEMM_H) {
+    const double isig = rsqrt(d.noise), is2 = 1.0 / d.noise;
+#pragma unroll
+    for (int fm = 0; fm < 8; ++fm) {
+      const int row = row0 + fm * 8;
+      const double rv = d.res[row] * is2;
+#pragma unroll
+      for (int fn = 0; fn < 4; ++fn) {
+        const int col = col0 + fn * 8;
+        const double2 a = *reinterpret_cast<const double2*>(d.At + (size_t)row * Mp + col);
+        double2 o;
+        o.x = col < d.M ? (a.x - acc.c[fm][fn][0]) * isig + rv * d.gam[col] : 0.0;
+        o.y = col + 1 < d.M ? (a.y - acc.c[fm][fn][1]) * isig + rv * d.gam[col + 1] : 0.0;
+        *reinterpret_cast<double2*>(out + (size_t)row * Mp + col) = o;
+      }
+    }
+    return;
+  }
+  const double alpha = (mode == SGPR_GEMM_A) ? rsqrt(d.noise) : 1.0;
 #pragma unroll
   for (int fm = 0; fm < 8; ++fm)
 #pragma unroll
     for (int fn = 0; fn < 4; ++fn)
-      *reinterpret_cast<double2*>(Og + (size_t)fm * 8 * ldo + fn * 8) =
+      *reinterpret_cast<double2*>(out + (size_t)(row0 + fm * 8) * ldo + col0 + fn * 8) =
           make_double2(alpha * acc.c[fm][fn][0], alpha * acc.c[fm][fn][1]);
+  if (mode == SGPR_GEMM_A && with_t) {
+    // transposed copy At[i][u]: lanes with equal lk write 8 consecutive doubles
+#pragma unroll
+    for (int fm = 0; fm < 8; ++fm)
+#pragma unroll
+      for (int fn = 0; fn < 4; ++fn) {
+        double* o = d.At + (size_t)(col0 + fn * 8) * Mp + row0 + fm * 8;
+        o[0] = alpha * acc.c[fm][fn][0];
+        o[Mp] = alpha * acc.c[fm][fn][1];
+      }
+  }
 }
 
 // Bm = sum of the split-K partials in a fixed order (+ I on the first M diagonal entries), lower tiles.
@@ -189,37 +454,122 @@ __global__ void __launch_bounds__(256) sgpr_reduce_kernel(const SgprDesc* __rest
   }
 }
 
-__global__ void sgpr_reset_kernel(const SlotDesc* __restrict__ slots, int S2) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= S2 || slots[s].expert < 0) return;
-  *slots[s].quad = 0.0;
-  *slots[s].notpd = 0;
+// entry k < M of c = LB^-1 A y / sigma: row M of the factored B slot
+__device__ __forceinline__ double sgpr_c_entry(const SlotDesc& sb, int M, int k) {
+  const int c0 = (sb.T - 1) * NB;
+  return (k >= c0) ? sb.Ld[(size_t)(sb.T - 1) * NB * NB + (size_t)(M - c0) * NB + (k - c0)]
+                   : sb.A[(size_t)M * sb.ld + k];
 }
 
-// elbo[e] from the by-products of the B sweep (gpflow.models.SGPR.elbo).
-__global__ void sgpr_finish_kernel(const SgprDesc* __restrict__ descs, const SlotDesc* __restrict__ slotsK,
-                                   const SlotDesc* __restrict__ slotsB, double* __restrict__ elbo,
-                                   int* __restrict__ status, int S) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s >= S) return;
-  const SgprDesc& d = descs[s];
+// One warp per row u < Mp: gamma_u = <UB_u, c>, bid_u = |UB_u|^2 = (B^-1)_uu  (0 for u >= M).
+__global__ void __launch_bounds__(256) sgpr_gamma_kernel(const SgprDesc* __restrict__ descs,
+                                                         const SlotDesc* __restrict__ slotsB) {
+  const SgprDesc& d = descs[blockIdx.y];
   if (d.expert < 0) return;
-  const SlotDesc& sb = slotsB[s];
+  const SlotDesc& sb = slotsB[blockIdx.y];
+  const int u = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (u >= d.Mp) return;
+  double s1 = 0.0, s2 = 0.0;
+  if (u < d.M) {
+    const double* row = d.UB + (size_t)u * d.Mp;
+    for (int k = u - (u & 31) + lane; k < d.M; k += 32) {
+      if (k < u) continue;
+      const double v = row[k];
+      s1 = fma(v, sgpr_c_entry(sb, d.M, k), s1);
+      s2 = fma(v, v, s2);
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s1 += __shfl_xor_sync(0xffffffffu, s1, o);
+    s2 += __shfl_xor_sync(0xffffffffu, s2, o);
+  }
+  if (lane == 0) { d.gam[u] = s1; d.bid[u] = s2; }
+}
+
+// r_i = y_i - sigma <At_i, gamma> (0 for i >= n); one warp per row, 64 rows per CTA, and the CTA's
+// share of r'r in a fixed order.
+__global__ void __launch_bounds__(256) sgpr_resid_kernel(const SgprDesc* __restrict__ descs) {
+  const SgprDesc& d = descs[blockIdx.y];
+  if (d.expert < 0) return;
+  const int i0 = blockIdx.x * SGPR_RES_ROWS;
+  if (i0 >= d.npad) return;
+  __shared__ double rs[SGPR_RES_ROWS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const double sigma = sqrt(d.noise);
+  for (int q = 0; q < SGPR_RES_ROWS / 8; ++q) {
+    const int i = i0 + warp * (SGPR_RES_ROWS / 8) + q;
+    double s = 0.0;
+    if (i < d.n) {
+      const double* row = d.At + (size_t)i * d.Mp;
+      for (int k = lane; k < d.M; k += 32) s = fma(row[k], d.gam[k], s);
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    if (lane == 0) {
+      const double r = (i < d.n) ? d.y[i] - sigma * s : 0.0;
+      d.res[i] = r;
+      rs[i - i0] = r * r;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double v = 0.0;
+    for (int q = 0; q < SGPR_RES_ROWS; ++q) v += rs[q];
+    d.rrp[blockIdx.x] = v;
+  }
+}
+
+// Q = 2 I - B - B^-1 - gamma gamma^T on [0, M)^2 (both triangles), zero elsewhere.
+__global__ void __launch_bounds__(256) sgpr_q_kernel(const SgprDesc* __restrict__ descs) {
+  const SgprDesc& d = descs[blockIdx.y];
+  if (d.expert < 0) return;
+  const int Mp = d.Mp, M = d.M;
+  const size_t total = (size_t)Mp * Mp;
+  for (size_t idx = blockIdx.x * (size_t)blockDim.x + threadIdx.x; idx < total; idx += (size_t)gridDim.x * blockDim.x) {
+    const int r = (int)(idx / Mp), c = (int)(idx - (size_t)r * Mp);
+    double v = 0.0;
+    if (r < M && c < M) {
+      const size_t lo = (r >= c) ? idx : (size_t)c * Mp + r;
+      v = (r == c ? 2.0 : 0.0) - d.Bm[lo] - d.Binv[lo] - d.gam[r] * d.gam[c];
+    }
+    d.Q[idx] = v;
+  }
+}
+
+// elbo (gpflow.models.SGPR.elbo) and, with_grad, d elbo / d theta from the by-products of one
+// evaluation; every sum runs in a fixed order.  Returns -inf when a factorisation failed.
+__device__ __forceinline__ double sgpr_finish_eval(const SgprDesc& d, const SlotDesc& sk, const SlotDesc& sb,
+                                                   double* gtheta, bool with_grad) {
   double logdet = 0.0;
   for (int t = 0; t < sb.T; ++t) logdet += sb.logdet[t];
   double trB = 0.0;
   for (int u = 0; u < d.M; ++u) trB += d.Bm[(size_t)u * d.Mp + u];
   const double yy = d.Bm[(size_t)d.M * d.Mp + d.M];          // y'y / s2
-  const double n = (double)d.n;
-  double v = -0.5 * n * 1.8378770664093453 - logdet - 0.5 * n * log(d.noise) - 0.5 * yy + 0.5 * (*sb.quad) -
-             0.5 * n * d.var / d.noise + 0.5 * (trB - (double)d.M);
-  const bool bad = *slotsK[s].notpd || *sb.notpd;
-  elbo[d.expert] = bad ? -INFINITY : v;
-  if (status) status[d.expert] = bad ? 1 : 0;
+  const double n = (double)d.n, s2 = d.noise;
+  double v = -0.5 * n * 1.8378770664093453 - logdet - 0.5 * n * log(s2) - 0.5 * yy + 0.5 * (*sb.quad) -
+             0.5 * n * d.var / s2 + 0.5 * (trB - (double)d.M);
+  const bool bad = *sk.notpd || *sb.notpd;
+  if (with_grad) {
+    const int MT = d.Mp / NB, ntc = (d.npad / NB) * MT, ntk = MT * MT;
+    double s[GPSAT_DMAX + 2];
+    for (int p = 0; p < GPSAT_DMAX + 2; ++p) s[p] = 0.0;
+    for (int t = 0; t < ntc; ++t)
+      for (int p = 0; p <= GPSAT_DMAX; ++p) s[p] += d.gpc[(size_t)t * (GPSAT_DMAX + 2) + p];
+    for (int t = 0; t < ntk; ++t)
+      for (int p = 0; p <= GPSAT_DMAX; ++p) s[p] += d.gpk[(size_t)t * (GPSAT_DMAX + 2) + p];
+    double rr = 0.0, trBinv = 0.0;
+    for (int q = 0; q < d.npad / SGPR_RES_ROWS; ++q) rr += d.rrp[q];
+    for (int u = 0; u < d.M; ++u) trBinv += d.bid[u];
+    for (int k = 0; k < d.D; ++k) gtheta[k] = d.var * s[k] * d.inv_ls[k];
+    gtheta[d.D] = s[GPSAT_DMAX] - 0.5 * n / s2;
+    gtheta[d.D + 1] = -0.5 * n / s2 + 0.5 * (rr + n * d.var - s2 * (trB - 2.0 * d.M + trBinv)) / (s2 * s2);
+  }
+  return bad ? -INFINITY : v;
 }
 
-// One warp per prediction point s: mean = <T2_s, c>, var = var_f + |T2_s|^2 - |T1_s|^2, c = row M of
-// the factored B slot (SGPR.predict_f, full_cov = False; y_var adds the likelihood variance).
+// One warp per prediction point s: mean = <T2_s, c>, var = var_f + |T2_s|^2 - |T1_s|^2
+// (SGPR.predict_f, full_cov = False; y_var adds the likelihood variance).
 __global__ void sgpr_predict_reduce_kernel(const SgprDesc* __restrict__ descs, const SlotDesc* __restrict__ slotsB,
                                            const int64_t* __restrict__ off_m, double* __restrict__ fmean,
                                            double* __restrict__ fvar, double* __restrict__ yvar) {
@@ -230,12 +580,10 @@ __global__ void sgpr_predict_reduce_kernel(const SgprDesc* __restrict__ descs, c
   if (warp >= d.m) return;
   const double* t1 = d.T1 + (size_t)warp * d.Mp;
   const double* t2 = d.T2 + (size_t)warp * d.Mp;
-  const int M = d.M, c0 = (sb.T - 1) * NB;
-  const double* crow = sb.A + (size_t)M * sb.ld;
-  const double* clast = sb.Ld + (size_t)(sb.T - 1) * NB * NB + (size_t)(M - c0) * NB;
+  const int M = d.M;
   double s1 = 0.0, s2 = 0.0, s3 = 0.0;
   for (int k = lane; k < M; k += 32) {
-    const double cv = (k >= c0) ? clast[k - c0] : crow[k];
+    const double cv = sgpr_c_entry(sb, M, k);
     const double a = t2[k], b = t1[k];
     s1 = fma(a, cv, s1); s2 = fma(a, a, s2); s3 = fma(b, b, s3);
   }

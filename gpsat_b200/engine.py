@@ -210,8 +210,10 @@ class Engine:
 
     def fit(self, batch: RaggedBatch, theta0, tkind, ta, tb, trainable, *, max_iter: int = 10_000,
             pgtol: float = 1e-5, ftol: float = SCIPY_FTOL, maxfun: int = 15_000, maxls: int = 20,
-            max_slots: int = 0, priors=None) -> FitResult:
-        """Batched L-BFGS fit.  ``priors``: optional ``(kind[E,P], a[E,P], b[E,P])`` (GPSAT_PRIOR_*)."""
+            max_slots: int = 0, priors=None, inducing=None) -> FitResult:
+        """Batched L-BFGS fit.  ``priors``: optional ``(kind[E,P], a[E,P], b[E,P])`` (GPSAT_PRIOR_*).
+        ``inducing``: one [M_e, D] array per expert switches to the sparse model (``gpsat_sgpr_fit``:
+        minimises -elbo with the inducing points fixed; ``FitResult.lml`` then holds the ELBO)."""
         E, P = batch.E, batch.D + 2
         mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
         th = self._in(batch, theta0, np.float64, (E, P))
@@ -233,9 +235,13 @@ class Engine:
         opt = _lib.FitOptions(pgtol, ftol, int(max_iter), int(maxfun), int(maxls), int(max_slots))
         cb = batch._c(False)
         self._pre(batch)
-        _lib.check(self._lib.gpsat_gpr_fit(self._h, C.byref(cb), mem, _ptr(th), _ptr(tk), _ptr(a), _ptr(b), _ptr(tr),
-                                           C.byref(opt), C.byref(pri) if pri is not None else None, _ptr(obj),
-                                           _ptr(lml), _ptr(nev), _ptr(nit), _ptr(status)))
+        tail = (_ptr(th), _ptr(tk), _ptr(a), _ptr(b), _ptr(tr), C.byref(opt),
+                C.byref(pri) if pri is not None else None, _ptr(obj), _ptr(lml), _ptr(nev), _ptr(nit), _ptr(status))
+        if inducing is None:
+            _lib.check(self._lib.gpsat_gpr_fit(self._h, C.byref(cb), mem, *tail))
+        else:
+            off_z, Zp = self._inducing(batch, inducing)
+            _lib.check(self._lib.gpsat_sgpr_fit(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, *tail))
         return FitResult(th, obj, lml, nev, nit, status)
 
     def predict(self, batch: RaggedBatch, theta):
@@ -284,19 +290,21 @@ class Engine:
         Zp = np.ascontiguousarray(np.concatenate(Zl, axis=0)) if Zl else np.zeros((0, batch.D))
         return off_z, self._in(batch, Zp, np.float64, Zp.shape)
 
-    def sgpr_elbo(self, batch: RaggedBatch, Z, theta):
-        """ELBO of ``gpflow.models.SGPR`` per expert at fixed theta.  Returns (elbo, status)."""
+    def sgpr_elbo(self, batch: RaggedBatch, Z, theta, with_grad: bool = False):
+        """ELBO of ``gpflow.models.SGPR`` per expert at fixed theta (and, ``with_grad``, its gradient
+        w.r.t. theta with Z fixed).  Returns (elbo, grad or None, status)."""
         E, P = batch.E, batch.D + 2
         mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
         off_z, Zp = self._inducing(batch, Z)
         th = self._in(batch, theta, np.float64, (E, P))
         elbo = self._empty(batch, (E,), np.float64)
+        grad = self._empty(batch, (E, P), np.float64) if with_grad else None
         status = self._empty(batch, (E,), np.int32)
         cb = batch._c(False)
         self._pre(batch)
         _lib.check(self._lib.gpsat_sgpr_elbo(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, _ptr(th), _ptr(elbo),
-                                             _ptr(status)))
-        return elbo, status
+                                             _ptr(grad), _ptr(status)))
+        return elbo, grad, status
 
     def sgpr_predict(self, batch: RaggedBatch, Z, theta):
         """``SGPR.predict_f`` / ``predict_y`` (full_cov=False) per expert at fixed theta."""

@@ -273,6 +273,10 @@ class B200GPRModel(BaseGPRModel):
     def engine(self) -> Engine:
         return get_engine(self.device)
 
+    def _inducing_list(self):
+        """``None`` for the exact model; the sparse subclass returns ``[Z]``."""
+        return None
+
     def update_obs_data(self, data=None, coords_col=None, obs_col=None, coords=None, obs=None, coords_scale=None,
                         obs_scale=None):
         """Swap the training data, keeping hyper-parameters (``gpflow_models.py:159-176``)."""
@@ -366,7 +370,7 @@ class B200GPRModel(BaseGPRModel):
             kw = {"ftol": float(tol), "pgtol": float(tol)}
         res = self.engine.fit(self._batch(), self._theta[None, :], self._tkind[None, :], self._ta[None, :],
                               self._tb[None, :], self._trainable[None, :].astype(np.uint8), max_iter=int(max_iter),
-                              priors=self._prior_arrays(1), **kw)
+                              priors=self._prior_arrays(1), inducing=self._inducing_list(), **kw)
         status = int(res.status[0])
         self.opt_info = {"status": status, "n_evals": int(res.n_evals[0]), "n_iters": int(res.n_iters[0]),
                          "objective": float(res.objective[0])}
@@ -510,10 +514,77 @@ class B200GPRModel(BaseGPRModel):
         return (np.tile(self._pkind, (E, 1)), np.tile(self._pa, (E, 1)), np.tile(self._pb, (E, 1)))
 
 
+class B200SGPRModel(B200GPRModel):
+    """Sparse GP regression (Titsias 2009) with fixed inducing points, mirroring ``GPflowSGPRModel``
+    (``gpflow_models.py:666-901``): the ``num_inducing_points`` (default 500) inducing points are
+    the first rows of a shuffled copy of the scaled training coordinates (``:816-819``; all of them
+    when there are fewer data points, ``:810-814``), the objective value is **+ELBO**
+    (``:860-862``), ``predict`` is the parent's (``predict_f`` / ``predict_y`` of the sparse model)
+    and ``param_names`` gains "inducing_points".  ``optimise_parameters(train_inducing_points=True)``
+    is not implemented: the device optimiser keeps Z fixed, which is the reference's default
+    (``:896-897``).  ``full_cov=True`` is not available for the sparse model.
+    """
+
+    def __init__(self, data=None, coords_col=None, obs_col=None, coords=None, obs=None, coords_scale=None,
+                 obs_scale=None, obs_mean=None, verbose=True, *, kernel="Matern32", num_inducing_points=500,
+                 kernel_kwargs=None, mean_function=None, mean_func_kwargs=None, noise_variance=None,
+                 likelihood=None, device: int = 0, priors: Optional[dict] = None, **kwargs):
+        super().__init__(data=data, coords_col=coords_col, obs_col=obs_col, coords=coords, obs=obs,
+                         coords_scale=coords_scale, obs_scale=obs_scale, obs_mean=obs_mean, verbose=verbose,
+                         kernel=kernel, kernel_kwargs=kernel_kwargs, mean_function=mean_function,
+                         mean_func_kwargs=mean_func_kwargs, noise_variance=noise_variance, likelihood=likelihood,
+                         device=device, priors=priors, **kwargs)
+        assert num_inducing_points is not None, "num_inducing_points is None, must be specified for SGPR"
+        if len(self.coords) < num_inducing_points:
+            print("number of inducing points is more than number of data points, "
+                  "setting inducing points to data points...")
+            self.inducing_points = self.coords
+        else:
+            X = self.coords.copy()
+            np.random.shuffle(X)          # the reference draws from numpy's global generator too
+            self.inducing_points = X[:int(num_inducing_points)]
+
+    def _inducing_list(self):
+        return [np.ascontiguousarray(self.inducing_points, dtype=np.float64)]
+
+    @property
+    def param_names(self) -> list:
+        return super().param_names + ["inducing_points"]
+
+    def get_inducing_points(self) -> np.ndarray:
+        return np.array(self.inducing_points, dtype=np.float64)
+
+    def set_inducing_points(self, inducing_points):
+        Z = np.asarray(inducing_points, dtype=np.float64)
+        assert Z.ndim == 2 and Z.shape[1] == self.D, f"inducing_points must have shape [M, {self.D}]"
+        assert np.all(np.isfinite(Z)), "inducing_points contains non-finite values"
+        self.inducing_points = Z.copy()
+
+    def predict(self, coords, full_cov=False, apply_scale=True) -> Dict[str, np.ndarray]:
+        if full_cov:
+            raise NotImplementedError("full_cov=True is not implemented for the sparse model")
+        Xs = self._prep_pred_coords(coords, apply_scale)
+        out = self.engine.sgpr_predict(self._batch(Xs), self._inducing_list(), self._theta[None, :])
+        if int(out["status"][0]) != _lib.STATUS_OK:
+            raise FloatingPointError("Kuu + jitter * I or B is not positive definite at the current parameters")
+        return {"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"], "f_bar": self._f_bar(len(out["f*"]))}
+
+    def optimise_parameters(self, train_inducing_points=False, max_iter=10_000, fixed_params=None, **opt_kwargs):
+        if train_inducing_points:
+            raise NotImplementedError("train_inducing_points=True is not implemented: the device optimiser keeps "
+                                      "the inducing points fixed (the reference's default)")
+        return super().optimise_parameters(max_iter=max_iter, fixed_params=fixed_params, **opt_kwargs)
+
+    def get_objective_function_value(self):
+        """ELBO at the current parameters (``gpflow_models.py:860-862``; note the sign: not negated)."""
+        elbo, _, _ = self.engine.sgpr_elbo(self._batch(), self._inducing_list(), self._theta[None, :])
+        return float(elbo[0])
+
+
 def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Sequence] = None, *,
                        optimise: bool = True, max_iter: int = 10_000, fixed_params=None, apply_scale: bool = True,
                        **opt_kwargs):
-    """Batched equivalent of the reference loop body (``local_experts.py:1126-1164``) for a list of
+    """Batched equivalent (exact or sparse models) of the reference loop body (``local_experts.py:1126-1164``) for a list of
     model instances that share kernel and input dimension: one ``gpsat_gpr_fit`` call for all
     experts, then one ``gpsat_gpr_predict`` call.  Updates every model's parameters in place and
     returns ``(success[E], objective[E], predictions)`` where ``predictions`` is a list of the
@@ -524,6 +595,10 @@ def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Seq
     m0 = models[0]
     assert all(m.kernel == m0.kernel and m.D == m0.D and m.device == m0.device for m in models), \
         "fit_predict_models needs one kernel / dimension / device per batch"
+    sparse = isinstance(m0, B200SGPRModel)
+    assert all(isinstance(m, B200SGPRModel) == sparse for m in models), \
+        "fit_predict_models needs one model class per batch (partition by model type, local_experts.py:1021-1041)"
+    inducing = [m._inducing_list()[0] for m in models] if sparse else None
     for m in models:
         m._fix_hyperparameters(fixed_params or [])
     Xs_list = None
@@ -543,7 +618,7 @@ def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Seq
                    np.stack([m._pb for m in models]))
         res = eng.fit(batch, theta, np.stack([m._tkind for m in models]), np.stack([m._ta for m in models]),
                       np.stack([m._tb for m in models]), np.stack([m._trainable for m in models]).astype(np.uint8),
-                      max_iter=int(max_iter), priors=pri, **kw)
+                      max_iter=int(max_iter), priors=pri, inducing=inducing, **kw)
         for e, m in enumerate(models):
             st = int(res.status[e])
             m.opt_info = {"status": st, "n_evals": int(res.n_evals[e]), "n_iters": int(res.n_iters[e]),
@@ -554,14 +629,21 @@ def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Seq
         theta = np.stack([m._theta for m in models])
     preds = None
     if Xs_list is not None:
-        out = eng.predict(batch, theta)
-        objective = -np.asarray(out["lml"])
+        if sparse:
+            out = eng.sgpr_predict(batch, inducing, theta)
+            objective = np.asarray(out["elbo"])           # the sparse model reports +ELBO
+        else:
+            out = eng.predict(batch, theta)
+            objective = -np.asarray(out["lml"])
         preds = []
         for e, m in enumerate(models):
             sl = slice(int(batch.off_m[e]), int(batch.off_m[e + 1]))
             preds.append({"f*": out["f*"][sl].copy(), "f*_var": out["f*_var"][sl].copy(),
                           "y_var": out["y_var"][sl].copy(), "f_bar": m._f_bar(sl.stop - sl.start)})
     else:
-        lml, _, _ = eng.lml_grad(batch, theta, with_grad=False)
-        objective = -np.asarray(lml)
+        if sparse:
+            objective = np.asarray(eng.sgpr_elbo(batch, inducing, theta)[0])
+        else:
+            lml, _, _ = eng.lml_grad(batch, theta, with_grad=False)
+            objective = -np.asarray(lml)
     return success, objective, preds

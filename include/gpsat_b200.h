@@ -164,15 +164,25 @@ int gpsat_gpr_predict_cov(gpsat_engine* eng, const gpsat_batch* batch, int mem, 
  *
  * gpsat_sgpr_elbo: elbo[e] = gpflow.models.SGPR.elbo() (jitter 1e-6 on Kuu) — the value behind
  * GPflowSGPRModel.get_objective_function_value (gpflow_models.py:860-862, which reports +elbo).
+ * grad (may be NULL): d elbo / d theta [E][P] in constrained space with Z fixed — the gradient
+ * TensorFlow autodiff hands to gpflow.optimizers.Scipy (gpflow_models.py:317-321 inherited).
  * status[e] = 1 when Kuu + jitter I or B is not positive definite (elbo = -inf). */
 int gpsat_sgpr_elbo(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,
-                    int mem, const double* theta, double* elbo, int32_t* status);
+                    int mem, const double* theta, double* elbo, double* grad, int32_t* status);
 
 /* SGPR.predict_f / predict_y (full_cov = False) at batch->Xs, as GPflowSGPRModel.predict uses them
  * (gpflow_models.py:229-230 inherited); elbo (may be NULL) comes out of the same factorisation. */
 int gpsat_sgpr_predict(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,
                        int mem, const double* theta, double* fmean, double* fvar, double* yvar,
                        double* elbo, int32_t* status);
+
+/* Replaces GPflowSGPRModel.optimise_parameters (gpflow_models.py:290-329 inherited: L-BFGS-B on
+ * training_loss = -elbo, inducing points fixed, :896-897) for all experts.  Arguments as
+ * gpsat_gpr_fit; objective[e] = -(elbo + log prior) at the optimum, elbo[e] (may be NULL) = elbo. */
+int gpsat_sgpr_fit(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,
+                   int mem, double* theta_io, const int32_t* tkind, const double* ta, const double* tb,
+                   const uint8_t* trainable, const gpsat_fit_options* opt, const gpsat_priors* priors,
+                   double* objective, double* elbo, int32_t* n_evals, int32_t* n_iters, int32_t* status);
 
 /* Test hook (single expert, host memory): dense factor of the augmented matrix.
  * Lout [(n+1)*(n+1)] row-major lower: rows < n = chol(K + s2 I), row n = (L^-1 y)^T, 1.

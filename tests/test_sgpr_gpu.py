@@ -40,7 +40,7 @@ def test_elbo_predict_ragged(engine, kind, D):
     theta = np.stack([_theta(rng, D) for _ in experts])
     b = _batch(kind, experts)
     Z = [e[3] for e in experts]
-    elbo, status = engine.sgpr_elbo(b, Z, theta)
+    elbo, _, status = engine.sgpr_elbo(b, Z, theta)
     out = engine.sgpr_predict(b, Z, theta)
     assert np.all(status == 0) and np.all(out["status"] == 0)
     np.testing.assert_array_equal(out["elbo"], elbo)          # same factorisation, same bits
@@ -96,7 +96,7 @@ def test_not_pd_is_per_expert(engine):
     Zbad = np.repeat(bad[3][:1], 30, axis=0)            # 30 identical inducing points, RBF: rank 1 + jitter
     theta = np.array([[1.5, 1.5, 1.0, 0.1], [1.5, 1.5, 1e8, 0.1]])
     b = _batch("RBF", [ok[:3], bad[:3]])
-    elbo, status = engine.sgpr_elbo(b, [ok[3], Zbad], theta)
+    elbo, _, status = engine.sgpr_elbo(b, [ok[3], Zbad], theta)
     assert status[0] == 0 and np.isfinite(elbo[0])
     ref = sgpr.elbo("RBF", ok[0], ok[1], ok[3], theta[0])
     assert abs(elbo[0] - ref) <= RTOL * abs(ref)
@@ -116,3 +116,80 @@ def test_device_memory_batch(engine):
     dev = engine.sgpr_predict(b.to_device("cuda:0"), Z, theta)
     for k in ("f*", "f*_var", "y_var", "elbo"):
         np.testing.assert_array_equal(dev[k].cpu().numpy(), host[k])
+
+
+@pytest.mark.parametrize("kind", gpr.KERNELS)
+@pytest.mark.parametrize("D", [1, 3])
+def test_elbo_gradient_ragged(engine, kind, D):
+    """d elbo / d theta against the oracle's analytic gradient (itself checked by finite differences
+    in tests/test_oracle_golden.py)."""
+    rng = np.random.default_rng(11 * D + len(kind))
+    # many inducing points on a line make Kuu + 1e-6 I ill-conditioned (cond ~ 1e8), and then the
+    # oracle's own gradient moves by 1e-3 under a 1e-15 perturbation of its inputs: keep M small in 1-D
+    shapes = ([(300, 12), (130, 20), (700, 16), (257, 24), (64, 5), (900, 18)] if D == 1 else
+              [(300, 40), (130, 127), (700, 128), (257, 129), (64, 5), (900, 300)])
+    experts = [_expert(rng, n, D, M, 0) for n, M in shapes]
+    theta = np.stack([_theta(rng, D) for _ in experts])
+    b = _batch(kind, experts)
+    Z = [e[3] for e in experts]
+    elbo, grad, status = engine.sgpr_elbo(b, Z, theta, with_grad=True)
+    assert np.all(status == 0)
+    for e, (X, y, _, Ze) in enumerate(experts):
+        v, g = sgpr.elbo_and_grad(kind, X, y, Ze, theta[e])
+        assert abs(elbo[e] - v) <= RTOL * abs(v)
+        # round-off sensitivity of the oracle itself (inputs perturbed in the last bit)
+        _, g2 = sgpr.elbo_and_grad(kind, X * (1 + 1e-15), y, Ze * (1 + 1e-15), theta[e])
+        atol = max(1e-6 * np.abs(g).max(), 100 * np.abs(g - g2).max())
+        assert atol < 1e-3 * np.abs(g).max(), "test case too ill-conditioned to be meaningful"
+        np.testing.assert_allclose(grad[e], g, rtol=1e-6, atol=atol)
+
+
+def test_fit_matches_oracle(engine):
+    """Optimised hyper-parameters and ELBO within 1e-4 of SciPy L-BFGS-B on the oracle's -elbo
+    (the north_star tolerance for optimised quantities), experts of different sizes in one call."""
+    rng = np.random.default_rng(21)
+    D = 2
+    experts = [_expert(rng, n, D, M, 0) for n, M in [(400, 60), (250, 40), (600, 130)]]
+    E, P = len(experts), D + 2
+    tr = gpr.Transform.gpflow_default(D)
+    theta0 = np.tile(np.array([1.0, 1.0, 1.0, 1.0]), (E, 1))
+    b = _batch("Matern32", experts)
+    Z = [e[3] for e in experts]
+    res = engine.fit(b, theta0, np.tile(tr.kind, (E, 1)), np.tile(tr.a, (E, 1)), np.tile(tr.b, (E, 1)),
+                     np.ones((E, P), np.uint8), inducing=Z)
+    assert np.all(res.status == 0)
+    for e, (X, y, _, Ze) in enumerate(experts):
+        th, val, ok, nfev = sgpr.fit("Matern32", X, y, Ze, theta0[e], tr)
+        assert ok
+        assert abs(res.lml[e] - val) <= 1e-4 * abs(val), (res.lml[e], val)
+        np.testing.assert_allclose(res.theta[e], th, rtol=2e-3)
+        assert abs(res.objective[e] + res.lml[e]) < 1e-12 * abs(val)
+
+
+def test_sgpr_model_driver_sequence(engine, golden_dir):
+    """B200SGPRModel through the call order of LocalExpertOI.run (local_experts.py:1043-1164) on the
+    reference's SGPR known-answer case (tests/test_localexperts.py:229-251): lengthscale, ELBO-side
+    prediction within the reference's 1e-4 of the sklearn values."""
+    import os
+    from gpsat_b200.models import B200SGPRModel
+    g = np.load(os.path.join(golden_dir, "kat_localexperts.npz"))
+    eps = float(g["eps"])
+    m = B200SGPRModel(coords=g["x_train"].copy(), obs=g["y_train"].copy(), kernel="Matern32",
+                      num_inducing_points=50, noise_variance=eps ** 2, verbose=False)
+    assert m.param_names == ["lengthscales", "kernel_variance", "likelihood_variance", "inducing_points"]
+    assert m.get_inducing_points().shape == (50, 1)
+    m.set_parameter_constraints({"lengthscales": {"low": float(g["constraint_low"]),
+                                                  "high": float(g["constraint_high"])}},
+                                move_within_tol=True, tol=1e-2)
+    ok = m.optimise_parameters(fixed_params=["kernel_variance", "likelihood_variance"])
+    assert ok
+    assert abs(m.get_lengthscales()[0] - float(g["ls"])) < 1e-4
+    th = np.concatenate([m.get_lengthscales(), [m.get_kernel_variance(), m.get_likelihood_variance()]])
+    ref = sgpr.elbo("Matern32", g["x_train"], g["y_train"][:, 0], m.get_inducing_points(), th)
+    assert abs(m.get_objective_function_value() - ref) < 1e-6 * abs(ref)         # +ELBO, not negated
+    p = m.predict(g["x_test"])
+    assert set(p) == {"f*", "f*_var", "y_var", "f_bar"}
+    assert abs(p["f*"][0] - g["pred_mean"][0]) < 1e-4
+    assert abs(p["f*_var"][0] - g["pred_std"][0] ** 2) < 1e-4
+    with pytest.raises(NotImplementedError):
+        m.optimise_parameters(train_inducing_points=True)
