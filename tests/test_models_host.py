@@ -145,3 +145,34 @@ def test_base_class_requires_get_set():
         def get_objective_function_value(self): ...
     with pytest.raises(AttributeError):
         Broken(coords=np.zeros((3, 1)), obs=np.zeros(3))
+
+
+def test_sgpr_model_inducing_points():
+    """gpflow_models.py:805-819: M random rows of the scaled coordinates (numpy's global generator),
+    or all of them when there are fewer observations; get / set round trip; param_names."""
+    from gpsat_b200.models import B200SGPRModel
+    df = _df(40)
+    np.random.seed(3)
+    m = B200SGPRModel(data=df, obs_col="obs", coords_col=["x", "y", "t"], coords_scale=[5e4, 5e4, 1],
+                      num_inducing_points=10)
+    Z = m.get_inducing_points()
+    assert Z.shape == (10, 3)
+    rows = {tuple(r) for r in m.coords}
+    assert all(tuple(z) in rows for z in Z)                          # a sub-sample of the scaled data
+    np.random.seed(3)
+    expect = m.coords.copy()
+    np.random.shuffle(expect)
+    np.testing.assert_array_equal(Z, expect[:10])                     # same draw as the reference's
+    assert m.param_names == ["lengthscales", "kernel_variance", "likelihood_variance", "inducing_points"]
+    m.set_inducing_points(Z[:4] + 0.5)
+    np.testing.assert_array_equal(m.get_parameters("inducing_points")["inducing_points"], Z[:4] + 0.5)
+    with pytest.raises(AssertionError):
+        m.set_inducing_points(np.zeros((3, 2)))
+    small = B200SGPRModel(data=_df(8), obs_col="obs", coords_col=["x", "y"])        # default M = 500 > n
+    np.testing.assert_array_equal(small.get_inducing_points(), small.coords)
+    with pytest.raises(AssertionError):
+        B200SGPRModel(data=_df(8), obs_col="obs", coords_col=["x", "y"], num_inducing_points=None)
+    with pytest.raises(NotImplementedError):
+        small.optimise_parameters(train_inducing_points=True)
+    with pytest.raises(NotImplementedError):
+        small.predict(np.zeros((1, 2)), full_cov=True)
