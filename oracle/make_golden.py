@@ -12,6 +12,11 @@ Three independent sources pin the oracle (and through it the CUDA path):
 3. ``sklearn_ard.npz`` - scikit-learn ``GaussianProcessRegressor`` LML, gradient and predictions
    for Matern-1/2, 3/2, 5/2 and RBF with ARD lengthscales (same math, independent code).
 
+4. ``vff_features.npz`` - the NumPy-only pieces of the reference's VFF implementation
+   (``/root/reference/GPSat/vff.py:518-559``: ``make_Kuf_np``, ``make_kvs_np``), executed from the
+   reference tree, and the static quantities ``GPR_kron.__init__`` derives from them (``:600-610``).
+   The TensorFlow parts of vff.py (``make_Kuu``, ``elbo``, ``predict_f``) cannot run here.
+
 Usage:  python oracle/make_golden.py
 """
 from __future__ import annotations
@@ -121,8 +126,32 @@ def sklearn_ard():
     np.savez(os.path.join(OUT, "sklearn_ard.npz"), **out)
 
 
+def vff_features():
+    path = os.path.join(REF, "GPSat", "vff.py")
+    tree = ast.parse(open(path).read())
+    wanted = {"make_Kuf_np", "make_kvs_two_np", "make_kvs_np"}
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in wanted]
+    from functools import reduce
+    ns = {"np": np, "reduce": reduce}
+    exec(compile(ast.Module(body=body, type_ignores=[]), path, "exec"), ns)
+    rng = np.random.default_rng(515)
+    n = 70
+    X = rng.uniform(-1.0, 1.0, (n, 3)) * np.array([2.0, 3.0, 1.0])
+    Y = rng.standard_normal((n, 1))
+    a = np.array([-2.5, -3.5, -1.25])
+    b = np.array([2.75, 3.25, 1.5])
+    ms = [np.arange(4), np.arange(3), np.arange(2)]
+    # GPR_kron.__init__, vff.py:600-610
+    Kuf = ns["make_kvs_np"]([ns["make_Kuf_np"](X[:, i:i + 1], a[i], b[i], ms[i]) for i in range(3)])
+    np.savez(os.path.join(OUT, "vff_features.npz"), X=X, Y=Y, a=a, b=b, m0=ms[0], m1=ms[1], m2=ms[2],
+             Kuf0=ns["make_Kuf_np"](X[:, 0:1], a[0], b[0], ms[0]), Kuf=Kuf, KufY=np.dot(Kuf, Y),
+             KufKfu=np.dot(Kuf, Kuf.T), tr_YTY=np.sum(np.square(Y)))
+    print("vff Kuf:", Kuf.shape)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     kat_localexperts()
     pure_python()
     sklearn_ard()
+    vff_features()

@@ -162,3 +162,84 @@ def test_sgpr_gradient_fd_and_tight_bound(kind):
     exact = gpr.lml(kind, X, y, th)
     assert v <= exact + 1e-9
     assert abs(sgpr.elbo(kind, X, y, X.copy(), th) - exact) < 1e-2
+
+
+# ---- VFF (oracle/vff.py) ---------------------------------------------------------------------
+def test_vff_features_match_reference_numpy(golden_dir):
+    """make_Kuf_np / make_kvs_np and the static quantities of GPR_kron.__init__
+    (/root/reference/GPSat/vff.py:518-559, 600-610), executed from the reference source by
+    oracle/make_golden.py."""
+    from oracle import vff
+    g = np.load(os.path.join(golden_dir, "vff_features.npz"))
+    ms = [g["m0"], g["m1"], g["m2"]]
+    np.testing.assert_allclose(vff.kuf_np(g["X"][:, 0:1], g["a"][0], g["b"][0], ms[0]), g["Kuf0"], rtol=0, atol=1e-15)
+    pre = vff.Precomputed(g["X"], g["Y"][:, 0], g["a"], g["b"], ms)
+    assert pre.Ms == [7, 5, 3]
+    np.testing.assert_allclose(pre.Kuf, g["Kuf"], rtol=0, atol=1e-15)
+    np.testing.assert_allclose(pre.KufY, g["KufY"][:, 0], rtol=1e-13, atol=1e-13)
+    np.testing.assert_allclose(pre.KufKfu, g["KufKfu"], rtol=1e-13, atol=1e-13)
+    assert abs(pre.trYY - float(g["tr_YTY"])) < 1e-12
+
+
+@pytest.mark.parametrize("kind", ["Matern32", "Matern52"])
+def test_vff_converges_to_exact_gpr(kind):
+    """With a domain much wider than the data and many features the inducing features determine f on
+    the data, so ELBO -> exact LML and predict_f -> exact GPR (1-D, where the product kernel is the
+    Matern kernel itself).  Pins make_Kuu / elbo / predict_f (vff.py:381-454, 612-675)."""
+    from oracle import vff
+    rng = np.random.default_rng(0)
+    n = 60
+    X = rng.uniform(-1.8, 1.9, (n, 1))
+    y = np.sin(2 * X[:, 0]) + 0.1 * rng.standard_normal(n)
+    th = np.array([0.7, 1.1, 0.05])
+    Xs = rng.uniform(-1.5, 1.5, (5, 1))
+    pre = vff.Precomputed(X, y, [-8.0], [8.0], [np.arange(768)])
+    exact = gpr.lml(kind, X, y, th)
+    v = vff.elbo(kind, pre, th)
+    assert v <= exact + 1e-9 and abs(v - exact) < 2e-4
+    p, q = vff.predict(kind, pre, th, Xs), gpr.predict(kind, X, y, th, Xs)
+    np.testing.assert_allclose(p["f*"], q["f*"], rtol=0, atol=1e-6)
+    np.testing.assert_allclose(p["f*_var"], q["f*_var"], rtol=0, atol=1e-6)
+    np.testing.assert_allclose(p["y_var"], p["f*_var"] + th[2])
+
+
+@pytest.mark.parametrize("kind", ["Matern12", "Matern32", "Matern52"])
+@pytest.mark.parametrize("D", [1, 2])
+def test_vff_gradient_fd(kind, D):
+    from oracle import vff
+    rng = np.random.default_rng(3 + D)
+    n = 80
+    X = rng.uniform(-1.8, 1.9, (n, D))
+    y = np.sin(2 * X[:, 0]) + 0.1 * rng.standard_normal(n)
+    pre = vff.Precomputed(X, y, [-2.2] * D, [2.3] * D, [np.arange(m) for m in ([12] if D == 1 else [6, 5])])
+    th = np.concatenate([rng.uniform(0.5, 1.5, D), rng.uniform(0.5, 1.5, D), [0.05]])
+    v, g = vff.elbo_and_grad(kind, pre, th)
+    for i in range(len(th)):
+        h = np.zeros_like(th)
+        h[i] = 1e-6 * th[i]
+        fd = (vff.elbo(kind, pre, th + h) - vff.elbo(kind, pre, th - h)) / (2 * h[i])
+        assert abs(fd - g[i]) <= 1e-6 * max(1.0, abs(g[i]))
+
+
+def test_vff_edge_features_and_fit():
+    """Prediction features outside [a, b] take the kernel's edge form (vff.py:472-497); Matern52
+    refuses them (:498-511).  The optimiser increases the ELBO."""
+    from oracle import vff
+    ms = np.arange(4)
+    X1 = np.array([[-3.0], [0.3], [2.9]])
+    inside = vff.kuf_np(X1[1:2], -2.0, 2.0, ms)
+    for kind in ("Matern12", "Matern32"):
+        F = vff.kuf_pred(kind, 0.8, X1, -2.0, 2.0, ms)
+        np.testing.assert_allclose(F[:, 1:2], inside)
+        assert np.allclose(F[:4, 0], F[0, 0]) and np.allclose(F[:4, 2], F[0, 2])      # cos rows share the edge value
+    np.testing.assert_allclose(vff.kuf_pred("Matern12", 0.8, X1, -2.0, 2.0, ms)[:4, 0], np.exp(-1.0 / 0.8))
+    assert np.all(vff.kuf_pred("Matern12", 0.8, X1, -2.0, 2.0, ms)[4:, [0, 2]] == 0.0)
+    with pytest.raises(AssertionError):
+        vff.kuf_pred("Matern52", 0.8, X1, -2.0, 2.0, ms)
+    rng = np.random.default_rng(9)
+    X = rng.uniform(-1.5, 1.5, (50, 1))
+    y = np.sin(3 * X[:, 0]) + 0.1 * rng.standard_normal(50)
+    pre = vff.Precomputed(X, y, [-2.5], [2.5], [np.arange(10)])
+    th0 = np.ones(3)
+    th, val, ok, nfev = vff.fit("Matern32", pre, th0)
+    assert ok and val > vff.elbo("Matern32", pre, th0) and nfev > 3
