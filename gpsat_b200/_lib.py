@@ -26,6 +26,7 @@ EXPORTED_SYMBOLS = (
     "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_fit_options_default",
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
     "gpsat_sgpr_elbo", "gpsat_sgpr_predict", "gpsat_sgpr_fit",
+    "gpsat_vff_elbo", "gpsat_vff_predict", "gpsat_vff_fit",
 )
 
 
@@ -42,6 +43,10 @@ class FitOptions(C.Structure):
 
 class Priors(C.Structure):
     _fields_ = [("kind", C.c_void_p), ("a", C.c_void_p), ("b", C.c_void_p)]
+
+
+class VffDomain(C.Structure):
+    _fields_ = [("a", C.c_void_p), ("b", C.c_void_p), ("nfreq", C.c_void_p)]
 
 
 class Stats(C.Structure):
@@ -89,6 +94,10 @@ def load():
     lib.gpsat_sgpr_fit.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp, vp,
                                    C.POINTER(FitOptions), C.POINTER(Priors), vp, vp, vp, vp, vp]
     lib.gpsat_sgpr_predict.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp, vp, vp]
+    lib.gpsat_vff_elbo.argtypes = [vp, C.POINTER(Batch), C.POINTER(VffDomain), C.c_int, vp, vp, vp, vp]
+    lib.gpsat_vff_predict.argtypes = [vp, C.POINTER(Batch), C.POINTER(VffDomain), C.c_int, vp, vp, vp, vp, vp, vp]
+    lib.gpsat_vff_fit.argtypes = [vp, C.POINTER(Batch), C.POINTER(VffDomain), C.c_int, vp, vp, vp, vp, vp,
+                                  C.POINTER(FitOptions), C.POINTER(Priors), vp, vp, vp, vp, vp]
     _lib = lib
     return lib
 

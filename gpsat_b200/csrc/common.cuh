@@ -41,6 +41,7 @@ struct SlotDesc {
   double* gpart;         // [T*(T+1)/2][GPSAT_DMAX + 2] gradient partial sums per lauum tile
   int* notpd;            // [1] set to 1 when a pivot is not positive
   const double* pre;     // kind == GPSAT_PRECOMPUTED: dense symmetric matrix (lower part read), else unused
+  const double* pre_s;   // kind == GPSAT_PRECOMPUTED with m > 0: prediction rows [m][ldpre] (Kus^T)
   int ldpre;
   double inv_ls[GPSAT_DMAX];
   double var;            // kernel variance

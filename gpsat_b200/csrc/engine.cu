@@ -84,6 +84,7 @@ struct SlotMem {
 
 }  // namespace gpsat
 #include "sgpr_kernels.cuh"
+#include "vff_kernels.cuh"
 namespace gpsat {
 
 // ---- transforms (gpflow.utilities.positive / tfp.bijectors.Sigmoid) -------------------------
@@ -153,7 +154,7 @@ __device__ __forceinline__ void slot_set_expert(SlotDesc& d, const SlotMem& mem,
   d.Xs = (m > 0) ? b.Xs + b.off_m[e] * b.D : nullptr;
   d.A = mem.A; d.Wd = mem.Wd; d.Ld = mem.Ld; d.logdet = mem.logdet; d.quad = mem.quad;
   d.gpart = mem.gpart; d.notpd = mem.notpd;
-  d.pre = nullptr; d.ldpre = 0;
+  d.pre = nullptr; d.pre_s = nullptr; d.ldpre = 0;
   *d.notpd = 0;
   *d.quad = 0.0;
 }
@@ -367,6 +368,7 @@ __global__ void debug_extract_kernel(const SlotDesc* slots, double* Lout, double
 }
 
 #include "sgpr_fit.cuh"
+#include "vff_fit.cuh"
 
 }  // namespace gpsat
 

@@ -80,6 +80,7 @@ static int engine_setup_kernels() {
   CUDA_TRY(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STEP_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(sgpr_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SGPR_GEMM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(vff_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, VFF_GRAD_SMEM_BYTES));
   return 0;
 }
 

@@ -111,7 +111,7 @@ static int sgpr_launch_eval(Engine& g, const SgprCall& c, bool with_grad, bool w
   transpose_w_kernel<<<dim3(T32, T32, S), 256, 0, st>>>(dd, c.sk, 0, with_grad ? 1 : 0);
   gemm(SGPR_GEMM_A, MT * NT, 1);
   gemm(SGPR_GEMM_SYRK, ntl, c.nsplit);
-  sgpr_reduce_kernel<<<dim3(std::min(256, (c.Mp * c.Mp + 255) / 256), S), 256, 0, st>>>(dd, c.nsplit);
+  sgpr_reduce_kernel<<<dim3(std::min(256, (c.Mp * c.Mp + 255) / 256), S), 256, 0, st>>>(dd, c.nsplit, 1);
   if (launch_sweep(g, S, MT, MT, with_grad || with_pred, c.sb, false)) return 1;
   g.stats.kernel_launches += 3;
   if (with_grad || with_pred) {
@@ -273,3 +273,5 @@ int gpsat_sgpr_fit(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off
 }
 
 }  // extern "C"
+
+#include "engine_vff.inl"

@@ -86,7 +86,7 @@ __device__ __forceinline__ void sgpr_fill_slot(SlotDesc& s, int expert, int M, i
   s.quad = s.logdet + L.lgd;
   s.gpart = nullptr;
   s.notpd = reinterpret_cast<int*>(s.quad + 2);
-  s.pre = nullptr; s.ldpre = 0;
+  s.pre = nullptr; s.pre_s = nullptr; s.ldpre = 0;
   s.Xs = nullptr;
 }
 
@@ -438,8 +438,9 @@ sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit, int w
   }
 }
 
-// Bm = sum of the split-K partials in a fixed order (+ I on the first M diagonal entries), lower tiles.
-__global__ void __launch_bounds__(256) sgpr_reduce_kernel(const SgprDesc* __restrict__ descs, int nsplit) {
+// Bm = sum of the split-K partials in a fixed order (+ I on the first M diagonal entries when add_eye),
+// lower tiles.
+__global__ void __launch_bounds__(256) sgpr_reduce_kernel(const SgprDesc* __restrict__ descs, int nsplit, int add_eye) {
   const SgprDesc& d = descs[blockIdx.y];
   if (d.expert < 0) return;
   const int Mp = d.Mp;
@@ -449,7 +450,7 @@ __global__ void __launch_bounds__(256) sgpr_reduce_kernel(const SgprDesc* __rest
     if (c / NB > r / NB) continue;
     double v = 0.0;
     for (int s = 0; s < nsplit; ++s) v += d.part[(size_t)s * total + idx];
-    if (r == c && r < d.M) v += 1.0;
+    if (add_eye && r == c && r < d.M) v += 1.0;
     d.Bm[idx] = v;
   }
 }

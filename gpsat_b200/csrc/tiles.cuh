@@ -271,7 +271,8 @@ __device__ __forceinline__ void add_pre_tile(const SlotDesc& d, int g0r, int g0c
     double v;
     if (gc >= n) v = (gr == gc && gr > n) ? 1.0 : 0.0;
     else if (gr == n) v = ycv;
-    else v = (gr < n) ? d.pre[(size_t)gr * d.ldpre + gc] : 0.0;
+    else if (gr < n) v = d.pre[(size_t)gr * d.ldpre + gc];
+    else v = (gr < n + 1 + d.m) ? d.pre_s[(size_t)(gr - n - 1) * d.ldpre + gc] : 0.0;
     Cs[r * LDC + c] += v;
   }
 }

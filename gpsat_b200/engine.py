@@ -210,11 +210,14 @@ class Engine:
 
     def fit(self, batch: RaggedBatch, theta0, tkind, ta, tb, trainable, *, max_iter: int = 10_000,
             pgtol: float = 1e-5, ftol: float = SCIPY_FTOL, maxfun: int = 15_000, maxls: int = 20,
-            max_slots: int = 0, priors=None, inducing=None) -> FitResult:
+            max_slots: int = 0, priors=None, inducing=None, vff=None) -> FitResult:
         """Batched L-BFGS fit.  ``priors``: optional ``(kind[E,P], a[E,P], b[E,P])`` (GPSAT_PRIOR_*).
         ``inducing``: one [M_e, D] array per expert switches to the sparse model (``gpsat_sgpr_fit``:
-        minimises -elbo with the inducing points fixed; ``FitResult.lml`` then holds the ELBO)."""
-        E, P = batch.E, batch.D + 2
+        minimises -elbo with the inducing points fixed; ``FitResult.lml`` then holds the ELBO).
+        ``vff``: ``(a[E,D], b[E,D], nfreq[E,D])`` switches to variational Fourier features
+        (``gpsat_vff_fit``; theta has 2 D + 1 columns: lengthscales, per-dimension variances, noise)."""
+        E = batch.E
+        P = 2 * batch.D + 1 if vff is not None else batch.D + 2
         mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
         th = self._in(batch, theta0, np.float64, (E, P))
         th = th.clone() if _is_torch(th) else th.copy()
@@ -237,7 +240,10 @@ class Engine:
         self._pre(batch)
         tail = (_ptr(th), _ptr(tk), _ptr(a), _ptr(b), _ptr(tr), C.byref(opt),
                 C.byref(pri) if pri is not None else None, _ptr(obj), _ptr(lml), _ptr(nev), _ptr(nit), _ptr(status))
-        if inducing is None:
+        if vff is not None:
+            dom, keep_dom = self._vff_domain(batch, vff)
+            _lib.check(self._lib.gpsat_vff_fit(self._h, C.byref(cb), C.byref(dom), mem, *tail))
+        elif inducing is None:
             _lib.check(self._lib.gpsat_gpr_fit(self._h, C.byref(cb), mem, *tail))
         else:
             off_z, Zp = self._inducing(batch, inducing)
@@ -320,6 +326,45 @@ class Engine:
         self._pre(batch)
         _lib.check(self._lib.gpsat_sgpr_predict(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, _ptr(th), _ptr(fm),
                                                 _ptr(fv), _ptr(yv), _ptr(elbo), _ptr(status)))
+        return {"f*": fm, "f*_var": fv, "y_var": yv, "elbo": elbo, "status": status}
+
+    # ---- variational Fourier features (GPflowVFFModel, vff_model.py:14-264) ----------------------------
+    def _vff_domain(self, batch: RaggedBatch, vff):
+        E, D = batch.E, batch.D
+        a = np.ascontiguousarray(vff[0], dtype=np.float64).reshape(E, D)
+        b = np.ascontiguousarray(vff[1], dtype=np.float64).reshape(E, D)
+        nf = np.ascontiguousarray(vff[2], dtype=np.int32).reshape(E, D)
+        return _lib.VffDomain(a.ctypes.data, b.ctypes.data, nf.ctypes.data), (a, b, nf)
+
+    def vff_elbo(self, batch: RaggedBatch, vff, theta, with_grad: bool = False):
+        """``GPR_kron.elbo`` per expert at fixed theta ([E, 2 D + 1]); returns (elbo, grad or None, status)."""
+        E, P = batch.E, 2 * batch.D + 1
+        mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
+        dom, keep = self._vff_domain(batch, vff)
+        th = self._in(batch, theta, np.float64, (E, P))
+        elbo = self._empty(batch, (E,), np.float64)
+        grad = self._empty(batch, (E, P), np.float64) if with_grad else None
+        status = self._empty(batch, (E,), np.int32)
+        cb = batch._c(False)
+        self._pre(batch)
+        _lib.check(self._lib.gpsat_vff_elbo(self._h, C.byref(cb), C.byref(dom), mem, _ptr(th), _ptr(elbo), _ptr(grad),
+                                            _ptr(status)))
+        return elbo, grad, status
+
+    def vff_predict(self, batch: RaggedBatch, vff, theta):
+        """``GPR_kron.predict_f`` / ``predict_y`` (full_cov=False) per expert at fixed theta."""
+        E, P = batch.E, 2 * batch.D + 1
+        mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
+        M = int(batch.off_m[-1])
+        dom, keep = self._vff_domain(batch, vff)
+        th = self._in(batch, theta, np.float64, (E, P))
+        fm, fv, yv = (self._empty(batch, (M,), np.float64) for _ in range(3))
+        elbo = self._empty(batch, (E,), np.float64)
+        status = self._empty(batch, (E,), np.int32)
+        cb = batch._c(True)
+        self._pre(batch)
+        _lib.check(self._lib.gpsat_vff_predict(self._h, C.byref(cb), C.byref(dom), mem, _ptr(th), _ptr(fm), _ptr(fv),
+                                               _ptr(yv), _ptr(elbo), _ptr(status)))
         return {"f*": fm, "f*_var": fv, "y_var": yv, "elbo": elbo, "status": status}
 
     def factor_debug(self, kernel: str, X, y, theta, want_U: bool = True):

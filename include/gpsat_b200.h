@@ -184,6 +184,40 @@ int gpsat_sgpr_fit(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* o
                    const uint8_t* trainable, const gpsat_fit_options* opt, const gpsat_priors* priors,
                    double* objective, double* elbo, int32_t* n_evals, int32_t* n_iters, int32_t* status);
 
+/* ---- variational Fourier features: GPflowVFFModel -> GPR_kron, GPSat/vff.py:564-675,
+ * GPSat/models/vff_model.py:14-264 -------------------------------------------------------------
+ * One 1-D Matern kernel per input dimension (batch->kernel in {MATERN12, MATERN32, MATERN52},
+ * D <= 3), cos / sin inducing features with frequencies 2 pi k / (b - a), k = 0 .. nfreq - 1
+ * (ms = arange(num_inducing_features), vff_model.py:201-204) on the domain [a, b] of each
+ * dimension (scaled coordinates, vff_model.py:180-199).  The arrays of gpsat_vff_domain are HOST
+ * arrays [E][D].  theta layout: [lengthscale_1..D, variance_1..D, likelihood variance], P = 2 D + 1
+ * (each 1-D kernel has its own variance, get_kernel_variance is their product, vff_model.py:217-218).
+ * Observations must lie strictly inside (a, b) (vff.py:602-603; checked for host batches).
+ * Prediction points outside [a, b] use the kernel's edge features (vff.py:472-497); Matern52 has
+ * none (:498-511) - the caller must keep them inside. */
+typedef struct gpsat_vff_domain {
+  const double* a;        /* [E][D] lower edge of the feature domain */
+  const double* b;        /* [E][D] upper edge */
+  const int32_t* nfreq;   /* [E][D] number of frequencies per dimension (2 nfreq - 1 <= 128 features) */
+} gpsat_vff_domain;
+
+/* elbo[e] = GPR_kron.elbo() (vff.py:612-643; GPflowVFFModel.get_objective_function_value reports it
+ * as is, vff_model.py:209-211); grad (may be NULL) = d elbo / d theta [E][P]. */
+int gpsat_vff_elbo(gpsat_engine* eng, const gpsat_batch* batch, const gpsat_vff_domain* dom, int mem,
+                   const double* theta, double* elbo, double* grad, int32_t* status);
+
+/* GPR_kron.predict_f (vff.py:645-675, full_cov = False) and predict_y at batch->Xs. */
+int gpsat_vff_predict(gpsat_engine* eng, const gpsat_batch* batch, const gpsat_vff_domain* dom, int mem,
+                      const double* theta, double* fmean, double* fvar, double* yvar, double* elbo,
+                      int32_t* status);
+
+/* The inherited optimise_parameters (gpflow_models.py:290-329) on -elbo; arguments as gpsat_gpr_fit
+ * with P = 2 D + 1. */
+int gpsat_vff_fit(gpsat_engine* eng, const gpsat_batch* batch, const gpsat_vff_domain* dom, int mem,
+                  double* theta_io, const int32_t* tkind, const double* ta, const double* tb,
+                  const uint8_t* trainable, const gpsat_fit_options* opt, const gpsat_priors* priors,
+                  double* objective, double* elbo, int32_t* n_evals, int32_t* n_iters, int32_t* status);
+
 /* Test hook (single expert, host memory): dense factor of the augmented matrix.
  * Lout [(n+1)*(n+1)] row-major lower: rows < n = chol(K + s2 I), row n = (L^-1 y)^T, 1.
  * Uout [(n+1)*(n+1)] row-major upper: L_aug^-T (may be NULL). */
