@@ -77,7 +77,7 @@ static int sgpr_setup(Engine& g, const gpsat_batch* batch, const int64_t* off_z,
   const int MT = c.Mp / NB, ntile_l = MT * (MT + 1) / 2;
   int S = (int)std::min<int64_t>(E, max_slots > 0 ? max_slots : 148);
   for (;;) {
-    c.nsplit = std::max(1, std::min({16, c.npad / NB, (592 + S * ntile_l - 1) / (S * ntile_l)}));
+    c.nsplit = (c.npad + SGPR_KCHUNK - 1) / SGPR_KCHUNK;
     c.L = sgpr_layout(c.npad, c.mpad, c.Mp, c.nsplit, with_grad, with_pred);
     if (c.L.total * 8 * S <= (size_t)((free_b + g.bsg.cap) * 0.8) || S == 1) break;
     S = std::max(1, S / 2);

@@ -91,7 +91,7 @@ static int vff_setup(Engine& g, const gpsat_batch* batch, const gpsat_vff_domain
   const int MT = c.Mp / NB, ntl = MT * (MT + 1) / 2;
   int S = (int)std::min<int64_t>(E, max_slots > 0 ? max_slots : 148);
   for (;;) {
-    c.nsplit = std::max(1, std::min({16, c.npad / NB, (592 + S * ntl - 1) / (S * ntl)}));
+    c.nsplit = (c.npad + SGPR_KCHUNK - 1) / SGPR_KCHUNK;
     c.L = vff_layout(D, c.npad, c.mpad, c.Mp, c.TRmax, c.nsplit, with_pred);
     if (c.L.total * 8 * S <= (size_t)((free_b + g.bsg.cap) * 0.8) || S == 1) break;
     S = std::max(1, S / 2);

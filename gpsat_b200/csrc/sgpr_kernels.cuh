@@ -30,6 +30,8 @@ namespace gpsat {
 
 constexpr double SGPR_JITTER = 1e-6;     // gpflow.config.default_jitter()
 constexpr int SGPR_RES_ROWS = 64;        // rows of the residual kernel per CTA
+constexpr int SGPR_KCHUNK = 2048;        // k range of one split of the SYRK: a property of the expert alone,
+                                         // so results do not depend on what else is in the batch
 
 struct SgprDesc {
   int expert;            // -1 = idle
@@ -320,9 +322,9 @@ sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit, int w
       if (tile >= MT * (MT + 1) / 2) return;
       tri_tile(tile, rt, ct);
       Aop = d.Aq; Bop = d.Aq; ldg = d.npad; out = d.part + (size_t)split * Mp * Mp;
-      const int nslab = d.npad / KC, per = (nslab + nsplit - 1) / nsplit;
-      kbeg = min(d.npad, split * per * KC);
-      kend = min(d.npad, (split + 1) * per * KC);
+      if (split * SGPR_KCHUNK >= d.npad) return;
+      kbeg = split * SGPR_KCHUNK;
+      kend = min(d.npad, kbeg + SGPR_KCHUNK);
       break;
     }
     case SGPR_GEMM_T1: case SGPR_GEMM_T2: case SGPR_GEMM_V: case SGPR_GEMM_H: case SGPR_GEMM_GC: {
@@ -449,7 +451,8 @@ __global__ void __launch_bounds__(256) sgpr_reduce_kernel(const SgprDesc* __rest
     const int r = (int)(idx / Mp), c = (int)(idx - (size_t)r * Mp);
     if (c / NB > r / NB) continue;
     double v = 0.0;
-    for (int s = 0; s < nsplit; ++s) v += d.part[(size_t)s * total + idx];
+    const int own = (d.npad + SGPR_KCHUNK - 1) / SGPR_KCHUNK;
+    for (int s = 0; s < own; ++s) v += d.part[(size_t)s * total + idx];
     if (add_eye && r == c && r < d.M) v += 1.0;
     d.Bm[idx] = v;
   }

@@ -277,6 +277,10 @@ class B200GPRModel(BaseGPRModel):
         """``None`` for the exact model; the sparse subclass returns ``[Z]``."""
         return None
 
+    def _fit_kwargs(self) -> dict:
+        """Extra ``Engine.fit`` arguments that select the model family."""
+        return {"inducing": self._inducing_list()}
+
     def update_obs_data(self, data=None, coords_col=None, obs_col=None, coords=None, obs=None, coords_scale=None,
                         obs_scale=None):
         """Swap the training data, keeping hyper-parameters (``gpflow_models.py:159-176``)."""
@@ -370,7 +374,7 @@ class B200GPRModel(BaseGPRModel):
             kw = {"ftol": float(tol), "pgtol": float(tol)}
         res = self.engine.fit(self._batch(), self._theta[None, :], self._tkind[None, :], self._ta[None, :],
                               self._tb[None, :], self._trainable[None, :].astype(np.uint8), max_iter=int(max_iter),
-                              priors=self._prior_arrays(1), inducing=self._inducing_list(), **kw)
+                              priors=self._prior_arrays(1), **self._fit_kwargs(), **kw)
         status = int(res.status[0])
         self.opt_info = {"status": status, "n_evals": int(res.n_evals[0]), "n_iters": int(res.n_iters[0]),
                          "objective": float(res.objective[0])}
@@ -581,6 +585,148 @@ class B200SGPRModel(B200GPRModel):
         return float(elbo[0])
 
 
+class B200VFFModel(B200GPRModel):
+    """Variational Fourier features (Hensman et al. 2017), mirroring ``GPflowVFFModel``
+    (``GPSat/models/vff_model.py:14-264`` -> ``GPR_kron``, ``GPSat/vff.py:564-675``): one 1-D Matern
+    kernel per input dimension, ``num_inducing_features`` frequencies per dimension (int or list;
+    ``2 k - 1`` cos / sin features each, their product over the dimensions in total), on the box
+    ``expert_loc +- domain_size`` (unscaled units) widened to contain the data (``:180-199``).
+
+    Parameters: "lengthscales" has one entry per dimension; every 1-D kernel has its own variance,
+    ``get_kernel_variance`` returns their product and ``set_kernel_variance`` gives each the D-th
+    root (``:213-233``); bounds passed to ``set_kernel_variance_constraints`` are raised to 1/D
+    (``:249-258``).  The likelihood variance starts at GPflow's 1.0 (no ``noise_variance`` argument
+    in the reference).  ``get_objective_function_value`` is **+ELBO** (``:209-211``).
+    Reference quirk kept: ``fixed_params=["lengthscales"]`` / ``["kernel_variance"]`` freeze only the
+    *last* dimension's kernel, because ``GPR_kron`` registers that one as ``model.kernel``
+    (``vff.py:572``, ``gpflow_models.py:281-284``).  ``domain_size=None`` (which raises ``TypeError``
+    in the reference, ``vff_model.py:177``) selects the data range +- 1e-8, the branch the reference
+    intended (``:181-184``).  At most 3 input dimensions and 64 frequencies per dimension.
+    """
+
+    def __init__(self, data=None, coords_col=None, obs_col=None, coords=None, coords_scale=None, obs=None,
+                 obs_scale=None, obs_mean=None, *, kernel="Matern32", num_inducing_features=None, kernel_kwargs=None,
+                 mean_function=None, mean_func_kwargs=None, domain_size=None, expert_loc=None, device: int = 0,
+                 verbose=True, **kwargs):
+        self.device = int(device)
+        BaseGPRModel.__init__(self, data=data, coords_col=coords_col, obs_col=obs_col, coords=coords, obs=obs,
+                              coords_scale=coords_scale, obs_scale=obs_scale, obs_mean=obs_mean, verbose=verbose)
+        assert kernel is not None, "kernel was not provided"
+        assert num_inducing_features is not None, "Number of inducing points per dimension not specified"
+        if kernel not in ("Matern12", "Matern32", "Matern52"):
+            raise NotImplementedError(f"VFF is defined for Matern12 / Matern32 / Matern52, got '{kernel}'")
+        if mean_function is not None:
+            raise NotImplementedError("only the zero mean function is implemented")
+        assert self.obs.shape[1] == 1, "B200VFFModel takes one observation column"
+        self.kernel = kernel
+        D = self.coords.shape[1]
+        assert 1 <= D <= 3, "B200VFFModel supports 1..3 input dimensions"
+        if kernel_kwargs is None:
+            kernel_kwargs = [dict(lengthscales=1.0) for _ in range(D)]
+        elif isinstance(kernel_kwargs, dict):
+            kernel_kwargs = [dict(kernel_kwargs) for _ in range(D)]
+        assert len(kernel_kwargs) == D
+        ls = np.array([float(np.asarray(k.get("lengthscales", 1.0))) for k in kernel_kwargs])
+        var = np.array([float(k.get("variance", 1.0)) for k in kernel_kwargs])
+        # domain of the Fourier features, scaled coordinates (vff_model.py:174-199)
+        if isinstance(domain_size, (int, float)):
+            domain_size = [domain_size for _ in range(D)]
+        cmin, cmax = self.coords.min(axis=0), self.coords.max(axis=0)
+        if domain_size is None:
+            a, b = cmin - 1e-8, cmax + 1e-8
+        else:
+            assert len(domain_size) == D, "length of margin list must match number of coordinate dimensions"
+            if expert_loc is None:
+                expert_loc = np.mean(self.coords, axis=0) * self.coords_scale.squeeze()
+            expert_loc = np.asarray(expert_loc, dtype=np.float64).reshape(-1)
+            scale = np.broadcast_to(np.atleast_2d(self.coords_scale)[0, :], (D,))
+            a = (expert_loc[:D] - np.asarray(domain_size, dtype=np.float64)) / scale
+            b = (expert_loc[:D] + np.asarray(domain_size, dtype=np.float64)) / scale
+            a = np.where(a < cmin, a, cmin - 1e-8)
+            b = np.where(b > cmax, b, cmax + 1e-8)
+        self.vff_a, self.vff_b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
+        if isinstance(num_inducing_features, (int, np.integer)):
+            nf = [int(num_inducing_features)] * D
+        else:
+            nf = [int(k) for k in num_inducing_features]
+            nf = nf * D if len(nf) == 1 else nf
+        assert len(nf) == D, "Number of ms must match number of kernels."
+        assert all(1 <= k <= 64 for k in nf), "num_inducing_features must be in [1, 64] per dimension"
+        self.vff_nfreq = np.asarray(nf, dtype=np.int32)
+        P = 2 * D + 1
+        self._theta = np.concatenate([ls, var, [1.0]])
+        self._tkind = np.zeros(P, np.int32)
+        self._ta = np.zeros(P)
+        self._tb = np.zeros(P)
+        self._ta[P - 1] = VARIANCE_LOWER_BOUND
+        self._trainable = np.ones(P, bool)
+        self._pkind = np.zeros(P, np.int32)
+        self._pa = np.zeros(P)
+        self._pb = np.zeros(P)
+        self.opt_info = {}
+
+    def _slice(self, name):
+        D = self.D
+        return {"lengthscales": slice(0, D), "kernel_variance": slice(D, 2 * D),
+                "likelihood_variance": slice(2 * D, 2 * D + 1)}[name]
+
+    def _vff(self):
+        return (self.vff_a[None, :], self.vff_b[None, :], self.vff_nfreq[None, :])
+
+    def _fit_kwargs(self) -> dict:
+        return {"vff": self._vff()}
+
+    @property
+    def num_features(self) -> int:
+        return int(np.prod(2 * self.vff_nfreq - 1))
+
+    def _fix_hyperparameters(self, params_list):
+        D = self.D
+        for param in params_list:
+            if param == "likelihood_variance":
+                self._trainable[2 * D] = False
+            elif param == "kernel_variance":
+                self._trainable[2 * D - 1] = False          # model.kernel is the last dimension's kernel
+            elif param == "lengthscales":
+                self._trainable[D - 1] = False
+            else:
+                print(f"{param} is not detected as a hyperparameter. Skipping...")
+
+    def predict(self, coords, full_cov=False, apply_scale=True) -> Dict[str, np.ndarray]:
+        if full_cov:
+            raise NotImplementedError("full_cov=True is not implemented (GPR_kron.predict_f raises too, vff.py:664-665)")
+        Xs = self._prep_pred_coords(coords, apply_scale)
+        if self.kernel == "Matern52":
+            assert np.all(Xs >= self.vff_a) and np.all(Xs <= self.vff_b), "Edges not implemented for Matern52"
+        out = self.engine.vff_predict(self._batch(Xs), self._vff(), self._theta[None, :])
+        if int(out["status"][0]) != _lib.STATUS_OK:
+            raise FloatingPointError("Kuf Kfu / s2 + Kuu is not positive definite at the current parameters")
+        return {"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"], "f_bar": self._f_bar(len(out["f*"]))}
+
+    def get_objective_function_value(self):
+        """ELBO at the current parameters (``vff_model.py:209-211``)."""
+        elbo, _, _ = self.engine.vff_elbo(self._batch(), self._vff(), self._theta[None, :])
+        return float(elbo[0])
+
+    def get_kernel_variance(self) -> float:
+        return float(np.prod(self._theta[self._slice("kernel_variance")]))
+
+    def set_kernel_variance(self, kernel_variance):
+        v = self._scalar(kernel_variance, "kernel_variance")
+        self._assign("kernel_variance", np.full(self.D, v ** (1.0 / self.D)))
+
+    def get_likelihood_variance(self) -> float:
+        return float(self._theta[2 * self.D])
+
+    def set_kernel_variance_constraints(self, low, high, move_within_tol=True, tol=1e-8, scale=False,
+                                        scale_magnitude=None):
+        alpha = 1.0 / self.D
+        low = float(np.asarray(low, dtype=np.float64).reshape(-1)[0]) ** alpha
+        high = float(np.asarray(high, dtype=np.float64).reshape(-1)[0]) ** alpha
+        self._set_param_constraints("kernel_variance", [low] * self.D, [high] * self.D, move_within_tol, tol, scale,
+                                    scale_magnitude)
+
+
 def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Sequence] = None, *,
                        optimise: bool = True, max_iter: int = 10_000, fixed_params=None, apply_scale: bool = True,
                        **opt_kwargs):
@@ -595,10 +741,13 @@ def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Seq
     m0 = models[0]
     assert all(m.kernel == m0.kernel and m.D == m0.D and m.device == m0.device for m in models), \
         "fit_predict_models needs one kernel / dimension / device per batch"
-    sparse = isinstance(m0, B200SGPRModel)
-    assert all(isinstance(m, B200SGPRModel) == sparse for m in models), \
+    sparse, fourier = isinstance(m0, B200SGPRModel), isinstance(m0, B200VFFModel)
+    assert all(type(m) is type(m0) for m in models), \
         "fit_predict_models needs one model class per batch (partition by model type, local_experts.py:1021-1041)"
     inducing = [m._inducing_list()[0] for m in models] if sparse else None
+    vff = ((np.stack([m.vff_a for m in models]), np.stack([m.vff_b for m in models]),
+            np.stack([m.vff_nfreq for m in models])) if fourier else None)
+    family = {"vff": vff} if fourier else {"inducing": inducing}
     for m in models:
         m._fix_hyperparameters(fixed_params or [])
     Xs_list = None
@@ -618,7 +767,7 @@ def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Seq
                    np.stack([m._pb for m in models]))
         res = eng.fit(batch, theta, np.stack([m._tkind for m in models]), np.stack([m._ta for m in models]),
                       np.stack([m._tb for m in models]), np.stack([m._trainable for m in models]).astype(np.uint8),
-                      max_iter=int(max_iter), priors=pri, inducing=inducing, **kw)
+                      max_iter=int(max_iter), priors=pri, **family, **kw)
         for e, m in enumerate(models):
             st = int(res.status[e])
             m.opt_info = {"status": st, "n_evals": int(res.n_evals[e]), "n_iters": int(res.n_iters[e]),
@@ -629,7 +778,10 @@ def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Seq
         theta = np.stack([m._theta for m in models])
     preds = None
     if Xs_list is not None:
-        if sparse:
+        if fourier:
+            out = eng.vff_predict(batch, vff, theta)
+            objective = np.asarray(out["elbo"])
+        elif sparse:
             out = eng.sgpr_predict(batch, inducing, theta)
             objective = np.asarray(out["elbo"])           # the sparse model reports +ELBO
         else:
@@ -641,7 +793,9 @@ def fit_predict_models(models: Sequence[B200GPRModel], pred_coords: Optional[Seq
             preds.append({"f*": out["f*"][sl].copy(), "f*_var": out["f*_var"][sl].copy(),
                           "y_var": out["y_var"][sl].copy(), "f_bar": m._f_bar(sl.stop - sl.start)})
     else:
-        if sparse:
+        if fourier:
+            objective = np.asarray(eng.vff_elbo(batch, vff, theta)[0])
+        elif sparse:
             objective = np.asarray(eng.sgpr_elbo(batch, inducing, theta)[0])
         else:
             lml, _, _ = eng.lml_grad(batch, theta, with_grad=False)

@@ -176,3 +176,38 @@ def test_sgpr_model_inducing_points():
         small.optimise_parameters(train_inducing_points=True)
     with pytest.raises(NotImplementedError):
         small.predict(np.zeros((1, 2)), full_cov=True)
+
+
+def test_vff_model_domain_and_parameters():
+    """vff_model.py:174-258: domain box widened to hold the data, per-dimension kernels, product
+    variance, D-th-root constraints, the reference's last-kernel quirk for fixed_params."""
+    from gpsat_b200.models import B200VFFModel
+    df = _df(30)
+    m = B200VFFModel(data=df, obs_col="obs", coords_col=["x", "y"], coords_scale=[5e4, 5e4],
+                     num_inducing_features=[6, 4], domain_size=[3e5, 1e3], expert_loc=np.array([0.0, 0.0]))
+    assert m.param_names == ["lengthscales", "kernel_variance", "likelihood_variance"]
+    np.testing.assert_array_equal(m.vff_nfreq, [6, 4])
+    assert m.num_features == 11 * 7
+    # dimension 0: the requested box (+-3e5 / 5e4 = +-6) contains the data; dimension 1: too small, widened
+    assert m.vff_a[0] == -6.0 and m.vff_b[0] == 6.0
+    assert m.vff_a[1] == m.coords[:, 1].min() - 1e-8 and m.vff_b[1] == m.coords[:, 1].max() + 1e-8
+    assert np.all(m.coords > m.vff_a) and np.all(m.coords < m.vff_b)
+    np.testing.assert_array_equal(m.get_lengthscales(), [1.0, 1.0])
+    assert m.get_kernel_variance() == 1.0 and m.get_likelihood_variance() == 1.0
+    m.set_kernel_variance(4.0)
+    np.testing.assert_allclose(m._theta[2:4], [2.0, 2.0])
+    assert abs(m.get_kernel_variance() - 4.0) < 1e-14
+    m.set_lengthscales([0.5, 2.0])
+    m.set_parameter_constraints({"lengthscales": {"low": [1e-3, 1e-3], "high": [1e5, 2e5], "scale": True},
+                                 "kernel_variance": {"low": 1e-4, "high": 9.0}})
+    np.testing.assert_allclose(m._tb[:2], [2.0, 4.0])                 # divided by coords_scale
+    np.testing.assert_allclose(m._ta[2:4], [1e-2, 1e-2])              # low ** (1 / D)
+    np.testing.assert_allclose(m._tb[2:4], [3.0, 3.0])
+    m._fix_hyperparameters(["lengthscales", "kernel_variance"])
+    np.testing.assert_array_equal(m._trainable, [True, False, True, False, True])
+    one = B200VFFModel(data=df, obs_col="obs", coords_col=["x"], num_inducing_features=5)
+    assert one.num_features == 9 and one.vff_a[0] == one.coords.min() - 1e-8        # domain_size=None
+    with pytest.raises(NotImplementedError):
+        B200VFFModel(data=df, obs_col="obs", coords_col=["x"], num_inducing_features=5, kernel="RBF")
+    with pytest.raises(AssertionError):
+        B200VFFModel(data=df, obs_col="obs", coords_col=["x"])

@@ -193,3 +193,35 @@ def test_sgpr_model_driver_sequence(engine, golden_dir):
     assert abs(p["f*_var"][0] - g["pred_std"][0] ** 2) < 1e-4
     with pytest.raises(NotImplementedError):
         m.optimise_parameters(train_inducing_points=True)
+
+
+def test_batched_helper_equals_loop(engine):
+    """fit_predict_models on sparse models == the per-model loop (same kernels, same order of sums)."""
+    import pandas as pd
+    from gpsat_b200.models import B200SGPRModel, fit_predict_models
+    rng = np.random.default_rng(4)
+
+    def build(seed):
+        r = np.random.default_rng(seed)
+        n = 300 + 40 * seed
+        xy = r.uniform(-2, 2, (n, 2))
+        df = pd.DataFrame({"x": xy[:, 0], "y": xy[:, 1],
+                           "obs": np.sin(2 * xy[:, 0]) + 0.3 * xy[:, 1] + 0.1 * r.standard_normal(n)})
+        np.random.seed(seed)
+        return B200SGPRModel(data=df, obs_col="obs", coords_col=["x", "y"], obs_mean="local",
+                             num_inducing_points=50, verbose=False)
+
+    pred = rng.uniform(-1.8, 1.8, (25, 2))
+    loop = [build(s) for s in (1, 2, 3)]
+    loop_ok = [m.optimise_parameters() for m in loop]
+    loop_obj = [m.get_objective_function_value() for m in loop]
+    loop_pred = [m.predict(pred) for m in loop]
+    batch = [build(s) for s in (1, 2, 3)]
+    ok_b, obj_b, pred_b = fit_predict_models(batch, [pred] * 3)
+    assert list(ok_b) == loop_ok
+    for e in range(3):
+        np.testing.assert_array_equal(batch[e].get_inducing_points(), loop[e].get_inducing_points())
+        np.testing.assert_allclose(batch[e]._theta, loop[e]._theta, rtol=1e-12)
+        assert abs(obj_b[e] - loop_obj[e]) <= 1e-12 * abs(loop_obj[e])
+        np.testing.assert_allclose(pred_b[e]["f*"], loop_pred[e]["f*"], rtol=1e-12, atol=1e-14)
+        np.testing.assert_allclose(pred_b[e]["f*_var"], loop_pred[e]["f*_var"], rtol=1e-12, atol=1e-14)

@@ -142,3 +142,60 @@ def test_bad_inputs(engine):
     big = dict(ex, nfreq=np.array([65], dtype=np.int32))
     with pytest.raises(RuntimeError):
         engine.vff_elbo(_batch("Matern32", [big]), _dom([big]), theta)           # > 128 features / dim
+
+
+def test_vff_model_driver_sequence_and_batched(engine):
+    """B200VFFModel through the call order of LocalExpertOI.run (local_experts.py:1043-1164), against
+    the oracle driven the same way; then the batched helper against the per-model loop."""
+    import pandas as pd
+    from gpsat_b200.models import B200VFFModel, fit_predict_models
+    rng = np.random.default_rng(8)
+    cs = np.array([5e4, 5e4])
+
+    def make(seed):
+        r = np.random.default_rng(seed)
+        n = 250
+        xy = r.uniform(-1.5e5, 1.5e5, (n, 2))
+        obs = np.sin(xy[:, 0] / 6e4) + 0.4 * np.cos(xy[:, 1] / 5e4) + 0.1 * r.standard_normal(n) + 3.0
+        return pd.DataFrame({"x": xy[:, 0], "y": xy[:, 1], "obs": obs})
+
+    def build(df):
+        m = B200VFFModel(data=df, obs_col="obs", coords_col=["x", "y"], coords_scale=list(cs), obs_mean="local",
+                         num_inducing_features=[7, 6], domain_size=2.5e5, expert_loc=np.array([0.0, 0.0]),
+                         verbose=False)
+        m.set_parameter_constraints({"lengthscales": {"low": [1e-8, 1e-8], "high": [6e5, 6e5], "scale": True}},
+                                    move_within_tol=True, tol=1e-2)
+        return m
+
+    dfs = [make(s) for s in (1, 2, 3)]
+    pred = rng.uniform(-1.2e5, 1.2e5, (40, 2))
+    m = build(dfs[0])
+    assert m.optimise_parameters()
+    th = m._theta.copy()
+    # oracle on the same scaled data / domain / transforms
+    pre = vff.Precomputed(m.coords, m.obs[:, 0], m.vff_a, m.vff_b, [np.arange(k) for k in m.vff_nfreq])
+    tr = vff.Transform.vff_default(2)
+    tr.set_sigmoid(0, 1e-8 / cs[0], 6e5 / cs[0])
+    tr.set_sigmoid(1, 1e-8 / cs[1], 6e5 / cs[1])
+    tho, val, ok, _ = vff.fit("Matern32", pre, np.ones(5), tr)
+    assert ok
+    assert abs(m.get_objective_function_value() - val) < 1e-4 * abs(val)
+    np.testing.assert_allclose(m.get_lengthscales(), tho[:2], rtol=5e-3)
+    np.testing.assert_allclose(m.get_kernel_variance(), np.prod(tho[2:4]), rtol=5e-3)
+    p = m.predict(pred)
+    po = vff.predict("Matern32", pre, th, pred / cs)
+    np.testing.assert_allclose(p["f*"], po["f*"], rtol=1e-7, atol=1e-9)
+    np.testing.assert_allclose(p["f*_var"], po["f*_var"], rtol=1e-7, atol=1e-9)
+    np.testing.assert_allclose(p["f_bar"], np.full(40, dfs[0]["obs"].mean()))
+    # batched helper == loop
+    loop = [build(df) for df in dfs]
+    loop_ok = [mm.optimise_parameters() for mm in loop]
+    loop_obj = [mm.get_objective_function_value() for mm in loop]
+    loop_pred = [mm.predict(pred) for mm in loop]
+    batch = [build(df) for df in dfs]
+    ok_b, obj_b, pred_b = fit_predict_models(batch, [pred] * 3)
+    assert list(ok_b) == loop_ok
+    for e in range(3):
+        np.testing.assert_allclose(batch[e]._theta, loop[e]._theta, rtol=1e-12)
+        assert abs(obj_b[e] - loop_obj[e]) <= 1e-12 * abs(loop_obj[e])
+        np.testing.assert_allclose(pred_b[e]["f*"], loop_pred[e]["f*"], rtol=1e-12, atol=1e-14)
