@@ -27,6 +27,7 @@ EXPORTED_SYMBOLS = (
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
     "gpsat_sgpr_elbo", "gpsat_sgpr_predict", "gpsat_sgpr_fit",
     "gpsat_vff_elbo", "gpsat_vff_predict", "gpsat_vff_fit",
+    "gpsat_gaussian_smooth", "gpsat_glue_predictions",
 )
 
 
@@ -98,6 +99,9 @@ def load():
     lib.gpsat_vff_predict.argtypes = [vp, C.POINTER(Batch), C.POINTER(VffDomain), C.c_int, vp, vp, vp, vp, vp, vp]
     lib.gpsat_vff_fit.argtypes = [vp, C.POINTER(Batch), C.POINTER(VffDomain), C.c_int, vp, vp, vp, vp, vp,
                                   C.POINTER(FitOptions), C.POINTER(Priors), vp, vp, vp, vp, vp]
+    lib.gpsat_gaussian_smooth.argtypes = [vp, C.c_int, C.c_int64, vp, vp, C.c_int64, C.c_int64, vp, vp,
+                                          C.c_double, C.c_double, vp, vp]
+    lib.gpsat_glue_predictions.argtypes = [vp, C.c_int, C.c_int64, C.c_int64, vp, C.c_int, vp, vp, vp, C.c_int64, vp, vp]
     _lib = lib
     return lib
 

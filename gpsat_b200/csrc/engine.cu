@@ -85,6 +85,7 @@ struct SlotMem {
 }  // namespace gpsat
 #include "sgpr_kernels.cuh"
 #include "vff_kernels.cuh"
+#include "post_kernels.cuh"
 namespace gpsat {
 
 // ---- transforms (gpflow.utilities.positive / tfp.bijectors.Sigmoid) -------------------------

@@ -267,3 +267,5 @@ int gpsat_vff_fit(gpsat_engine* h, const gpsat_batch* batch, const gpsat_vff_dom
 }
 
 }  // extern "C"
+
+#include "engine_post.inl"

@@ -32,7 +32,32 @@ import numpy as np
 import pandas as pd
 from scipy.spatial import cKDTree
 
-from .models import B200GPRModel, fit_predict_models
+import importlib
+import warnings
+
+from .models import B200GPRModel, B200SGPRModel, B200VFFModel, fit_predict_models
+
+# model names accepted in ``model_config["oi_model"]``: this package's classes, and the names of the
+# reference classes they stand in for (``GPSat/models/__init__.py:3-28``)
+_MODEL_CLASSES = {"B200GPRModel": B200GPRModel, "B200SGPRModel": B200SGPRModel, "B200VFFModel": B200VFFModel,
+                  "GPflowGPRModel": B200GPRModel, "GPflowSGPRModel": B200SGPRModel, "GPflowVFFModel": B200VFFModel}
+
+
+def resolve_model(oi_model):
+    """``LocalExpertOI.set_model`` (``local_experts.py:309-330``): a name, a class, or
+    ``{"path_to_model": module, "model_name": class}``; the class must derive from ``B200GPRModel``
+    (the batched engine calls need its parameter layout)."""
+    if isinstance(oi_model, dict):
+        cls = getattr(importlib.import_module(oi_model["path_to_model"]), oi_model["model_name"])
+    elif isinstance(oi_model, str):
+        if oi_model not in _MODEL_CLASSES:
+            raise NotImplementedError(f"oi_model '{oi_model}' is not available in the batched driver; "
+                                      f"choose from {sorted(_MODEL_CLASSES)}")
+        cls = _MODEL_CLASSES[oi_model]
+    else:
+        cls = oi_model
+    assert isinstance(cls, type) and issubclass(cls, B200GPRModel), "the batched driver runs B200GPRModel subclasses"
+    return cls
 
 _COMPS = {">=": np.greater_equal, ">": np.greater, "==": np.equal, "<": np.less, "<=": np.less_equal}
 
@@ -118,8 +143,11 @@ def dict_to_tables(x: dict, ref_loc: dict, table: Optional[str] = None) -> Dict[
         v = np.asarray(v)
         if v.ndim == 0:
             df = pd.DataFrame({k: [v.item()]})
-        else:
+        elif v.ndim == 1:
             df = pd.DataFrame({"_dim_0": np.arange(len(v)), k: v})
+        else:                                   # n-d (inducing points): one _dim_i column per axis, C order
+            grid = np.indices(v.shape).reshape(v.ndim, -1)
+            df = pd.DataFrame({**{f"_dim_{i}": grid[i] for i in range(v.ndim)}, k: v.reshape(-1)})
         df.index = index(len(df))
         out[k] = df
     return out
@@ -143,8 +171,8 @@ class LocalExpertOI:
         self.coords_col = list(data_config["coords_col"])
         self.local_select = data_config["local_select"]
         mc = dict(model_config or {})
-        oi_model = mc.get("oi_model", "B200GPRModel")
-        assert oi_model in ("B200GPRModel", B200GPRModel), "the batched driver runs B200GPRModel experts"
+        self.model_cls = resolve_model(mc.get("oi_model", "B200GPRModel"))
+        self.load_params = mc.get("load_params")
         self.init_params = dict(mc.get("init_params") or {})
         self.constraints = mc.get("constraints")
         self.optim_kwargs = dict(mc.get("optim_kwargs") or {})
@@ -165,6 +193,57 @@ class LocalExpertOI:
             cons["lengthscales"]["scale"] = True
         return cons
 
+    # ---- load_params (local_experts.py:553-689) ---------------------------------------------------
+    def _param_lookup(self, param_names):
+        """{param: {expert location tuple: values ordered by _dim_*}} from the configured tables."""
+        lp = self.load_params
+        if not lp:
+            return None
+        if lp.get("index_adjust"):
+            raise NotImplementedError("load_params.index_adjust is not implemented in the batched driver")
+        suffix = lp.get("table_suffix", "")
+        names = lp.get("param_names") or param_names
+        for pn in names:
+            assert pn in param_names, f"provide param name:{pn}\nis not in param_names:{param_names}"
+        tables = lp.get("tables")
+        if tables is None:
+            assert isinstance(lp.get("file"), str), "load_params needs 'tables' or 'file'"
+            with pd.HDFStore(lp["file"], mode="r") as store:              # needs PyTables, like the reference
+                tables = {f"{k}{suffix}": store.select(f"{k}{suffix}") for k in names if f"/{k}{suffix}" in store.keys()}
+        lookup = {}
+        for k in names:
+            df = tables.get(f"{k}{suffix}")
+            if df is None:
+                print(f"KeyError\n 'No object named {k}{suffix}'\nskipping param_name: {k}")
+                continue
+            df = df.reset_index(drop=False) if df.index.names != [None] else df
+            keys = [c for c in self.coords_col if c in df.columns]
+            dim_cols = sorted(c for c in df.columns if c.startswith("_dim_"))
+            per = {}
+            for loc, sub in df.groupby(keys, sort=False):
+                loc = loc if isinstance(loc, tuple) else (loc,)
+                sub = sub.sort_values(dim_cols) if dim_cols else sub
+                v = sub[k].values.astype(np.float64)
+                if len(dim_cols) > 1:                  # n-d parameter: back to its array shape
+                    v = v.reshape([int(sub[c].max()) + 1 for c in dim_cols])
+                per[tuple(float(x) for x in loc)] = v if dim_cols else float(v[0])
+            lookup[k] = (keys, per)
+        return lookup
+
+    @staticmethod
+    def _params_for(lookup, ref: dict) -> dict:
+        out = {}
+        for k, (keys, per) in lookup.items():
+            v = per.get(tuple(float(ref[c]) for c in keys))
+            if v is None:
+                warnings.warn(f"\n******\nno parameters found in table:\n{k}\nfor location:\n{ref}\n******")
+                continue
+            if np.any(np.isnan(v)):
+                warnings.warn(f"\n{k}: found some nans for ref location: {ref}, removing those parameters")
+                continue
+            out[k] = v
+        return out
+
     def run(self, store_path: Optional[str] = None, optimise: bool = True, predict: bool = True,
             min_obs: int = 3, table_suffix: str = "", config_id: int = 1) -> Dict[str, pd.DataFrame]:
         """All experts: select, fit, predict, tabulate.  Returns ``{table name: DataFrame}`` with the
@@ -180,6 +259,7 @@ class LocalExpertOI:
             pred_cols = [c for c in coords_col if c in self.pred_df]
             pred_tree = cKDTree(self.pred_df[pred_cols].values)
         cons = self._constraints_for_model()
+        lookup = None
         models, pcs, refs, skipped = [], [], [], []
         for _, rl in self.expert_locs.iterrows():
             ref = {c: rl[c] for c in coords_col}
@@ -190,8 +270,14 @@ class LocalExpertOI:
             if len(df_local) < min_obs:
                 skipped.append((ref, len(df_local)))       # local_experts.py:988-1012
                 continue
-            m = B200GPRModel(data=df_local, obs_col=self.obs_col, coords_col=coords_col,
-                             expert_loc=np.array([ref[c] for c in coords_col]), verbose=False, **self.init_params)
+            m = self.model_cls(data=df_local, obs_col=self.obs_col, coords_col=coords_col,
+                               expert_loc=np.array([ref[c] for c in coords_col]), verbose=False, **self.init_params)
+            if self.load_params:                            # before the constraints, local_experts.py:1065-1115
+                if lookup is None:
+                    lookup = self._param_lookup(m.param_names)
+                loaded = self._params_for(lookup, ref)
+                if loaded:
+                    m.set_parameters(**loaded)
             if cons is not None:
                 m.set_parameter_constraints(cons, move_within_tol=True, tol=1e-2)
             models.append(m); pcs.append(pc); refs.append(ref)
@@ -211,7 +297,7 @@ class LocalExpertOI:
             for k, v in tabs.items():
                 frames.setdefault(k + table_suffix, []).append(v)
 
-        model_name = f"{B200GPRModel.__module__}.{B200GPRModel.__name__}"[:64]
+        model_name = f"{self.model_cls.__module__}.{self.model_cls.__name__}"[:64]
         for ref, nobs in skipped:
             add(dict_to_tables({"num_obs": nobs, "run_time": np.nan, "objective_value": np.nan,
                                 "parameters_optimised": optimise, "optimise_success": False, "model": model_name,

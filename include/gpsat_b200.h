@@ -218,6 +218,23 @@ int gpsat_vff_fit(gpsat_engine* eng, const gpsat_batch* batch, const gpsat_vff_d
                   const uint8_t* trainable, const gpsat_fit_options* opt, const gpsat_priors* priors,
                   double* objective, double* elbo, int32_t* n_evals, int32_t* n_iters, int32_t* status);
 
+/* ---- post-processing reductions (the "next" rows of the local-expert workflow) ------------------
+ * gaussian_2d_weight, the kernel of smooth_hyperparameters (GPSat/postprocessing.py:22-52, 96-395):
+ * for F fields given at the same n positions (vals: [F][n]) and n0 reference positions (out: [F][n0]),
+ *   out[f][i] = sum_j w_ij vals[f][j] / sum_j w_ij over non-NaN vals[f][j],
+ *   w_ij = exp(-(((x_j - x0_i) / lx)^2 + ((y_j - y0_i) / ly)^2) / 2);  NaN when the weights sum to 0. */
+int gpsat_gaussian_smooth(gpsat_engine* eng, int mem, int64_t n0, const double* x0, const double* y0,
+                          int64_t n, int64_t F, const double* x, const double* y, double lx, double ly,
+                          const double* vals, double* out);
+
+/* glue_local_predictions_1d / _2d (GPSat/postprocessing.py:462-593): rows sorted by prediction
+ * location, group g = rows seg[g] .. seg[g+1) (seg: HOST array [G+1]); pred, xprt: [ndim][n]
+ * prediction / expert coordinates, sigma [n] = inference_radius / R, vals [V][n]:
+ *   w_i = prod_d normal_pdf(pred[d][i]; xprt[d][i], sigma[i]),  out[v][g] = sum w vals[v] / sum w. */
+int gpsat_glue_predictions(gpsat_engine* eng, int mem, int64_t n, int64_t G, const int64_t* seg, int ndim,
+                           const double* pred, const double* xprt, const double* sigma, int64_t V,
+                           const double* vals, double* out);
+
 /* Test hook (single expert, host memory): dense factor of the augmented matrix.
  * Lout [(n+1)*(n+1)] row-major lower: rows < n = chol(K + s2 I), row n = (L^-1 y)^T, 1.
  * Uout [(n+1)*(n+1)] row-major upper: L_aug^-T (may be NULL). */

@@ -17,6 +17,10 @@ Three independent sources pin the oracle (and through it the CUDA path):
    reference tree, and the static quantities ``GPR_kron.__init__`` derives from them (``:600-610``).
    The TensorFlow parts of vff.py (``make_Kuu``, ``elbo``, ``predict_f``) cannot run here.
 
+5. ``post_smooth.npz`` / ``post_glue.npz`` - the reference's own ``gaussian_2d_weight`` (numba),
+   ``glue_local_predictions_1d`` and ``_2d`` (``/root/reference/GPSat/postprocessing.py:22-52,
+   462-593``) executed from the reference source on seeded inputs.
+
 Usage:  python oracle/make_golden.py
 """
 from __future__ import annotations
@@ -149,9 +153,47 @@ def vff_features():
     print("vff Kuf:", Kuf.shape)
 
 
+def postprocessing():
+    import numba as nb
+    import pandas as pd
+    from typing import Dict, List, Union
+    from scipy.stats import norm
+    path = os.path.join(REF, "GPSat", "postprocessing.py")
+    tree = ast.parse(open(path).read())
+    wanted = {"gaussian_2d_weight", "glue_local_predictions_1d", "glue_local_predictions_2d"}
+    body = [n for n in tree.body if isinstance(n, ast.FunctionDef) and n.name in wanted]
+    ns = {"np": np, "nb": nb, "pd": pd, "norm": norm, "Union": Union, "List": List, "Dict": Dict}
+    exec(compile(ast.Module(body=body, type_ignores=[]), path, "exec"), ns)
+    rng = np.random.default_rng(99)
+    n = 60
+    x, y = rng.uniform(-5e5, 5e5, n), rng.uniform(-5e5, 5e5, n)
+    vals = rng.uniform(0.5, 3.0, n)
+    vals[[3, 17, 40]] = np.nan
+    sm = ns["gaussian_2d_weight"](x, y, x, y, 2e5, 1e5, vals)
+    far = ns["gaussian_2d_weight"](np.array([1e9]), np.array([1e9]), x, y, 1.0, 1.0, vals)     # all weights underflow
+    np.savez(os.path.join(OUT, "post_smooth.npz"), x=x, y=y, vals=vals, l_x=2e5, l_y=1e5, out=sm, far=far)
+    # overlapping experts on a grid, predictions on shared locations
+    rows = []
+    for ex in (0.0, 100.0, 200.0):
+        for ey in (0.0, 100.0):
+            for px in np.arange(ex - 100, ex + 101, 50.0):
+                for py in np.arange(ey - 100, ey + 101, 50.0):
+                    rows.append((ex, ey, px, py, rng.normal(), rng.uniform(0.1, 1.0)))
+    df = pd.DataFrame(rows, columns=["x", "y", "pred_loc_x", "pred_loc_y", "f*", "f*_var"])
+    g2 = ns["glue_local_predictions_2d"](df, ["pred_loc_x", "pred_loc_y"], ["x", "y"], ["f*", "f*_var"], 150.0, R=3)
+    d1 = df[df["y"] == 0.0]
+    radius = {0.0: 150.0, 100.0: 120.0, 200.0: 90.0}
+    g1 = ns["glue_local_predictions_1d"](d1, "pred_loc_x", "x", ["f*", "f*_var"], radius, R=2)
+    np.savez(os.path.join(OUT, "post_glue.npz"), df=df.values, cols=np.array(df.columns), g2=g2.values,
+             g2cols=np.array(g2.columns), g1=g1.values, g1cols=np.array(g1.columns),
+             radius_keys=np.array(list(radius.keys())), radius_vals=np.array(list(radius.values())))
+    print("postprocessing:", sm[:3], far, g2.shape, g1.shape)
+
+
 if __name__ == "__main__":
     os.makedirs(OUT, exist_ok=True)
     kat_localexperts()
     pure_python()
     sklearn_ard()
     vff_features()
+    postprocessing()

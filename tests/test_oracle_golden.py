@@ -243,3 +243,22 @@ def test_vff_edge_features_and_fit():
     th0 = np.ones(3)
     th, val, ok, nfev = vff.fit("Matern32", pre, th0)
     assert ok and val > vff.elbo("Matern32", pre, th0) and nfev > 3
+
+
+# ---- post-processing (oracle/postprocessing.py) ---------------------------------------------------
+def test_postprocessing_oracle_matches_reference_functions(golden_dir):
+    """gaussian_2d_weight / glue_local_predictions_1d / _2d of /root/reference/GPSat/postprocessing.py
+    (:22-52, :462-593), executed from the reference source by oracle/make_golden.py."""
+    import pandas as pd
+    from oracle import postprocessing as pp
+    g = np.load(os.path.join(golden_dir, "post_smooth.npz"))
+    np.testing.assert_allclose(pp.gaussian_2d_weight(g["x"], g["y"], g["x"], g["y"], float(g["l_x"]), float(g["l_y"]),
+                                                     g["vals"]), g["out"], rtol=1e-13)
+    assert np.isnan(pp.gaussian_2d_weight([1e9], [1e9], g["x"], g["y"], 1.0, 1.0, g["vals"])[0]) and np.isnan(g["far"][0])
+    q = np.load(os.path.join(golden_dir, "post_glue.npz"), allow_pickle=True)
+    df = pd.DataFrame(q["df"], columns=list(q["cols"]))
+    g2 = pp.glue_2d(df, ["pred_loc_x", "pred_loc_y"], ["x", "y"], ["f*", "f*_var"], 150.0, R=3)
+    np.testing.assert_allclose(g2[list(q["g2cols"])].values, q["g2"], rtol=1e-13)
+    radius = dict(zip(q["radius_keys"].tolist(), q["radius_vals"].tolist()))
+    g1 = pp.glue_1d(df[df["y"] == 0.0], "pred_loc_x", "x", ["f*", "f*_var"], radius, R=2)
+    np.testing.assert_allclose(g1[list(q["g1cols"])].values, q["g1"], rtol=1e-13)
