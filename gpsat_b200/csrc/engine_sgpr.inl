@@ -21,6 +21,7 @@ static SgprLay sgpr_layout(int npad, int mpad, int Mp, int nsplit, bool with_gra
   take(L.gam, with_grad ? Mp : 0); take(L.bid, with_grad ? Mp : 0); take(L.res, with_grad ? npad : 0);
   take(L.rrp, with_grad ? npad / SGPR_RES_ROWS : 0);
   take(L.gpc, with_grad ? (size_t)(npad / NB) * MT * PG : 0); take(L.gpk, with_grad ? (size_t)MT * MT * PG : 0);
+  take(L.sums, SGPR_NSUMS);
   take(L.cts, with_pred ? pm : 0); take(L.t1, with_pred ? pm : 0); take(L.t2, with_pred ? pm : 0);
   take(L.ak, mm); take(L.ab, mm);
   take(L.side_k, side); take(L.side_b, side);
@@ -130,6 +131,8 @@ static int sgpr_launch_eval(Engine& g, const SgprCall& c, bool with_grad, bool w
     gemm(SGPR_GEMM_GK, MT * MT, 1);
     g.stats.kernel_launches += 3;
   }
+  sgpr_sums_kernel<<<S, 256, 0, st>>>(dd, with_grad ? 1 : 0);
+  g.stats.kernel_launches++;
   if (with_pred) {
     kuf_build_kernel<<<dim3(PT, MT, S), GPSAT_THREADS, 0, st>>>(dd, 1);
     gemm(SGPR_GEMM_T1, PT * MT, 1);

@@ -58,6 +58,7 @@ struct SgprDesc {
   double* rrp;           // [npad / 64]  partial sums of r'r
   double* gpc;           // [npad/128 * Mp/128][8] partial gradient sums of the Kuf term
   double* gpk;           // [(Mp/128)^2][8]        partial gradient sums of the Kuu term
+  double* sums;          // [12] block-reduced scalars of one evaluation (sgpr_sums_kernel)
   double* Cts;           // [mpad][Mp]
   double* T1;            // [mpad][Mp]
   double* T2;            // [mpad][Mp]
@@ -65,7 +66,7 @@ struct SgprDesc {
 
 // Offsets (in doubles) of one slot's workspace; the same for every slot of a call.
 struct SgprLay {
-  size_t ct, aq, at, w, u, wb, ub, bm, binv, q, tt, part, gam, bid, res, rrp, gpc, gpk, cts, t1, t2, ak, ab,
+  size_t ct, aq, at, w, u, wb, ub, bm, binv, q, tt, part, gam, bid, res, rrp, gpc, gpk, sums, cts, t1, t2, ak, ab,
       side_k, side_b, total, tile_d;
   int Tmax, lgd;         // tiles per side of the M x M slots; aligned length of logdet[]
 };
@@ -109,7 +110,8 @@ __device__ __forceinline__ void sgpr_set_expert(SgprDesc& d, SlotDesc& k, SlotDe
   d.Ct = base + L.ct; d.Aq = base + L.aq; d.At = base + L.at; d.W = base + L.w; d.U = base + L.u;
   d.WB = base + L.wb; d.UB = base + L.ub; d.Bm = base + L.bm; d.Binv = base + L.binv; d.Q = base + L.q;
   d.TT = base + L.tt; d.part = base + L.part; d.gam = base + L.gam; d.bid = base + L.bid; d.res = base + L.res;
-  d.rrp = base + L.rrp; d.gpc = base + L.gpc; d.gpk = base + L.gpk; d.Cts = base + L.cts; d.T1 = base + L.t1;
+  d.rrp = base + L.rrp; d.gpc = base + L.gpc; d.gpk = base + L.gpk; d.sums = base + L.sums;
+  d.Cts = base + L.cts; d.T1 = base + L.t1;
   d.T2 = base + L.t2;
   sgpr_fill_slot(k, e, d.M, d.kind, d.D, base + L.ak, base + L.side_k, L);
   k.X = d.Z; k.y = in.zero;
@@ -541,32 +543,58 @@ __global__ void __launch_bounds__(256) sgpr_q_kernel(const SgprDesc* __restrict_
   }
 }
 
+// Block-reduced scalars of one evaluation, one CTA per slot, fixed summation order:
+//   sums[p], p = 0..8 : sum over the tiles of gpc + gpk (gradient partial sums; with_grad)
+//   sums[9] = r'r, sums[10] = tr B^-1 (with_grad), sums[11] = tr B
+constexpr int SGPR_NSUMS = 12;
+__global__ void __launch_bounds__(256) sgpr_sums_kernel(const SgprDesc* __restrict__ descs, int with_grad) {
+  const SgprDesc& d = descs[blockIdx.x];
+  if (d.expert < 0) return;
+  const int tid = threadIdx.x;
+  double acc[SGPR_NSUMS];
+#pragma unroll
+  for (int p = 0; p < SGPR_NSUMS; ++p) acc[p] = 0.0;
+  for (int u = tid; u < d.M; u += 256) acc[11] += d.Bm[(size_t)u * d.Mp + u];
+  if (with_grad) {
+    const int MT = d.Mp / NB, ntc = (d.npad / NB) * MT, ntk = MT * MT;
+    for (int t = tid; t < ntc; t += 256)
+#pragma unroll
+      for (int p = 0; p <= GPSAT_DMAX; ++p) acc[p] += d.gpc[(size_t)t * (GPSAT_DMAX + 2) + p];
+    for (int t = tid; t < ntk; t += 256)
+#pragma unroll
+      for (int p = 0; p <= GPSAT_DMAX; ++p) acc[p] += d.gpk[(size_t)t * (GPSAT_DMAX + 2) + p];
+    for (int q = tid; q < d.npad / SGPR_RES_ROWS; q += 256) acc[9] += d.rrp[q];
+    for (int u = tid; u < d.M; u += 256) acc[10] += d.bid[u];
+  }
+  __shared__ double red[256];
+  for (int p = 0; p < SGPR_NSUMS; ++p) {
+    red[tid] = acc[p];
+    __syncthreads();
+    for (int h = 128; h > 0; h >>= 1) {
+      if (tid < h) red[tid] += red[tid + h];
+      __syncthreads();
+    }
+    if (tid == 0) d.sums[p] = red[0];
+    __syncthreads();
+  }
+}
+
 // elbo (gpflow.models.SGPR.elbo) and, with_grad, d elbo / d theta from the by-products of one
-// evaluation; every sum runs in a fixed order.  Returns -inf when a factorisation failed.
+// evaluation (after sgpr_sums_kernel).  Returns -inf when a factorisation failed.
 __device__ __forceinline__ double sgpr_finish_eval(const SgprDesc& d, const SlotDesc& sk, const SlotDesc& sb,
                                                    double* gtheta, bool with_grad) {
   double logdet = 0.0;
   for (int t = 0; t < sb.T; ++t) logdet += sb.logdet[t];
-  double trB = 0.0;
-  for (int u = 0; u < d.M; ++u) trB += d.Bm[(size_t)u * d.Mp + u];
+  const double trB = d.sums[11];
   const double yy = d.Bm[(size_t)d.M * d.Mp + d.M];          // y'y / s2
   const double n = (double)d.n, s2 = d.noise;
   double v = -0.5 * n * 1.8378770664093453 - logdet - 0.5 * n * log(s2) - 0.5 * yy + 0.5 * (*sb.quad) -
              0.5 * n * d.var / s2 + 0.5 * (trB - (double)d.M);
   const bool bad = *sk.notpd || *sb.notpd;
   if (with_grad) {
-    const int MT = d.Mp / NB, ntc = (d.npad / NB) * MT, ntk = MT * MT;
-    double s[GPSAT_DMAX + 2];
-    for (int p = 0; p < GPSAT_DMAX + 2; ++p) s[p] = 0.0;
-    for (int t = 0; t < ntc; ++t)
-      for (int p = 0; p <= GPSAT_DMAX; ++p) s[p] += d.gpc[(size_t)t * (GPSAT_DMAX + 2) + p];
-    for (int t = 0; t < ntk; ++t)
-      for (int p = 0; p <= GPSAT_DMAX; ++p) s[p] += d.gpk[(size_t)t * (GPSAT_DMAX + 2) + p];
-    double rr = 0.0, trBinv = 0.0;
-    for (int q = 0; q < d.npad / SGPR_RES_ROWS; ++q) rr += d.rrp[q];
-    for (int u = 0; u < d.M; ++u) trBinv += d.bid[u];
-    for (int k = 0; k < d.D; ++k) gtheta[k] = d.var * s[k] * d.inv_ls[k];
-    gtheta[d.D] = s[GPSAT_DMAX] - 0.5 * n / s2;
+    const double rr = d.sums[9], trBinv = d.sums[10];
+    for (int k = 0; k < d.D; ++k) gtheta[k] = d.var * d.sums[k] * d.inv_ls[k];
+    gtheta[d.D] = d.sums[GPSAT_DMAX] - 0.5 * n / s2;
     gtheta[d.D + 1] = -0.5 * n / s2 + 0.5 * (rr + n * d.var - s2 * (trB - 2.0 * d.M + trBinv)) / (s2 * s2);
   }
   return bad ? -INFINITY : v;

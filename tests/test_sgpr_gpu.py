@@ -225,3 +225,24 @@ def test_batched_helper_equals_loop(engine):
         assert abs(obj_b[e] - loop_obj[e]) <= 1e-12 * abs(loop_obj[e])
         np.testing.assert_allclose(pred_b[e]["f*"], loop_pred[e]["f*"], rtol=1e-12, atol=1e-14)
         np.testing.assert_allclose(pred_b[e]["f*_var"], loop_pred[e]["f*_var"], rtol=1e-12, atol=1e-14)
+
+
+def test_full_size_c5_expert(engine):
+    """One expert at the c5 shape (n = 20 000, M = 500, 3-D): ELBO, gradient and predictions against
+    the oracle (a few seconds of LAPACK on the host)."""
+    from gpsat_b200 import synthetic as syn
+    spec = syn.WorkloadSpec("c5", 1, 20000, 20000, 300, 300, 500e3, 15, (25e3, 25e3, 1.0), (600e3, 600e3, 30.0))
+    X, y, Xs = syn.make_expert(spec, 0, 5)
+    Z = X[np.random.default_rng(1).permutation(len(X))[:500]].copy()
+    theta = np.array([[4.0, 4.0, 5.0, 0.05, 0.005]])
+    b = _batch("Matern32", [(X, y, Xs)])
+    elbo, grad, status = engine.sgpr_elbo(b, [Z], theta, with_grad=True)
+    v, g = sgpr.elbo_and_grad("Matern32", X, y, Z, theta[0])
+    assert status[0] == 0 and abs(elbo[0] - v) <= 1e-7 * abs(v)
+    _, g2 = sgpr.elbo_and_grad("Matern32", X * (1 + 1e-15), y, Z * (1 + 1e-15), theta[0])
+    atol = max(1e-6 * np.abs(g).max(), 100 * np.abs(g - g2).max())
+    np.testing.assert_allclose(grad[0], g, rtol=1e-6, atol=atol)
+    out = engine.sgpr_predict(b, [Z], theta)
+    p = sgpr.predict("Matern32", X, y, Z, theta[0], Xs)
+    np.testing.assert_allclose(out["f*"], p["f*"], rtol=1e-6, atol=1e-8)
+    np.testing.assert_allclose(out["f*_var"], p["f*_var"], rtol=1e-6, atol=1e-9)
