@@ -286,9 +286,9 @@ enum SgprGemmMode : int {
   SGPR_GEMM_SYRK = 1,  // part[split] = Aq Aq^T over one k range, lower tiles
   SGPR_GEMM_T1 = 2,    // T1[mpad][Mp] = Cts W^T                      (k <= column tile)
   SGPR_GEMM_T2 = 3,    // T2[mpad][Mp] = T1 WB^T                      (k <= column tile)
-  SGPR_GEMM_V = 4,     // Vt[npad][Mp] = At WB^T                      (k <= column tile)
-  SGPR_GEMM_H = 5,     // Ht[npad][Mp] = (At - Vt UB^T) / sigma + r gamma^T / s2     (k >= column tile)
-  SGPR_GEMM_GC = 6,    // G_C^T tile = Ht U^T, contracted with dKuf/dtheta -> gpc     (k >= column tile)
+  SGPR_GEMM_V = 4,     // V = WB At^T, stored as Vt[npad][Mp]         (k <= row tile, last block triangular)
+  SGPR_GEMM_H = 5,     // UB Vt^T -> Ht[npad][Mp] = (At - Vt UB^T) / sigma + r gamma^T / s2   (k >= row tile)
+  SGPR_GEMM_GC = 6,    // G_C tile = U Ht^T, contracted with dKuf/dtheta -> gpc                (k >= row tile)
   SGPR_GEMM_BINV = 7,  // Binv = UB UB^T, lower tiles                 (k >= row tile)
   SGPR_GEMM_TT = 8,    // TT = U Q                                    (k >= row tile)
   SGPR_GEMM_GK = 9     // G_K tile = 1/2 U TT^T, contracted with dKuu/dtheta -> gpk   (k >= row tile)
@@ -311,13 +311,14 @@ sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit, int w
   const double *Aop, *Bop;
   double* out = nullptr;
   int ldg, ldo = Mp, rt, ct, kbeg = 0, kend = Mp;
+  bool tri_first = false, tri_last = false;
   switch (mode) {
     case SGPR_GEMM_A: {
       const int nct = d.npad / NB;
       if (tile >= MT * nct) return;
       rt = tile / nct; ct = tile - rt * nct;
       Aop = d.W; Bop = d.Ct; ldg = Mp; out = d.Aq; ldo = d.npad;
-      kend = (rt + 1) * NB;
+      kend = (rt + 1) * NB; tri_last = true;
       break;
     }
     case SGPR_GEMM_SYRK: {
@@ -329,28 +330,38 @@ sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit, int w
       kend = min(d.npad, kbeg + SGPR_KCHUNK);
       break;
     }
-    case SGPR_GEMM_T1: case SGPR_GEMM_T2: case SGPR_GEMM_V: case SGPR_GEMM_H: case SGPR_GEMM_GC: {
-      const int nrt = ((mode == SGPR_GEMM_T1 || mode == SGPR_GEMM_T2) ? d.mpad : d.npad) / NB;
+    case SGPR_GEMM_V: case SGPR_GEMM_H: case SGPR_GEMM_GC: {
+      // M-side operand (triangular) as A, data-side operand as B: the tile is the transpose of the
+      // [n][M] quantity it stands for, and the skipped half of the triangular 128-block is skipped
+      // by row fragments (balanced over the four schedulers)
+      const int nct = d.npad / NB;
+      if (tile >= MT * nct) return;
+      rt = tile / nct; ct = tile - rt * nct;
+      ldg = Mp;
+      if (mode == SGPR_GEMM_V) { Aop = d.WB; Bop = d.At; kend = (rt + 1) * NB; tri_last = true; }
+      else if (mode == SGPR_GEMM_H) { Aop = d.UB; Bop = d.Aq; kbeg = rt * NB; tri_first = true; }
+      else { Aop = d.U; Bop = d.Ct; kbeg = rt * NB; tri_first = true; }
+      break;
+    }
+    case SGPR_GEMM_T1: case SGPR_GEMM_T2: {
+      const int nrt = d.mpad / NB;
       if (tile >= nrt * MT) return;
       rt = tile / MT; ct = tile - rt * MT;
       ldg = Mp;
       if (mode == SGPR_GEMM_T1) { Aop = d.Cts; Bop = d.W; out = d.T1; kend = (ct + 1) * NB; }
-      else if (mode == SGPR_GEMM_T2) { Aop = d.T1; Bop = d.WB; out = d.T2; kend = (ct + 1) * NB; }
-      else if (mode == SGPR_GEMM_V) { Aop = d.At; Bop = d.WB; out = d.Aq; kend = (ct + 1) * NB; }
-      else if (mode == SGPR_GEMM_H) { Aop = d.Aq; Bop = d.UB; out = d.Ct; kbeg = ct * NB; }
-      else { Aop = d.Ct; Bop = d.U; kbeg = ct * NB; }
+      else { Aop = d.T1; Bop = d.WB; out = d.T2; kend = (ct + 1) * NB; }
       break;
     }
     case SGPR_GEMM_BINV: {
       if (tile >= MT * (MT + 1) / 2) return;
       tri_tile(tile, rt, ct);
-      Aop = d.UB; Bop = d.UB; ldg = Mp; out = d.Binv; kbeg = rt * NB;
+      Aop = d.UB; Bop = d.UB; ldg = Mp; out = d.Binv; kbeg = rt * NB; tri_first = true;
       break;
     }
     default: {
       if (tile >= MT * MT) return;
       rt = tile / MT; ct = tile - rt * MT;
-      ldg = Mp; kbeg = rt * NB;
+      ldg = Mp; kbeg = rt * NB; tri_first = true;
       Aop = d.U;
       if (mode == SGPR_GEMM_TT) { Bop = d.Q; out = d.TT; }
       else Bop = d.TT;
@@ -369,21 +380,21 @@ sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit, int w
   const double* Bg = Bop + (size_t)ct * NB * ldg;
   gemm_nt_prologue(Ag, Bg, ldg, kbeg, kend, smem, tid);
   if (mode == SGPR_GEMM_GC) {
-    load_scaled_coords(d.X, d.n, d.D, d.inv_ls, rt * NB, xr, tid);
-    load_scaled_coords(d.Z, d.M, d.D, d.inv_ls, ct * NB, xc, tid);
+    load_scaled_coords(d.Z, d.M, d.D, d.inv_ls, rt * NB, xr, tid);
+    load_scaled_coords(d.X, d.n, d.D, d.inv_ls, ct * NB, xc, tid);
   } else if (mode == SGPR_GEMM_GK) {
     load_scaled_coords(d.Z, d.M, d.D, d.inv_ls, rt * NB, xr, tid);
     load_scaled_coords(d.Z, d.M, d.D, d.inv_ls, ct * NB, xc, tid);
   }
-  gemm_nt_mainloop(acc, Ag, Bg, ldg, kbeg, kend, smem, tid);
+  gemm_nt_mainloop(acc, Ag, Bg, ldg, kbeg, kend, smem, tid, tri_first, tri_last);
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3, lr = lane >> 2, lk = lane & 3;
 
   if (mode == SGPR_GEMM_GC || mode == SGPR_GEMM_GK) {
     // ---- contraction epilogue: the tile of G never leaves the SM ----
     acc_to_smem(acc, Cs, tid, mode == SGPR_GEMM_GK ? 0.5 : 1.0);
     __syncthreads();
-    const int nr = min(NB, max(0, (mode == SGPR_GEMM_GC ? d.n : d.M) - rt * NB));
-    const int nc = min(NB, max(0, d.M - ct * NB));
+    const int nr = min(NB, max(0, d.M - rt * NB));
+    const int nc = min(NB, max(0, (mode == SGPR_GEMM_GC ? d.n : d.M) - ct * NB));
     double part[GPSAT_DMAX + 2];
     cross_grad_tile(d.kind, d.D, xr, xc, nr, nc, Cs, tid, part);
 #pragma unroll
@@ -398,26 +409,40 @@ sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit, int w
       double v = 0.0;
       for (int w8 = 0; w8 < 8; ++w8) v += red[w8 * 8 + tid];
       double* gp = (mode == SGPR_GEMM_GC) ? d.gpc : d.gpk;
-      gp[(size_t)(rt * MT + ct) * (GPSAT_DMAX + 2) + tid] = v;
+      const int ncols = (mode == SGPR_GEMM_GC) ? d.npad / NB : MT;
+      gp[(size_t)(rt * ncols + ct) * (GPSAT_DMAX + 2) + tid] = v;
     }
     return;
   }
 
   const int row0 = rt * NB + wm * 64 + lr, col0 = ct * NB + wn * 32 + 2 * lk;
+  if (mode == SGPR_GEMM_V) {
+    // tile (u, i) of V = WB A, stored as Vt[i][u] (lanes with equal lk write 8 consecutive doubles)
+#pragma unroll
+    for (int fm = 0; fm < 8; ++fm)
+#pragma unroll
+      for (int fn = 0; fn < 4; ++fn) {
+        double* o = d.Aq + (size_t)(col0 + fn * 8) * Mp + row0 + fm * 8;
+        o[0] = acc.c[fm][fn][0];
+        o[Mp] = acc.c[fm][fn][1];
+      }
+    return;
+  }
   if (mode == SGPR_GEMM_H) {
+    // tile (u, i) of UB Vt^T; Ht[i][u] = (At[i][u] - acc) / sigma + r_i gamma_u / s2, zero for u >= M
     const double isig = rsqrt(d.noise), is2 = 1.0 / d.noise;
 #pragma unroll
     for (int fm = 0; fm < 8; ++fm) {
-      const int row = row0 + fm * 8;
-      const double rv = d.res[row] * is2;
+      const int u = row0 + fm * 8;
+      const double gu = u < d.M ? d.gam[u] * is2 : 0.0;
 #pragma unroll
       for (int fn = 0; fn < 4; ++fn) {
-        const int col = col0 + fn * 8;
-        const double2 a = *reinterpret_cast<const double2*>(d.At + (size_t)row * Mp + col);
-        double2 o;
-        o.x = col < d.M ? (a.x - acc.c[fm][fn][0]) * isig + rv * d.gam[col] : 0.0;
-        o.y = col + 1 < d.M ? (a.y - acc.c[fm][fn][1]) * isig + rv * d.gam[col + 1] : 0.0;
-        *reinterpret_cast<double2*>(out + (size_t)row * Mp + col) = o;
+        const int i = col0 + fn * 8;
+        const size_t o = (size_t)i * Mp + u;
+        const double v0 = u < d.M ? (d.At[o] - acc.c[fm][fn][0]) * isig + d.res[i] * gu : 0.0;
+        const double v1 = u < d.M ? (d.At[o + Mp] - acc.c[fm][fn][1]) * isig + d.res[i + 1] * gu : 0.0;
+        d.Ct[o] = v0;
+        d.Ct[o + Mp] = v1;
       }
     }
     return;

@@ -99,6 +99,31 @@ __device__ __forceinline__ void mma_slab_tri(Acc& acc, const double* As, int lda
   }
 }
 
+// Mirror case: a slab of a lower-triangular A block (A[a][k] = 0 for k > a): fragments whose rows all
+// lie above the slab's k range are skipped.
+__device__ __forceinline__ void mma_slab_tri_lo(Acc& acc, const double* As, int lda, const double* Bs, int ldb,
+                                                int nk4, int wm, int wn, int lane, int kl0) {
+  const int lr = lane >> 2, lk = lane & 3;
+  const double* ap = As + (wm * 64 + lr) * lda + lk;
+  const double* bp = Bs + (wn * 32 + lr) * ldb + lk;
+#pragma unroll
+  for (int k4 = 0; k4 < nk4; ++k4) {
+    const int kfirst = kl0 + 4 * k4;
+    if (kfirst > wm * 64 + 63) continue;
+    double b[4];
+#pragma unroll
+    for (int f = 0; f < 4; ++f) b[f] = bp[f * 8 * ldb + k4 * 4];
+#pragma unroll
+    for (int fm = 0; fm < 8; ++fm) {
+      if (kfirst <= wm * 64 + fm * 8 + 7) {
+        const double a = ap[fm * 8 * lda + k4 * 4];
+#pragma unroll
+        for (int fn = 0; fn < 4; ++fn) dmma884(acc.c[fm][fn][0], acc.c[fm][fn][1], a, b[fn]);
+      }
+    }
+  }
+}
+
 // Strip mapping, one block of 4 k values: acc[rf][cf] += A[strip rows][k] * B[8cf .. 8cf+8][k]^T for
 // the column fragments cf_lo <= cf < cf_hi (warp-uniform bounds).  ap / bp point at this lane's
 // element of the k block: ap = A + (16*strip + lr) * lda + k + lk,  bp = B + lr * ldb + k + lk.
@@ -144,10 +169,10 @@ __device__ __forceinline__ void gemm_nt_prologue(const double* Ag, const double*
 
 // acc += sum_{k in [kbeg, kend)} Ag[m][k] * Bg[n][k]   (kbeg, kend multiples of KC), after
 // gemm_nt_prologue with the same arguments.  tri_first: the first 128-block of A
-// (k in [kbeg, kbeg + 128)) is upper triangular.
+// (k in [kbeg, kbeg + 128)) is upper triangular; tri_last: the last one is lower triangular.
 __device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, const double* Bg, int ldg,
                                                  int kbeg, int kend, double* stages, int tid,
-                                                 bool tri_first = false) {
+                                                 bool tri_first = false, bool tri_last = false) {
   const int warp = tid >> 5, lane = tid & 31, wm = warp >> 2, wn = warp & 3;
   const int nslab = (kend - kbeg) / KC;
   for (int s = 0; s < nslab; ++s) {
@@ -162,6 +187,8 @@ __device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, con
     cp_async_commit();
     const double* st = stages + (s % NSTAGE) * STAGE_D;
     if (tri_first && s < NB / KC) mma_slab_tri(acc, st, LDS_S, st + NB * LDS_S, LDS_S, KC / 4, wm, wn, lane, s * KC);
+    else if (tri_last && s >= nslab - NB / KC)
+      mma_slab_tri_lo(acc, st, LDS_S, st + NB * LDS_S, LDS_S, KC / 4, wm, wn, lane, (s - (nslab - NB / KC)) * KC);
     else mma_slab(acc, st, LDS_S, st + NB * LDS_S, LDS_S, KC / 4, wm, wn, lane);
   }
   cp_async_wait<0>();
