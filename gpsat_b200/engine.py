@@ -293,7 +293,7 @@ class Engine:
             raise ValueError(f"need one inducing-point array per expert: got {len(Zl)} for {batch.E} experts")
         off_z = np.zeros(batch.E + 1, dtype=np.int64)
         off_z[1:] = np.cumsum([len(z) for z in Zl])
-        Zp = np.ascontiguousarray(np.concatenate(Zl, axis=0)) if Zl else np.zeros((0, batch.D))
+        Zp = np.ascontiguousarray(np.concatenate(Zl, axis=0)) if Zl else np.zeros((1, batch.D))
         return off_z, self._in(batch, Zp, np.float64, Zp.shape)
 
     def sgpr_elbo(self, batch: RaggedBatch, Z, theta, with_grad: bool = False):

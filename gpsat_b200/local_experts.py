@@ -159,7 +159,10 @@ class LocalExpertOI:
     ``expert_locs``: DataFrame with (at least) the coordinate columns; ``data``: DataFrame of
     observations; the config dicts use the reference's keys - ``data_config``: ``obs_col``,
     ``coords_col``, ``local_select``; ``model_config``: ``init_params``, ``constraints``,
-    ``optim_kwargs``, ``pred_kwargs``, ``params_to_store``; ``pred_loc_config``: ``df`` (or ``None``
+    ``optim_kwargs``, ``pred_kwargs``, ``params_to_store``, ``replacement_threshold`` /
+    ``replacement_model`` / ``replacement_init_params`` / ``replacement_constraints`` /
+    ``replacement_optim_kwargs`` / ``replacement_pred_kwargs`` (another model for experts with fewer
+    observations than the threshold, ``local_experts.py:1021-1041``; each family is one batch); ``pred_loc_config``: ``df`` (or ``None``
     to predict at the expert location) and ``max_dist`` (``config_dataclasses.py:9-509``).
     """
 
@@ -173,6 +176,14 @@ class LocalExpertOI:
         mc = dict(model_config or {})
         self.model_cls = resolve_model(mc.get("oi_model", "B200GPRModel"))
         self.load_params = mc.get("load_params")
+        # replacement model for experts with few observations (local_experts.py:1021-1041)
+        self.replacement_threshold = mc.get("replacement_threshold")
+        if self.replacement_threshold is not None:
+            self.replacement_cls = resolve_model(mc.get("replacement_model") or "B200GPRModel")
+            self.replacement_init_params = dict(mc.get("replacement_init_params") or {})
+            self.replacement_constraints = mc.get("replacement_constraints")
+            self.replacement_optim_kwargs = dict(mc.get("replacement_optim_kwargs") or {})
+            self.replacement_pred_kwargs = dict(mc.get("replacement_pred_kwargs") or {})
         self.init_params = dict(mc.get("init_params") or {})
         self.constraints = mc.get("constraints")
         self.optim_kwargs = dict(mc.get("optim_kwargs") or {})
@@ -183,15 +194,19 @@ class LocalExpertOI:
         self.pred_df = pc.get("df")
         self.max_dist = pc.get("max_dist")
 
-    def _constraints_for_model(self):
+    @staticmethod
+    def _scaled_constraints(constraints, init_params):
         """The driver forces ``scale=True`` on the lengthscale bounds when ``coords_scale`` is given
         (``local_experts.py:1110-1114``)."""
-        if self.constraints is None:
+        if constraints is None:
             return None
-        cons = {k: dict(v) for k, v in self.constraints.items()}
-        if "coords_scale" in self.init_params and "lengthscales" in cons:
+        cons = {k: dict(v) for k, v in constraints.items()}
+        if "coords_scale" in init_params and "lengthscales" in cons:
             cons["lengthscales"]["scale"] = True
         return cons
+
+    def _constraints_for_model(self):
+        return self._scaled_constraints(self.constraints, self.init_params)
 
     # ---- load_params (local_experts.py:553-689) ---------------------------------------------------
     def _param_lookup(self, param_names):
@@ -259,8 +274,15 @@ class LocalExpertOI:
             pred_cols = [c for c in coords_col if c in self.pred_df]
             pred_tree = cKDTree(self.pred_df[pred_cols].values)
         cons = self._constraints_for_model()
+        # group 0: the configured model; group 1: the replacement model for small experts
+        groups = [dict(cls=self.model_cls, init=self.init_params, cons=cons, optim=self.optim_kwargs,
+                       pred=self.pred_kwargs)]
+        if self.replacement_threshold is not None:
+            groups.append(dict(cls=self.replacement_cls, init=self.replacement_init_params,
+                               cons=self._scaled_constraints(self.replacement_constraints, self.replacement_init_params),
+                               optim=self.replacement_optim_kwargs, pred=self.replacement_pred_kwargs))
         lookup = None
-        models, pcs, refs, skipped = [], [], [], []
+        models, pcs, refs, skipped, group_of = [], [], [], [], []
         for _, rl in self.expert_locs.iterrows():
             ref = {c: rl[c] for c in coords_col}
             pc = prediction_coords_for(self.pred_df, ref, coords_col, self.max_dist, pred_tree, pred_cols)
@@ -270,25 +292,37 @@ class LocalExpertOI:
             if len(df_local) < min_obs:
                 skipped.append((ref, len(df_local)))       # local_experts.py:988-1012
                 continue
-            m = self.model_cls(data=df_local, obs_col=self.obs_col, coords_col=coords_col,
-                               expert_loc=np.array([ref[c] for c in coords_col]), verbose=False, **self.init_params)
+            gi = 1 if (self.replacement_threshold is not None and len(df_local) < self.replacement_threshold) else 0
+            grp = groups[gi]
+            m = grp["cls"](data=df_local, obs_col=self.obs_col, coords_col=coords_col,
+                           expert_loc=np.array([ref[c] for c in coords_col]), verbose=False, **grp["init"])
             if self.load_params:                            # before the constraints, local_experts.py:1065-1115
                 if lookup is None:
                     lookup = self._param_lookup(m.param_names)
                 loaded = self._params_for(lookup, ref)
                 if loaded:
                     m.set_parameters(**loaded)
-            if cons is not None:
-                m.set_parameter_constraints(cons, move_within_tol=True, tol=1e-2)
-            models.append(m); pcs.append(pc); refs.append(ref)
-        # phase B: one fit call + one predict call for every expert
-        opt_kwargs = dict(self.optim_kwargs)
+            if grp["cons"] is not None:
+                m.set_parameter_constraints(grp["cons"], move_within_tol=True, tol=1e-2)
+            models.append(m); pcs.append(pc); refs.append(ref); group_of.append(gi)
+        # phase B: per model family one fit call + one predict call for all its experts
         t_sel = time.time()
-        if models:
-            success, objective, preds = fit_predict_models(
-                models, pcs if predict else None, optimise=optimise, max_iter=opt_kwargs.pop("max_iter", 10_000),
-                fixed_params=opt_kwargs.pop("fixed_params", None),
-                apply_scale=self.pred_kwargs.get("apply_scale", True), **opt_kwargs)
+        success = np.zeros(len(models), bool)
+        objective = np.full(len(models), np.nan)
+        preds = [None] * len(models)
+        for gi, grp in enumerate(groups):
+            idx = [k for k, g in enumerate(group_of) if g == gi]
+            if not idx:
+                continue
+            opt_kwargs = dict(grp["optim"])
+            ok_g, obj_g, pred_g = fit_predict_models(
+                [models[k] for k in idx], [pcs[k] for k in idx] if predict else None, optimise=optimise,
+                max_iter=opt_kwargs.pop("max_iter", 10_000), fixed_params=opt_kwargs.pop("fixed_params", None),
+                apply_scale=grp["pred"].get("apply_scale", True), **opt_kwargs)
+            for j, k in enumerate(idx):
+                success[k], objective[k] = ok_g[j], obj_g[j]
+                if predict:
+                    preds[k] = pred_g[j]
         t_fit = time.time()
         # phase C: tables
         frames: Dict[str, List[pd.DataFrame]] = {}
@@ -307,7 +341,8 @@ class LocalExpertOI:
             device = m.cpu_name if m.gpu_name is None else m.gpu_name
             add(dict_to_tables({"num_obs": len(m.obs), "run_time": per_expert, "objective_value": float(objective[e]),
                                 "parameters_optimised": optimise, "optimise_success": bool(success[e]) if optimise else False,
-                                "model": model_name, "device": str(device)[:64], "config_id": config_id},
+                                "model": f"{type(m).__module__}.{type(m).__name__}"[:64], "device": str(device)[:64],
+                                "config_id": config_id},
                                refs[e], "run_details"))
             if predict:
                 pred = dict(preds[e])

@@ -245,6 +245,15 @@ def test_empty_batch_and_api_misuse(engine):
     bad = RaggedBatch("Matern32", 9, np.array([0, 4], np.int64), np.zeros((4, 9)), np.zeros(4))
     with pytest.raises(RuntimeError, match="D out of range"):
         engine.lml_grad(bad, np.ones((1, 11)))
+    # the sparse and the Fourier-feature entry points: empty batch, bad inducing sets
+    assert engine.sgpr_elbo(b, [], np.zeros((0, 5)))[0].shape == (0,)
+    assert engine.sgpr_predict(b, [], np.zeros((0, 5)))["f*"].shape == (0,)
+    assert engine.vff_elbo(b, (np.zeros((0, 3)), np.zeros((0, 3)), np.zeros((0, 3), np.int32)), np.zeros((0, 7)))[0].shape == (0,)
+    one = RaggedBatch.from_lists("Matern32", [np.random.default_rng(0).uniform(-1, 1, (20, 3))], [np.zeros(20)])
+    with pytest.raises(RuntimeError, match="inducing points"):
+        engine.sgpr_elbo(one, [np.zeros((0, 3))], np.ones((1, 5)))
+    with pytest.raises(ValueError, match="one inducing-point array per expert"):
+        engine.sgpr_elbo(one, [], np.ones((1, 5)))
 
 
 @pytest.mark.parametrize("n", [2000, 4000])
@@ -290,7 +299,7 @@ def test_bitwise_repeatable_and_order_independent(engine):
 
 
 @pytest.mark.parametrize("n", [2000, 3100])
-def test_full_size_expert(engine, n):
+def test_full_size_single_expert(engine, n):
     """One expert at the sizes of configs c3 / north star (BASELINE.json): LML, gradient and
     predictions against the oracle (LAPACK) at the fixed-theta tolerance."""
     rng = np.random.default_rng(n)
@@ -308,3 +317,50 @@ def test_full_size_expert(engine, n):
     p = gpr.predict("Matern32", X, y, th[0], Xs)
     np.testing.assert_allclose(pred["f*"], p["f*"], rtol=RTOL_FIXED, atol=1e-9)
     np.testing.assert_allclose(pred["f*_var"], p["f*_var"], rtol=RTOL_FIXED, atol=1e-11)
+
+
+def test_property_random_shapes(engine):
+    """Property test (hypothesis): any n in [1, 600], D in {1, 2, 3}, any of the four kernels, any
+    hyper-parameters in a plausible box - LML, gradient and predictions agree with the oracle."""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=30, deadline=None, derandomize=True, suppress_health_check=list(HealthCheck))
+    @given(n=st.integers(1, 600), D=st.integers(1, 3), kind=st.sampled_from(list(gpr.KERNELS)),
+           m=st.integers(0, 40), seed=st.integers(0, 2 ** 16),
+           ls=st.floats(0.3, 4.0), var=st.floats(0.05, 3.0), noise=st.floats(1e-3, 0.5))
+    def check(n, D, kind, m, seed, ls, var, noise):
+        rng = np.random.default_rng(seed)
+        X, y, Xs = _expert(rng, n, D, m=m)
+        th = np.concatenate([np.full(D, ls) * rng.uniform(0.7, 1.4, D), [var, noise]])[None, :]
+        b = _batch(kind, [(X, y, Xs)])
+        lml, grad, st_ = engine.lml_grad(b, th)
+        v, g = gpr.lml_and_grad(kind, X, y, th[0])
+        assert st_[0] == 0
+        assert abs(lml[0] - v) <= RTOL_FIXED * max(abs(v), 1.0)
+        np.testing.assert_allclose(grad[0], g, rtol=1e-7, atol=1e-7 * max(np.abs(g).max(), 1.0))
+        if m:
+            pred = engine.predict(b, th)
+            p = gpr.predict(kind, X, y, th[0], Xs)
+            np.testing.assert_allclose(pred["f*"], p["f*"], rtol=RTOL_FIXED, atol=1e-10 * max(1.0, np.abs(y).max()))
+            np.testing.assert_allclose(pred["f*_var"], p["f*_var"], rtol=RTOL_FIXED, atol=1e-11 * var)
+
+    check()
+
+
+def test_gradient_matches_finite_differences_of_the_cuda_lml(engine):
+    """Size-independent property at a c3-sized expert: the analytic gradient equals central finite
+    differences of the engine's own LML (no oracle involved)."""
+    rng = np.random.default_rng(8)
+    X, y, _ = _expert(rng, 2500, 3)
+    th = np.array([1.8, 1.4, 2.6, 0.7, 0.08])
+    b = _batch("Matern32", [(X, y, np.zeros((0, 3)))])
+    _, grad, _ = engine.lml_grad(b, th[None, :])
+    for p in range(5):
+        h = 1e-5 * th[p]
+        tp, tm = th.copy(), th.copy()
+        tp[p] += h
+        tm[p] -= h
+        lp, _, _ = engine.lml_grad(b, tp[None, :], with_grad=False)
+        lm, _, _ = engine.lml_grad(b, tm[None, :], with_grad=False)
+        fd = (lp[0] - lm[0]) / (2 * h)
+        assert abs(fd - grad[0][p]) <= 2e-5 * max(1.0, abs(grad[0][p])), (p, fd, grad[0][p])

@@ -143,3 +143,32 @@ def test_driver_runs_sparse_and_vff_models(engine, oi_model, init):
     if oi_model == "B200SGPRModel":
         ip = t["inducing_points"]
         assert list(ip.columns) == ["_dim_0", "_dim_1", "inducing_points"] and len(ip) == 9 * 40 * 3
+
+
+def test_replacement_model_for_small_experts(engine):
+    """local_experts.py:1021-1041: experts with fewer observations than replacement_threshold run the
+    replacement model; the two families are batched separately and the tables keep expert order."""
+    oi = _oi()
+    from gpsat_b200.local_experts import resolve_model
+    counts = []
+    from gpsat_b200.local_experts import local_data_select
+    for _, rl in oi.expert_locs.iterrows():
+        counts.append(len(local_data_select(oi.data, {c: rl[c] for c in oi.coords_col}, oi.local_select)))
+    thr = int(np.median(counts))
+    oi.model_cls = resolve_model("B200SGPRModel")
+    oi.init_params = dict(oi.init_params, num_inducing_points=60)
+    oi.constraints = None
+    oi.replacement_threshold = thr
+    oi.replacement_cls = resolve_model("GPflowGPRModel")
+    oi.replacement_init_params = {"coords_scale": [5e4, 5e4, 1], "obs_mean": "local"}
+    oi.replacement_constraints = {"lengthscales": {"low": [1e-8, 1e-8, 1e-8], "high": [6e5, 6e5, 9]}}
+    oi.replacement_optim_kwargs = {}
+    oi.replacement_pred_kwargs = {}
+    np.random.seed(1)
+    t = oi.run()
+    rd = t["run_details"]
+    small = np.array(counts) < thr
+    assert list(rd["num_obs"]) == counts
+    assert all(("B200GPRModel" in mname) == s for mname, s in zip(rd["model"], small))
+    assert np.all(np.isfinite(rd["objective_value"])) and np.all(np.isfinite(t["preds"]["f*"]))
+    assert "inducing_points" in t and len(t["lengthscales"]) == 27
