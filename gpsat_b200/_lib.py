@@ -27,7 +27,7 @@ EXPORTED_SYMBOLS = (
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
     "gpsat_sgpr_elbo", "gpsat_sgpr_predict", "gpsat_sgpr_fit",
     "gpsat_vff_elbo", "gpsat_vff_predict", "gpsat_vff_fit",
-    "gpsat_gaussian_smooth", "gpsat_glue_predictions",
+    "gpsat_gaussian_smooth", "gpsat_glue_predictions", "gpsat_local_select",
 )
 
 
@@ -48,6 +48,11 @@ class Priors(C.Structure):
 
 class VffDomain(C.Structure):
     _fields_ = [("a", C.c_void_p), ("b", C.c_void_p), ("nfreq", C.c_void_p)]
+
+
+class SelectCond(C.Structure):
+    _fields_ = [("kind", C.c_int32), ("op", C.c_int32), ("ncol", C.c_int32), ("col", C.c_int32 * 3),
+                ("loc_col", C.c_int32 * 3), ("val", C.c_double)]
 
 
 class Stats(C.Structure):
@@ -102,6 +107,8 @@ def load():
     lib.gpsat_gaussian_smooth.argtypes = [vp, C.c_int, C.c_int64, vp, vp, C.c_int64, C.c_int64, vp, vp,
                                           C.c_double, C.c_double, vp, vp]
     lib.gpsat_glue_predictions.argtypes = [vp, C.c_int, C.c_int64, C.c_int64, vp, C.c_int, vp, vp, vp, C.c_int64, vp, vp]
+    lib.gpsat_local_select.argtypes = [vp, C.c_int64, C.c_int32, vp, C.c_int64, C.c_int32, vp, C.c_int32,
+                                       C.POINTER(SelectCond), vp, vp, vp]
     _lib = lib
     return lib
 

@@ -86,6 +86,7 @@ struct SlotMem {
 #include "sgpr_kernels.cuh"
 #include "vff_kernels.cuh"
 #include "post_kernels.cuh"
+#include "select_kernels.cuh"
 namespace gpsat {
 
 // ---- transforms (gpflow.utilities.positive / tfp.bijectors.Sigmoid) -------------------------

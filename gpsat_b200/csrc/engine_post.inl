@@ -77,3 +77,5 @@ int gpsat_glue_predictions(gpsat_engine* h, int mem, int64_t n, int64_t G, const
 }
 
 }  // extern "C"
+
+#include "engine_select.inl"

@@ -260,10 +260,18 @@ class LocalExpertOI:
         return out
 
     def run(self, store_path: Optional[str] = None, optimise: bool = True, predict: bool = True,
-            min_obs: int = 3, table_suffix: str = "", config_id: int = 1) -> Dict[str, pd.DataFrame]:
+            min_obs: int = 3, table_suffix: str = "", config_id: int = 1,
+            device_select: bool = False) -> Dict[str, pd.DataFrame]:
         """All experts: select, fit, predict, tabulate.  Returns ``{table name: DataFrame}`` with the
         reference's tables (``preds``, ``run_details``, one per stored hyper-parameter), each name
-        extended by ``table_suffix``."""
+        extended by ``table_suffix``.  ``device_select=True`` evaluates the selection rules of all
+        experts in one GPU launch (``gpsat_local_select``) and builds the packed batch and the
+        tables with array operations instead of one model instance and one DataFrame per expert
+        (exact-GPR model only); the tables are identical to the default path."""
+        if device_select:
+            tables = self._run_vectorised(optimise, predict, min_obs, table_suffix, config_id)
+            self._store(tables, store_path)
+            return tables
         t0 = time.time()
         coords_col = self.coords_col
         # phase A: selection (KD-trees are built once, as the reference caches them per global select)
@@ -353,12 +361,215 @@ class LocalExpertOI:
             add(dict_to_tables(hypes, refs[e], None))
         tables = {k: pd.concat(v) for k, v in frames.items()}
         self.timings = {"select_s": t_sel - t0, "engine_s": t_fit - t_sel, "tables_s": time.time() - t_fit}
-        if store_path is not None:
-            try:
-                with pd.HDFStore(store_path, mode="a") as store:     # needs PyTables, like the reference
-                    for k, v in tables.items():
-                        store.append(k, v, data_columns=True)
-            except ImportError as exc:
-                raise ImportError("writing result tables to HDF5 needs PyTables; call run(store_path=None) "
-                                  "to get the tables as DataFrames") from exc
+        self._store(tables, store_path)
         return tables
+
+    @staticmethod
+    def _store(tables, store_path):
+        if store_path is None:
+            return
+        try:
+            with pd.HDFStore(store_path, mode="a") as store:     # needs PyTables, like the reference
+                for k, v in tables.items():
+                    store.append(k, v, data_columns=True)
+        except ImportError as exc:
+            raise ImportError("writing result tables to HDF5 needs PyTables; call run(store_path=None) "
+                              "to get the tables as DataFrames") from exc
+
+
+# ---- vectorised driver path: batched selection on the GPU, array-built batch and tables ----------
+_OPS = {">=": 0, ">": 1, "==": 2, "<": 3, "<=": 4}
+
+
+def select_all(engine, table: np.ndarray, locs: np.ndarray, conds: list):
+    """``gpsat_local_select`` for every row of ``locs``: (counts[E], off[E+1], idx[off[E]]).
+    ``conds``: tuples ``(kind, op, cols, loc_cols, val)`` (see ``include/gpsat_b200.h``)."""
+    import ctypes as C
+    from . import _lib
+    table = np.ascontiguousarray(table, dtype=np.float64)
+    locs = np.ascontiguousarray(locs, dtype=np.float64)
+    E = len(locs)
+    arr = (_lib.SelectCond * max(len(conds), 1))()
+    for q, (kind, op, cols, lcols, val) in enumerate(conds):
+        arr[q].kind, arr[q].op, arr[q].ncol, arr[q].val = kind, _OPS[op], len(cols), float(val)
+        for k in range(len(cols)):
+            arr[q].col[k], arr[q].loc_col[k] = int(cols[k]), int(lcols[k])
+    counts = np.zeros(E, dtype=np.int64)
+    args = (engine._h, len(table), table.shape[1], C.c_void_p(table.ctypes.data), E, locs.shape[1],
+            C.c_void_p(locs.ctypes.data), len(conds), arr)
+    _lib.check(engine._lib.gpsat_local_select(*args, C.c_void_p(counts.ctypes.data), None, None))
+    off = np.zeros(E + 1, dtype=np.int64)
+    off[1:] = np.cumsum(counts)
+    idx = np.zeros(max(int(off[-1]), 1), dtype=np.int64)
+    if off[-1] > 0:
+        _lib.check(engine._lib.gpsat_local_select(*args, C.c_void_p(counts.ctypes.data), C.c_void_p(off.ctypes.data),
+                                                  C.c_void_p(idx.ctypes.data)))
+    return counts, off, idx[:int(off[-1])]
+
+
+def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
+    from .engine import RaggedBatch
+    t0 = time.time()
+    if self.model_cls is not B200GPRModel or self.replacement_threshold is not None:
+        raise NotImplementedError("device_select=True supports the exact model (B200GPRModel) without a replacement model")
+    coords_col, D = self.coords_col, len(self.coords_col)
+    obs_col = self.obs_col if isinstance(self.obs_col, str) else self.obs_col[0]
+    locs = self.expert_locs[coords_col].values.astype(np.float64)
+    E = len(locs)
+    # template model: parameter values, transforms and trainable flags do not depend on the data
+    def template():
+        return B200GPRModel(coords=np.arange(2.0 * D).reshape(2, D), obs=np.array([[0.0], [1.0]]),
+                            coords_col=coords_col, obs_col=[obs_col], verbose=False, **self.init_params)
+
+    tmpl = template()
+    eng = tmpl.engine
+    cs = np.broadcast_to(np.atleast_2d(tmpl.coords_scale)[0, :], (D,)).astype(np.float64)
+    obs_scale = float(np.atleast_2d(tmpl.obs_scale).reshape(-1)[0])
+    local_mean = isinstance(self.init_params.get("obs_mean"), str) and self.init_params.get("obs_mean") == "local"
+    # ---- phase A: selection of observations and prediction locations for all experts ----
+    table = np.ascontiguousarray(self.data[coords_col + [obs_col]].values, dtype=np.float64)
+    conds = []
+    for ls in self.local_select:
+        col, comp = ls["col"], ls["comp"]
+        if isinstance(col, str):
+            assert col in coords_col and comp in _OPS, f"local_select entry not understood: {ls}"
+            conds.append((0, comp, [coords_col.index(col)], [coords_col.index(col)], ls["val"]))
+        else:
+            assert comp in ["<", "<="], "for multi dimensional values only less than comparison handled"
+            ids = [coords_col.index(c) for c in col]
+            conds.append((1, "<=", ids, ids, ls["val"]))          # KD-tree ball query: d <= r
+    n_all, off_all, idx_all = select_all(eng, table, locs, conds)
+    if self.pred_df is None:
+        m_all = np.ones(E, dtype=np.int64)
+        poff_all = np.arange(E + 1, dtype=np.int64)
+        pidx_all, shared = None, []
+    else:
+        shared = [c for c in coords_col if c in self.pred_df]
+        ptab = np.ascontiguousarray(self.pred_df[shared].values, dtype=np.float64)
+        sid = [coords_col.index(c) for c in shared]
+        pconds = [] if self.max_dist is None else [(1, "<", list(range(len(shared))), sid, self.max_dist)]
+        m_all, poff_all, pidx_all = select_all(eng, ptab, locs, pconds)
+    has_pred = m_all > 0                                       # local_experts.py:962-965
+    small = has_pred & (n_all < min_obs)                       # local_experts.py:988-1012
+    keep = np.flatnonzero(has_pred & ~small)
+    K = len(keep)
+    # packed observations of the kept experts
+    seg = [idx_all[off_all[e]:off_all[e + 1]] for e in keep]
+    rows = np.concatenate(seg) if K else np.zeros(0, np.int64)
+    off_n = np.zeros(K + 1, dtype=np.int64)
+    off_n[1:] = np.cumsum(n_all[keep])
+    local = table[rows]
+    assert not np.isnan(local[:, :D]).any(), "nans found in coords"
+    assert not np.isnan(local[:, D]).any(), "nans found in obs"
+    X = local[:, :D] / cs
+    y = local[:, D].copy()
+    means = np.zeros(K)
+    if local_mean:
+        for k in range(K):
+            means[k] = np.mean(y[off_n[k]:off_n[k + 1]].reshape(-1, 1), axis=0)[0]    # base_model.py:195-198
+    y -= np.repeat(means, n_all[keep])
+    y /= obs_scale
+    # packed prediction coordinates (unscaled for the tables, scaled for the engine)
+    off_m = np.zeros(K + 1, dtype=np.int64)
+    off_m[1:] = np.cumsum(m_all[keep])
+    pc = np.repeat(locs[keep], m_all[keep], axis=0)
+    if pidx_all is not None and K:
+        prow = np.concatenate([pidx_all[poff_all[e]:poff_all[e + 1]] for e in keep])
+        for j, c in enumerate(shared):
+            pc[:, coords_col.index(c)] = ptab[prow, j]
+    apply_scale = self.pred_kwargs.get("apply_scale", True)
+    Xs = pc / cs if apply_scale else pc.copy()
+    batch = RaggedBatch(tmpl.kernel, D, off_n, np.ascontiguousarray(X), np.ascontiguousarray(y), off_m,
+                        np.ascontiguousarray(Xs))
+    # hyper-parameters, transforms, trainable flags per expert
+    cons = self._constraints_for_model()
+    P = D + 2
+    theta = np.empty((K, P)); tkind = np.empty((K, P), np.int32); ta = np.empty((K, P)); tb = np.empty((K, P))
+    lookup = self._param_lookup(tmpl.param_names) if self.load_params else None
+    base = None
+    for k, e in enumerate(keep):
+        m = None
+        if lookup is not None:
+            loaded = self._params_for(lookup, dict(zip(coords_col, locs[e])))
+            if loaded:                                      # before the constraints, local_experts.py:1065-1115
+                m = template()
+                m.set_parameters(**loaded)
+                if cons is not None:
+                    m.set_parameter_constraints(cons, move_within_tol=True, tol=1e-2)
+        if m is None:
+            if base is None:
+                base = template()
+                if cons is not None:
+                    base.set_parameter_constraints(cons, move_within_tol=True, tol=1e-2)
+            m = base
+        theta[k], tkind[k], ta[k], tb[k] = m._theta, m._tkind, m._ta, m._tb
+    opt_kwargs = dict(self.optim_kwargs)
+    fixed = opt_kwargs.pop("fixed_params", None) or []
+    tmpl._fix_hyperparameters(fixed)
+    trainable = np.tile(tmpl._trainable.astype(np.uint8), (K, 1))
+    t_sel = time.time()
+    # ---- phase B ----
+    success = np.zeros(K, bool)
+    if K and optimise:
+        tol = opt_kwargs.pop("tol", None)
+        kw = {} if tol is None else {"ftol": float(tol), "pgtol": float(tol)}
+        pri = None
+        if np.any(tmpl._pkind):
+            pri = (np.tile(tmpl._pkind, (K, 1)), np.tile(tmpl._pa, (K, 1)), np.tile(tmpl._pb, (K, 1)))
+        res = eng.fit(batch, theta, tkind, ta, tb, trainable, max_iter=int(opt_kwargs.pop("max_iter", 10_000)),
+                      priors=pri, **kw)
+        ok_theta = res.status != 1
+        theta = np.where(ok_theta[:, None], res.theta, theta)
+        success = res.status == 0
+    if K and predict:
+        out = eng.predict(batch, theta)
+        objective = -np.asarray(out["lml"])
+    elif K:
+        objective = -np.asarray(eng.lml_grad(batch, theta, with_grad=False)[0])
+    else:
+        objective = np.zeros(0)
+    t_fit = time.time()
+    # ---- phase C: tables, in the row order of the per-expert path ----
+    def midx(rows_locs):
+        if D == 1:
+            return pd.Index(rows_locs[:, 0], name=coords_col[0])
+        return pd.MultiIndex.from_arrays([rows_locs[:, j] for j in range(D)], names=coords_col)
+
+    model_name = f"{B200GPRModel.__module__}.{B200GPRModel.__name__}"[:64]
+    device = str(tmpl.cpu_name if tmpl.gpu_name is None else tmpl.gpu_name)[:64]
+    sk = np.flatnonzero(small)
+    per_expert = (t_fit - t_sel) / max(K, 1)
+    rd = pd.DataFrame({
+        "num_obs": np.concatenate([n_all[sk], n_all[keep]]),
+        "run_time": np.concatenate([np.full(len(sk), np.nan), np.full(K, per_expert)]),
+        "objective_value": np.concatenate([np.full(len(sk), np.nan), objective]),
+        "parameters_optimised": optimise,
+        "optimise_success": np.concatenate([np.zeros(len(sk), bool), success if optimise else np.zeros(K, bool)]),
+        "model": model_name,
+        "device": np.concatenate([np.full(len(sk), "", dtype=object), np.full(K, device, dtype=object)]),
+        "config_id": config_id})
+    rd.index = midx(np.concatenate([locs[sk], locs[keep]]))
+    tables = {"run_details" + table_suffix: rd} if len(rd) else {}
+    if K and predict:
+        f_bar = np.repeat(means, m_all[keep]) if local_mean else np.zeros(len(pc))
+        pr = pd.DataFrame({"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"], "f_bar": f_bar})
+        for j, c in enumerate(coords_col):
+            pr[f"pred_loc_{c}"] = pc[:, j]
+        pr.index = midx(np.repeat(locs[keep], m_all[keep], axis=0))
+        tables["preds" + table_suffix] = pr
+    store = self.params_to_store or tmpl.param_names
+    if K:
+        if "lengthscales" in store:
+            ls = pd.DataFrame({"_dim_0": np.tile(np.arange(D), K), "lengthscales": theta[:, :D].reshape(-1)})
+            ls.index = midx(np.repeat(locs[keep], D, axis=0))
+            tables["lengthscales" + table_suffix] = ls
+        for name, col in (("kernel_variance", D), ("likelihood_variance", D + 1)):
+            if name in store:
+                df = pd.DataFrame({name: theta[:, col].copy()})
+                df.index = midx(locs[keep])
+                tables[name + table_suffix] = df
+    self.timings = {"select_s": t_sel - t0, "engine_s": t_fit - t_sel, "tables_s": time.time() - t_fit}
+    return tables
+
+
+LocalExpertOI._run_vectorised = _run_vectorised

@@ -235,6 +235,26 @@ int gpsat_glue_predictions(gpsat_engine* eng, int mem, int64_t n, int64_t G, con
                            const double* pred, const double* xprt, const double* sigma, int64_t V,
                            const double* vals, double* out);
 
+/* ---- batched local selection (DataLoader.local_data_select, GPSat/dataloader.py:2354-2447, and the
+ * max_dist filter of PredictionLocations, GPSat/prediction_locations.py:18-43) for all experts ------
+ * data [N][C]: point table (row-major, host); locs [E][CL]: expert locations (host).  A row is kept
+ * for expert e when every condition holds:
+ *   kind 0:  data[col[0]] <op> locs[e][loc_col[0]] + val          (op: 0 >=, 1 >, 2 ==, 3 <, 4 <=)
+ *   kind 1:  sum_k (data[col[k]] - locs[e][loc_col[k]])^2 <op> val^2   (ball query: op 4; strict: op 3)
+ * Two calls: with idx = off = NULL the matches per expert are counted into counts[E]; with
+ * off[E+1] (exclusive prefix sums of counts) and idx[off[E]] the matching row indices are written in
+ * increasing order per expert.  All arrays are HOST arrays. */
+typedef struct gpsat_select_cond {
+  int32_t kind, op, ncol;
+  int32_t col[3];
+  int32_t loc_col[3];
+  double val;
+} gpsat_select_cond;
+
+int gpsat_local_select(gpsat_engine* eng, int64_t N, int32_t C, const double* data, int64_t E, int32_t CL,
+                       const double* locs, int32_t ncond, const gpsat_select_cond* conds, int64_t* counts,
+                       const int64_t* off, int64_t* idx);
+
 /* Test hook (single expert, host memory): dense factor of the augmented matrix.
  * Lout [(n+1)*(n+1)] row-major lower: rows < n = chol(K + s2 I), row n = (L^-1 y)^T, 1.
  * Uout [(n+1)*(n+1)] row-major upper: L_aug^-T (may be NULL). */

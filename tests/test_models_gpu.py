@@ -209,3 +209,94 @@ def test_batched_driver_equals_reference_loop(built):
         assert tabs["kernel_variance"].loc[[key]]["kernel_variance"].iloc[0] == m.get_kernel_variance()
         k += 1
     assert k == 3
+
+
+def _driver_case(seed=21, n=2500):
+    rng = np.random.default_rng(seed)
+    data = pd.DataFrame({"x": rng.uniform(-4e5, 4e5, n), "y": rng.uniform(-4e5, 4e5, n),
+                         "t": rng.integers(-6, 7, n).astype(float)})
+    data["obs"] = np.sin(data.x / 1.5e5) + np.cos(data.y / 1e5) + 0.1 * data.t + 0.1 * rng.standard_normal(n)
+    locs = pd.DataFrame({"x": [-1e5, 0.0, 1.5e5, 3.9e5, 9e5, 2e5], "y": [0.0, 1e5, -1e5, 3.9e5, 9e5, 2e5],
+                         "t": [0.0, 1.0, -1.0, 0.0, 0.0, 2.0]})
+    grid = pd.DataFrame({"x": np.repeat(np.linspace(-4e5, 4e5, 33), 33), "y": np.tile(np.linspace(-4e5, 4e5, 33), 33)})
+    data_cfg = {"obs_col": "obs", "coords_col": ["x", "y", "t"],
+                "local_select": [{"col": "t", "comp": "<=", "val": 4}, {"col": "t", "comp": ">=", "val": -4},
+                                 {"col": ["x", "y"], "comp": "<", "val": 1.5e5}]}
+    model_cfg = {"oi_model": "B200GPRModel", "init_params": {"coords_scale": [5e4, 5e4, 1], "obs_mean": "local"},
+                 "constraints": {"lengthscales": {"low": [1e-8] * 3, "high": [6e5, 6e5, 9]}},
+                 "optim_kwargs": {"max_iter": 40}}
+    return locs, data, data_cfg, model_cfg, grid
+
+
+def test_device_selection_equals_host_selection(built):
+    """gpsat_local_select (all experts in one launch) returns exactly the rows, in data order, that
+    DataLoader.local_data_select (dataloader.py:2403-2447) and the prediction-location distance
+    filter (prediction_locations.py:31-43) keep - including no-match experts and every comparison."""
+    from gpsat_b200.local_experts import local_data_select, prediction_coords_for, select_all
+    from gpsat_b200.models import get_engine
+    locs, data, data_cfg, _, grid = _driver_case()
+    cols = ["x", "y", "t"]
+    table = data[cols + ["obs"]].values
+    L = locs[cols].values
+    conds = [(0, "<=", [2], [2], 4), (0, ">=", [2], [2], -4), (1, "<=", [0, 1], [0, 1], 1.5e5)]
+    counts, off, idx = select_all(get_engine(0), table, L, conds)
+    for e in range(len(L)):
+        ref = dict(zip(cols, L[e]))
+        want = local_data_select(data, ref, data_cfg["local_select"]).index.values
+        np.testing.assert_array_equal(idx[off[e]:off[e + 1]], want)
+        assert counts[e] == len(want)
+    assert counts[4] == 0
+    # every scalar comparison, against numpy
+    for op, fn in ((">=", np.greater_equal), (">", np.greater), ("==", np.equal), ("<", np.less), ("<=", np.less_equal)):
+        c, o, i = select_all(get_engine(0), table, L, [(0, op, [2], [2], 2.0)])
+        for e in range(len(L)):
+            np.testing.assert_array_equal(i[o[e]:o[e + 1]], np.flatnonzero(fn(table[:, 2], L[e, 2] + 2.0)))
+    # prediction locations: strict d^2 < max_dist^2 over the shared columns
+    c, o, i = select_all(get_engine(0), grid[["x", "y"]].values, L, [(1, "<", [0, 1], [0, 1], 1e5)])
+    for e in range(len(L)):
+        pc = prediction_coords_for(grid, dict(zip(cols, L[e])), cols, 1e5)
+        np.testing.assert_array_equal(grid[["x", "y"]].values[i[o[e]:o[e + 1]]], pc[:, :2])
+    # no condition at all selects everything; an empty table selects nothing
+    c, o, i = select_all(get_engine(0), table[:7], L, [])
+    assert np.all(c == 7) and np.array_equal(i, np.tile(np.arange(7), len(L)))
+    c, o, i = select_all(get_engine(0), table[:0], L, conds)
+    assert np.all(c == 0) and len(i) == 0
+
+
+@pytest.mark.parametrize("optimise,predict", [(True, True), (False, True), (True, False)])
+def test_vectorised_driver_equals_per_model_driver(built, optimise, predict):
+    """LocalExpertOI.run(device_select=True) - GPU selection, array-built batch and tables - returns
+    the same tables as the per-model path, value for value (run_time aside)."""
+    from gpsat_b200.local_experts import LocalExpertOI
+    locs, data, data_cfg, model_cfg, grid = _driver_case()
+    a = LocalExpertOI(locs, data, data_cfg, model_cfg, {"df": grid, "max_dist": 1e5}).run(
+        min_obs=100, optimise=optimise, predict=predict, table_suffix="_A", config_id=3)
+    b = LocalExpertOI(locs, data, data_cfg, model_cfg, {"df": grid, "max_dist": 1e5}).run(
+        min_obs=100, optimise=optimise, predict=predict, table_suffix="_A", config_id=3, device_select=True)
+    assert set(a) == set(b)
+    for k in a:
+        ta, tb = a[k], b[k]
+        if k.startswith("run_details"):
+            ta, tb = ta.drop(columns="run_time"), tb.drop(columns="run_time")
+        pd.testing.assert_frame_equal(ta, tb, check_exact=True, check_dtype=False)
+
+
+def test_vectorised_driver_other_configs(built):
+    """No prediction table (predict at the expert location), no local mean, fixed parameters, and the
+    refusal for other model families."""
+    from gpsat_b200.local_experts import LocalExpertOI
+    locs, data, data_cfg, model_cfg, _ = _driver_case(seed=5, n=1500)
+    model_cfg = dict(model_cfg, init_params={"coords_scale": [5e4, 5e4, 1]},
+                     optim_kwargs={"max_iter": 25, "fixed_params": ["likelihood_variance"]},
+                     params_to_store=["lengthscales", "likelihood_variance"])
+    a = LocalExpertOI(locs, data, data_cfg, model_cfg).run(min_obs=30)
+    b = LocalExpertOI(locs, data, data_cfg, model_cfg).run(min_obs=30, device_select=True)
+    assert set(a) == set(b) == {"run_details", "preds", "lengthscales", "likelihood_variance"}
+    for k in a:
+        ta, tb = a[k], b[k]
+        if k == "run_details":
+            ta, tb = ta.drop(columns="run_time"), tb.drop(columns="run_time")
+        pd.testing.assert_frame_equal(ta, tb, check_exact=True, check_dtype=False)
+    assert np.all(b["likelihood_variance"]["likelihood_variance"].values == 1.0)
+    with pytest.raises(NotImplementedError):
+        LocalExpertOI(locs, data, data_cfg, dict(model_cfg, oi_model="B200SGPRModel")).run(device_select=True)
