@@ -43,6 +43,8 @@ struct SlotDesc {
   const double* pre;     // kind == GPSAT_PRECOMPUTED: dense symmetric matrix (lower part read), else unused
   const double* pre_s;   // kind == GPSAT_PRECOMPUTED with m > 0: prediction rows [m][ldpre] (Kus^T)
   int ldpre;
+  int8_t* Uq;            // int8 slice planes of the upper block triangle (i8mma.cuh), nullptr = DMMA lauum
+  int* uex;              // [T*NB] row scale exponents of the planes
   double inv_ls[GPSAT_DMAX];
   double var;            // kernel variance
   double noise;          // likelihood variance

@@ -23,6 +23,7 @@
 #include "diag_kernel.cuh"
 #include "step_kernel.cuh"
 #include "lauum_kernel.cuh"
+#include "i8mma.cuh"
 
 namespace gpsat {
 
@@ -80,6 +81,7 @@ struct FitDev {
 // Slot-private scratch carved from the workspace; constant for the lifetime of a call.
 struct SlotMem {
   double* A; double* Wd; double* Ld; double* logdet; double* quad; double* gpart; int* notpd;
+  int8_t* Uq; int* uex;
 };
 
 }  // namespace gpsat
@@ -157,6 +159,7 @@ __device__ __forceinline__ void slot_set_expert(SlotDesc& d, const SlotMem& mem,
   d.A = mem.A; d.Wd = mem.Wd; d.Ld = mem.Ld; d.logdet = mem.logdet; d.quad = mem.quad;
   d.gpart = mem.gpart; d.notpd = mem.notpd;
   d.pre = nullptr; d.pre_s = nullptr; d.ldpre = 0;
+  d.Uq = mem.Uq; d.uex = mem.uex;
   *d.notpd = 0;
   *d.quad = 0.0;
 }

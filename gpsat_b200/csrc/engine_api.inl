@@ -16,6 +16,20 @@ int gpsat_engine_set_profile(gpsat_engine* h, int on) {
   return 0;
 }
 
+int gpsat_engine_set_lauum_path(gpsat_engine* h, int path) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  REQUIRE(path == GPSAT_LAUUM_DMMA || path == GPSAT_LAUUM_I8, "unknown lauum path");
+  h->e.i8_lauum = path == GPSAT_LAUUM_I8;
+  return 0;
+}
+
+int gpsat_engine_i8_timeouts(gpsat_engine* h, int* out) {
+  REQUIRE(h != nullptr && out != nullptr, "NULL argument");
+  CUDA_TRY(cudaStreamSynchronize(h->e.stream));
+  CUDA_TRY(cudaMemcpyFromSymbol(out, g_i8_timeout, sizeof(int)));
+  return 0;
+}
+
 void gpsat_fit_options_default(gpsat_fit_options* o) {
   o->pgtol = 1e-5;
   o->ftol = 2.220446049250313e-09;
@@ -52,6 +66,7 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
   CUDA_TRY(cudaEventCreate(&h->e.ev1));
   CUDA_TRY(cudaMallocHost(&h->e.h_counters, 4 * sizeof(int)));
   if (engine_setup_kernels()) { delete h; return 1; }
+  if (const char* lp = getenv("GPSAT_B200_LAUUM")) h->e.i8_lauum = strcmp(lp, "dmma") != 0;
   *out = h;
   return 0;
 }
@@ -63,7 +78,7 @@ int gpsat_engine_destroy(gpsat_engine* h) {
   cudaStreamSynchronize(g.stream);
   for (cudaEvent_t ev : g.evpool) cudaEventDestroy(ev);
   for (DevBuf* b : {&g.bX, &g.by, &g.bXs, &g.boffn, &g.boffm, &g.border, &g.btheta, &g.bmisc, &g.bslots,
-                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov, &g.bZ, &g.bsg})
+                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov, &g.bZ, &g.bsg, &g.bUq})
     b->release();
   if (g.h_counters) cudaFreeHost(g.h_counters);
   cudaEventDestroy(g.ev0); cudaEventDestroy(g.ev1);
@@ -118,7 +133,7 @@ int gpsat_gpr_lml_grad(gpsat_engine* h, const gpsat_batch* batch, int mem, const
   if (engine_load_batch(g, batch, mem, false, bd)) return 1;
   const int S = choose_slots(g, E, g.Tmax, g.Tmax, 0);
   int ld = 0;
-  if (engine_alloc_slots(g, S, g.Tmax, g.Tmax, ld)) return 1;
+  if (engine_alloc_slots(g, S, g.Tmax, g.Tmax, ld, grad != nullptr)) return 1;
   // device-side theta / outputs
   size_t o_theta = 0, o_lml = (size_t)E * P * 8, o_grad = o_lml + (size_t)E * 8, o_status = o_grad + (size_t)E * P * 8;
   if (g.bout.ensure(o_status + (size_t)E * 4)) return 1;
@@ -168,7 +183,7 @@ static int predict_impl(gpsat_engine* h, const gpsat_batch* batch, int mem, cons
   if (engine_load_batch(g, batch, mem, true, bd)) return 1;
   const int S = choose_slots(g, E, g.Tmax, g.TRmax, 0);
   int ld = 0;
-  if (engine_alloc_slots(g, S, g.Tmax, g.TRmax, ld)) return 1;
+  if (engine_alloc_slots(g, S, g.Tmax, g.TRmax, ld, false)) return 1;
   size_t o_theta = 0, o_lml = (size_t)E * P * 8, o_status = o_lml + (size_t)E * 8;
   size_t o_pred = (o_status + (size_t)E * 4 + 15) & ~(size_t)15;
   if (g.bout.ensure(o_pred + (size_t)std::max<int64_t>(M, 1) * 3 * 8)) return 1;

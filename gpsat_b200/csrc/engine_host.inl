@@ -34,6 +34,9 @@ struct Engine {
   std::vector<int> order;
   int Tmax = 0, TRmax = 0;
   // optional per-kernel timing (gpsat_engine_set_profile)
+  // K^-1 tile products of the gradient on the int8 tensor path (i8mma.cuh); GPSAT_B200_LAUUM=dmma turns it off
+  bool i8_lauum = true;
+  DevBuf bUq;
   bool profile = false;
   std::vector<cudaEvent_t> evpool;
   std::vector<int> evtype;          // kernel type of event pair k (events 2k, 2k+1)
@@ -79,6 +82,7 @@ static int engine_setup_kernels() {
   CUDA_TRY(cudaFuncSetAttribute(diag_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, DIAG_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STEP_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(lauum_grad_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_I8_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(sgpr_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SGPR_GEMM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(vff_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, VFF_GRAD_SMEM_BYTES));
   return 0;
@@ -149,7 +153,11 @@ static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with
 }
 
 // Carve per-slot scratch for S slots with `rows` x `ld` matrices.
-static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out) {
+static size_t i8_slot_bytes(int Tmax) {
+  return (size_t)Tmax * (Tmax + 1) / 2 * I8_S * I8_PLANE_B + (size_t)Tmax * NB * sizeof(int);
+}
+
+static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out, bool with_grad = true) {
   const int ld = Tmax * NB;
   const size_t rows = (size_t)TRmax * NB;
   const size_t a_d = rows * ld;
@@ -160,6 +168,9 @@ static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out
   if (g.bA.ensure(a_d * 8 * S) || g.bside.ensure(side_d * 8 * S) || g.bslots.ensure(sizeof(SlotDesc) * S) ||
       g.bmems.ensure(sizeof(SlotMem) * S))
     return 1;
+  const bool i8 = g.i8_lauum && with_grad;
+  const size_t uq_b = i8_slot_bytes(Tmax);
+  if (i8 && g.bUq.ensure(uq_b * S)) return 1;
   std::vector<SlotMem> mems(S);
   for (int s = 0; s < S; ++s) {
     double* sd = g.bside.as<double>() + side_d * s;
@@ -171,6 +182,8 @@ static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out
     m.quad = m.logdet + align_up(Tmax, 2);
     m.gpart = m.quad + 2;
     m.notpd = reinterpret_cast<int*>(m.gpart + ntile * PG);
+    m.Uq = i8 ? g.bUq.as<int8_t>() + uq_b * s : nullptr;
+    m.uex = i8 ? reinterpret_cast<int*>(m.Uq + (size_t)Tmax * (Tmax + 1) / 2 * I8_S * I8_PLANE_B) : nullptr;
   }
   CUDA_TRY(cudaMemcpyAsync(g.bmems.p, mems.data(), sizeof(SlotMem) * S, cudaMemcpyHostToDevice, g.stream));
   CUDA_TRY(cudaStreamSynchronize(g.stream));   // `mems` is a stack-lifetime source
@@ -182,7 +195,8 @@ static int choose_slots(Engine& g, int64_t E, int Tmax, int TRmax, int max_slots
   size_t free_b = 0, total_b = 0;
   cudaMemGetInfo(&free_b, &total_b);
   size_t per = (size_t)TRmax * NB * Tmax * NB * 8 + (size_t)2 * Tmax * NB * NB * 8 + (1 << 16);
-  size_t avail = (size_t)((free_b + g.bA.cap + g.bside.cap) * 0.80);
+  if (g.i8_lauum) per += i8_slot_bytes(Tmax);
+  size_t avail = (size_t)((free_b + g.bA.cap + g.bside.cap + g.bUq.cap) * 0.80);
   int64_t S = max_slots > 0 ? max_slots : 592;      // 4 x 148 SMs: amortises the per-step launches
   S = std::min<int64_t>(S, E);
   S = std::min<int64_t>(S, (int64_t)(avail / per));
@@ -209,8 +223,16 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, cons
   }
   if (do_inv && with_lauum) {
     ProfScope ps(g, PROF_LAUUM);
-    lauum_grad_kernel<<<dim3(Tmax * (Tmax + 1) / 2, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots);
-    g.stats.kernel_launches++;
+    const int ntile = Tmax * (Tmax + 1) / 2;
+    if (g.i8_lauum) {
+      u_rowmax_kernel<<<dim3(Tmax * NB / 8, S), 256, 0, g.stream>>>(slots);
+      u_slice_kernel<<<dim3(ntile, S), 256, 0, g.stream>>>(slots);
+      lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots);
+      g.stats.kernel_launches += 3;
+    } else {
+      lauum_grad_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots);
+      g.stats.kernel_launches++;
+    }
   }
   CUDA_TRY(cudaGetLastError());
   return 0;

@@ -162,6 +162,17 @@ class Engine:
         """Bracket every kernel launch with CUDA events; per-kernel times appear in :meth:`stats`."""
         _lib.check(self._lib.gpsat_engine_set_profile(self._h, int(bool(on))))
 
+    def set_lauum_path(self, path: str):
+        """``"i8"`` (default): K^-1 tile products of the gradient by error-free int8 slicing on the
+        tcgen05 tensor path; ``"dmma"``: FP64 ``mma.sync``.  Both give FP64-level results."""
+        _lib.check(self._lib.gpsat_engine_set_lauum_path(self._h, {"dmma": 0, "i8": 1}[path]))
+
+    def i8_timeouts(self) -> int:
+        """1 if a bounded barrier wait of the int8 path ever gave up (results invalid), else 0."""
+        out = C.c_int(0)
+        _lib.check(self._lib.gpsat_engine_i8_timeouts(self._h, C.byref(out)))
+        return int(out.value)
+
     @property
     def stream_ptr(self) -> int:
         """cudaStream_t of the engine (wrap with torch.cuda.ExternalStream to record events on it)."""

@@ -129,6 +129,16 @@ int gpsat_engine_stats(const gpsat_engine* eng, gpsat_stats* out);
 void* gpsat_engine_stream(const gpsat_engine* eng);
 /* on != 0: bracket every kernel launch with CUDA events and report per-kernel times in stats. */
 int gpsat_engine_set_profile(gpsat_engine* eng, int on);
+/* How the K^-1 tile products of the gradient (the LAUUM piece of the sweep, the inverse GPflow's
+ * autodiff forms implicitly at gpflow_models.py:317-321) are evaluated:
+ *   GPSAT_LAUUM_I8   (default) error-free int8 slicing on the tcgen05 tensor path, FP64-equivalent result
+ *   GPSAT_LAUUM_DMMA FP64 mma.sync
+ * The environment variable GPSAT_B200_LAUUM=dmma selects the second at engine creation. */
+#define GPSAT_LAUUM_DMMA 0
+#define GPSAT_LAUUM_I8 1
+int gpsat_engine_set_lauum_path(gpsat_engine* eng, int path);
+/* out = 1 if a bounded barrier wait of the int8 path ever gave up (a bug indicator; results invalid). */
+int gpsat_engine_i8_timeouts(gpsat_engine* eng, int* out);
 void gpsat_fit_options_default(gpsat_fit_options* opt);
 
 /* lml[e] = log marginal likelihood, grad[e][P] = d lml / d theta (constrained space). */

@@ -364,3 +364,30 @@ def test_gradient_matches_finite_differences_of_the_cuda_lml(engine):
         lm, _, _ = engine.lml_grad(b, tm[None, :], with_grad=False)
         fd = (lp[0] - lm[0]) / (2 * h)
         assert abs(fd - grad[0][p]) <= 2e-5 * max(1.0, abs(grad[0][p])), (p, fd, grad[0][p])
+
+
+@pytest.mark.parametrize("kind,D", [("Matern32", 3), ("RBF", 2), ("Matern52", 1)])
+def test_i8_gradient_path_matches_dmma_path(engine, kind, D):
+    """The K^-1 tile products of the gradient on the int8 tensor path (error-free slicing, i8mma.cuh)
+    against the FP64 mma.sync path on the same factor, and against the oracle: ragged sizes around
+    the tile and slab edges (k ranges of 1..5 blocks, partial last slabs, diagonal and off-diagonal tiles)."""
+    rng = np.random.default_rng(77 + D)
+    ns = [1, 15, 16, 31, 100, 127, 128, 129, 200, 256, 383, 600]
+    experts = [_expert(rng, n, D) for n in ns]
+    b = _batch(kind, experts, with_pred=False)
+    theta = np.stack([_theta(rng, D) for _ in ns])
+    try:
+        engine.set_lauum_path("dmma")
+        lml0, g0, st0 = engine.lml_grad(b, theta)
+        engine.set_lauum_path("i8")
+        lml1, g1, st1 = engine.lml_grad(b, theta)
+    finally:
+        engine.set_lauum_path("i8")
+    assert engine.i8_timeouts() == 0
+    assert np.all(st0 == 0) and np.all(st1 == 0)
+    np.testing.assert_array_equal(lml0, lml1)                  # the factorisation is the same code
+    for e, (X, y, _) in enumerate(experts):
+        scale = np.abs(g0[e]).max()
+        np.testing.assert_allclose(g1[e], g0[e], rtol=1e-10, atol=1e-11 * scale)
+        v, g = gpr.lml_and_grad(kind, X, y, theta[e])
+        np.testing.assert_allclose(g1[e], g, rtol=1e-7, atol=1e-8 * np.abs(g).max())

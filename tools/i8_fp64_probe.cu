@@ -1,0 +1,390 @@
+// Probe: FP64 tile products emulated on the int8 tensor path of sm_100a (tcgen05.mma kind::i8,
+// accumulators in TMEM) - the Ozaki splitting: every FP64 row is written as 2^e * sum_s q_s 2^(-7s)
+// with int8 slices q_s, slice products are exact int32 sums, and the groups s + t = g are recombined
+// in int64 / FP64.  Three modes, each bounded (no unbounded spin: a wait that does not complete
+// sets an error flag and returns):
+//   check : one 128 x 128 x 32 int8 MMA against the host                     (layout / descriptor)
+//   rate  : resident operands, 36 MMAs per 32-wide slab, N = 64 / 128 / 256     (int8 TOPS per GPU)
+//   emul  : C[128 x 128] = A[128 x K] B[128 x K]^T in FP64 via S slices, against a host FP64 product,
+//           timed on 148 x 4 CTAs next to the DMMA main loop of tools/mainloop_probe.cu
+//   nvcc -gencode arch=compute_100a,code=sm_100a -O3 -o build/i8_fp64_probe tools/i8_fp64_probe.cu
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <cuda_runtime.h>
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { \
+  fprintf(stderr, "CUDA error %s at %s:%d\n", cudaGetErrorString(e_), __FILE__, __LINE__); exit(1);} } while (0)
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// K-major operand without swizzle: 8-row x 16-byte core matrices; LBO = distance between the two
+// 16-byte K chunks of one MMA, SBO = distance between 8-row groups (both in bytes, multiples of 16)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;                       // descriptor version of sm_100
+  return d;
+}
+// instruction descriptor: D = s32, A = B = signed int8, both K-major, M = 128
+__host__ __device__ constexpr uint32_t idesc_i8(int n) {
+  return (2u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((128u >> 4) << 24);
+}
+__device__ __forceinline__ void mma_i8(uint32_t tmem_d, uint64_t a, uint64_t b, uint32_t idesc, uint32_t accumulate) {
+  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+               "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %6, %7, %8}, p;\n\t}\n"
+               :: "r"(tmem_d), "l"(a), "l"(b), "r"(idesc), "r"(accumulate), "r"(0), "r"(0), "r"(0), "r"(0) : "memory");
+}
+__device__ __forceinline__ void mma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" :: "r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" :: "r"(bar), "r"(count) : "memory");
+}
+// bounded wait: false when the phase did not complete within ~2^24 polls
+__device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
+  for (int spin = 0; spin < (1 << 24); ++spin) {
+    uint32_t done;
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
+                 : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    if (done) return true;
+  }
+  return false;
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" :: "r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" :: "r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory"); }
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+// 32 lanes x 16 consecutive 32-bit columns: thread l of the warp gets lane (lane base + l)
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                 "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+               : "r"(taddr) : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+}
+
+// operand plane in shared memory: [K / 16 chunks][rows][16 bytes]
+__device__ __forceinline__ uint32_t plane_off(int rows, int r, int k) { return (uint32_t)((k >> 4) * rows * 16 + r * 16 + (k & 15)); }
+
+// ---- mode check -----------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) check_kernel(const int8_t* __restrict__ A, const int8_t* __restrict__ B,
+                                                       int32_t* __restrict__ D, int* __restrict__ err) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint32_t tmem_base;
+  __shared__ __align__(8) uint64_t bar;
+  uint8_t* sa = smem;                 // 128 x 32
+  uint8_t* sb = smem + 4096;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  for (int i = tid; i < 128 * 32; i += 128) {
+    const int r = i / 32, k = i % 32;
+    sa[plane_off(128, r, k)] = (uint8_t)A[i];
+    sb[plane_off(128, r, k)] = (uint8_t)B[i];
+  }
+  if (tid == 0) { mbar_init(smem_u32(&bar), 1); asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_base), 128);
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tb = tmem_base;
+  if (tid == 0) {
+    mma_i8(tb, umma_desc(smem_u32(sa), 2048, 128), umma_desc(smem_u32(sb), 2048, 128), idesc_i8(128), 0);
+    mma_commit(smem_u32(&bar));
+  }
+  const bool ok = mbar_wait(smem_u32(&bar), 0);
+  tc_fence_after();
+  if (!ok) { if (tid == 0) *err = 1; }
+  else {
+    for (int c = 0; c < 128; c += 16) {
+      uint32_t v[16];
+      tmem_ld16(tb + ((uint32_t)(warp * 32) << 16) + c, v);
+      for (int j = 0; j < 16; ++j) D[(warp * 32 + lane) * 128 + c + j] = (int32_t)v[j];
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tb, 128);
+}
+
+// ---- mode rate ------------------------------------------------------------------------------------
+// 8 A planes and 8 B planes of one 32-wide slab stay resident; every "slab" issues the 36 slice pairs
+template <int N>
+__global__ void __launch_bounds__(128, 1) rate_kernel(int iters, int* __restrict__ err) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint32_t tmem_base;
+  __shared__ __align__(8) uint64_t bar;
+  constexpr int APL = 128 * 32, BPL = N * 32;
+  uint8_t* sa = smem;
+  uint8_t* sb = smem + 8 * APL;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < 8 * APL + 8 * BPL; i += 128) smem[i] = (uint8_t)((i * 37 + 11) & 3);
+  if (tid == 0) { mbar_init(smem_u32(&bar), 1); asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_base), 512);
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tb = tmem_base;
+  constexpr int NACC = 512 / N;
+  if (tid == 0) {
+    for (int it = 0; it < iters; ++it)
+      for (int g = 0; g < 8; ++g)
+        for (int s = 0; s <= g; ++s)
+          mma_i8(tb + (uint32_t)((g % NACC) * N), umma_desc(smem_u32(sa + s * APL), 128 * 16, 128),
+                 umma_desc(smem_u32(sb + (g - s) * BPL), N * 16, 128), idesc_i8(N), 1);
+    mma_commit(smem_u32(&bar));
+  }
+  const bool ok = mbar_wait(smem_u32(&bar), 0);
+  tc_fence_after();
+  if (!ok && tid == 0) *err = 1;
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tb, 512);
+}
+
+// ---- mode emul ------------------------------------------------------------------------------------
+constexpr int KB = 64;               // columns per scale block (all slice planes of one block are resident)
+constexpr int SMAX = 8;
+
+// exact power of two 2^p
+__device__ __forceinline__ double pow2i(int p) { return __longlong_as_double((long long)(p + 1023) << 52); }
+
+// S slices of a [128 x KB] FP64 block (row stride ld) into planes[s] (canonical layout) and the row scale
+// exponent into ex[r] (value = 2^(ex - 6) * sum_s q_s 2^(-7 s)); 256 threads, two per row
+template <int S>
+__device__ __forceinline__ void slice_block(const double* __restrict__ X, int ld, uint8_t* planes, int* ex, int tid) {
+  const int r = tid >> 1, h = tid & 1;
+  const double* row = X + (size_t)r * ld + h * 32;
+  double x[32];
+  double mx = 0.0;
+#pragma unroll
+  for (int j = 0; j < 32; ++j) { x[j] = row[j]; mx = fmax(mx, fabs(x[j])); }
+  mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, 1));
+  int e = 0;
+  if (mx > 0.0) e = (int)((__double_as_longlong(mx) >> 52) & 0x7ff) - 1022;     // mx < 2^e
+  if (h == 0) ex[r] = e;
+  const double sc = pow2i(6 - e);
+#pragma unroll
+  for (int j = 0; j < 32; ++j) x[j] *= sc;
+#pragma unroll
+  for (int s = 0; s < S; ++s) {
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {                // two 16-byte chunks per thread and plane
+      uint32_t w[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        uint32_t pk = 0;
+#pragma unroll
+        for (int b = 0; b < 4; ++b) {
+          const int j = c * 16 + q * 4 + b;
+          const int qi = __double2int_rn(x[j]);
+          x[j] = (x[j] - (double)qi) * 128.0;
+          pk |= ((uint32_t)qi & 0xffu) << (8 * b);
+        }
+        w[q] = pk;
+      }
+      *reinterpret_cast<uint4*>(planes + s * (128 * KB) + plane_off(128, r, h * 32 + c * 16)) = make_uint4(w[0], w[1], w[2], w[3]);
+    }
+  }
+}
+
+template <int S>
+__global__ void __launch_bounds__(256, 1) emul_kernel(const double* __restrict__ A, const double* __restrict__ B,
+                                                      double* __restrict__ C, int K, int slice_every, int* __restrict__ err) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint32_t tmem_base;
+  __shared__ __align__(8) uint64_t bar;
+  __shared__ int exA[128], exB[128];
+  constexpr int PL = 128 * KB;          // bytes per plane
+  uint8_t* sa = smem;
+  uint8_t* sb = smem + S * PL;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int row = (warp & 3) * 32 + lane, chalf = warp >> 2;      // accumulator row, 64-column half
+  const double* Ag = A + (size_t)blockIdx.x * 128 * K;
+  const double* Bg = B + (size_t)blockIdx.x * 128 * K;
+  if (tid == 0) { mbar_init(smem_u32(&bar), 1); asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_base), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tb = tmem_base;
+  double acc[64];
+#pragma unroll
+  for (int j = 0; j < 64; ++j) acc[j] = 0.0;
+  uint32_t parity = 0;
+  bool ok = true;
+  constexpr int NG = S;                                              // groups 0 .. S-1
+  for (int kb = 0; kb < K / KB; ++kb) {
+    if (kb % slice_every == 0) {
+      slice_block<S>(Ag + kb * KB, K, sa, exA, tid);
+      slice_block<S>(Bg + kb * KB, K, sb, exB, tid);
+      fence_async_smem();
+    }
+    __syncthreads();
+    for (int pass = 0; pass * 4 < NG; ++pass) {
+      const int g0 = pass * 4, g1 = (g0 + 4 < NG) ? g0 + 4 : NG;
+      if (tid == 0) {
+        tc_fence_after();
+        for (int g = g0; g < g1; ++g)
+          for (int s = 0; s <= g; ++s)
+            for (int k32 = 0; k32 < KB / 32; ++k32)
+              mma_i8(tb + (uint32_t)((g - g0) * 128), umma_desc(smem_u32(sa + s * PL + k32 * 2 * 2048), 2048, 128),
+                     umma_desc(smem_u32(sb + (g - s) * PL + k32 * 2 * 2048), 2048, 128), idesc_i8(128),
+                     (s > 0 || k32 > 0) ? 1u : 0u);
+        mma_commit(smem_u32(&bar));
+      }
+      ok = ok && mbar_wait(smem_u32(&bar), parity);
+      parity ^= 1;
+      tc_fence_after();
+      if (!ok) break;
+      // drain: sum_g G_g 2^(-7 g) in int64 (exact), one conversion and one FMA per element
+      const double rs = pow2i(exA[row] - 6 - 6 - 7 * (g1 - 1));
+#pragma unroll
+      for (int c = 0; c < 64; c += 16) {
+        long long sum[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) sum[j] = 0;
+        for (int g = g0; g < g1; ++g) {
+          uint32_t v[16];
+          tmem_ld16(tb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((g - g0) * 128 + chalf * 64 + c), v);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) sum[j] = sum[j] * 128 + (long long)(int32_t)v[j];
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j)
+          acc[c + j] = fma((double)sum[j] * rs, pow2i(exB[chalf * 64 + c + j]), acc[c + j]);
+      }
+      tc_fence_before();
+      __syncthreads();
+    }
+    if (!ok) break;
+  }
+  if (!ok) { if (tid == 0) *err = 1; }
+  else {
+    double* Cg = C + (size_t)blockIdx.x * 128 * 128 + (size_t)row * 128 + chalf * 64;
+#pragma unroll
+    for (int j = 0; j < 64; j += 2) *reinterpret_cast<double2*>(Cg + j) = make_double2(acc[j], acc[j + 1]);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tb, 512);
+}
+
+// ---- host -----------------------------------------------------------------------------------------
+static int run_check() {
+  std::vector<int8_t> A(128 * 32), B(128 * 32);
+  srand(1);
+  for (auto& v : A) v = (int8_t)(rand() % 129 - 64);
+  for (auto& v : B) v = (int8_t)(rand() % 129 - 64);
+  int8_t *dA, *dB; int32_t* dD; int* derr;
+  CK(cudaMalloc(&dA, A.size())); CK(cudaMalloc(&dB, B.size())); CK(cudaMalloc(&dD, 128 * 128 * 4)); CK(cudaMalloc(&derr, 4));
+  CK(cudaMemcpy(dA, A.data(), A.size(), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(dB, B.data(), B.size(), cudaMemcpyHostToDevice));
+  CK(cudaMemset(dD, 0xff, 128 * 128 * 4)); CK(cudaMemset(derr, 0, 4));
+  check_kernel<<<1, 128, 8192>>>(dA, dB, dD, derr);
+  CK(cudaDeviceSynchronize());
+  std::vector<int32_t> D(128 * 128); int err = 0;
+  CK(cudaMemcpy(D.data(), dD, D.size() * 4, cudaMemcpyDeviceToHost)); CK(cudaMemcpy(&err, derr, 4, cudaMemcpyDeviceToHost));
+  long bad = 0;
+  for (int m = 0; m < 128; ++m)
+    for (int n = 0; n < 128; ++n) {
+      int32_t ref = 0;
+      for (int k = 0; k < 32; ++k) ref += (int32_t)A[m * 32 + k] * (int32_t)B[n * 32 + k];
+      if (ref != D[m * 128 + n]) { if (bad < 4) fprintf(stderr, "mismatch (%d,%d): got %d want %d\n", m, n, D[m * 128 + n], ref); ++bad; }
+    }
+  printf("\"check\": {\"timeout\": %d, \"mismatches\": %ld}", err, bad);
+  return (err || bad) ? 1 : 0;
+}
+
+template <int N>
+static void run_rate(bool first) {
+  const int iters = 2000, grid = 148;
+  const int smem = 8 * 128 * 32 + 8 * N * 32;
+  int* derr; CK(cudaMalloc(&derr, 4)); CK(cudaMemset(derr, 0, 4));
+  CK(cudaFuncSetAttribute(rate_kernel<N>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  rate_kernel<N><<<grid, 128, smem>>>(50, derr);
+  CK(cudaDeviceSynchronize());
+  CK(cudaEventRecord(e0));
+  rate_kernel<N><<<grid, 128, smem>>>(iters, derr);
+  CK(cudaEventRecord(e1));
+  CK(cudaDeviceSynchronize());
+  float ms; CK(cudaEventElapsedTime(&ms, e0, e1));
+  int err; CK(cudaMemcpy(&err, derr, 4, cudaMemcpyDeviceToHost));
+  const double tops = (double)grid * iters * 36 * 2.0 * 128 * N * 32 / (ms * 1e-3) / 1e12;
+  printf("%s\"n%d\": {\"int8_tops\": %.1f, \"ms\": %.3f, \"timeout\": %d}", first ? "" : ", ", N, tops, ms, err);
+}
+
+template <int S>
+static void run_emul(bool first) {
+  const int K = 1024, grid = 148 * 4;
+  const size_t nA = (size_t)grid * 128 * K;
+  std::vector<double> A(nA), B(nA);
+  srand(7);
+  for (size_t i = 0; i < nA; ++i) {
+    // entries of very different magnitude inside a row, as in the rows of a Cholesky factor
+    A[i] = (rand() / (double)RAND_MAX - 0.5) * std::pow(10.0, -(double)(rand() % 7));
+    B[i] = (rand() / (double)RAND_MAX - 0.5) * std::pow(10.0, -(double)(rand() % 7));
+  }
+  double *dA, *dB, *dC; int* derr;
+  CK(cudaMalloc(&dA, nA * 8)); CK(cudaMalloc(&dB, nA * 8)); CK(cudaMalloc(&dC, (size_t)grid * 128 * 128 * 8)); CK(cudaMalloc(&derr, 4));
+  CK(cudaMemcpy(dA, A.data(), nA * 8, cudaMemcpyHostToDevice)); CK(cudaMemcpy(dB, B.data(), nA * 8, cudaMemcpyHostToDevice));
+  CK(cudaMemset(derr, 0, 4));
+  const int smem = 2 * S * 128 * KB;
+  CK(cudaFuncSetAttribute(emul_kernel<S>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  emul_kernel<S><<<grid, 256, smem>>>(dA, dB, dC, K, 1, derr);
+  CK(cudaDeviceSynchronize());
+  int err; CK(cudaMemcpy(&err, derr, 4, cudaMemcpyDeviceToHost));
+  // accuracy on the first two tiles: |C - ref| against sum |a||b| (the FP64 dot-product error scale)
+  std::vector<double> C((size_t)2 * 128 * 128);
+  CK(cudaMemcpy(C.data(), dC, C.size() * 8, cudaMemcpyDeviceToHost));
+  double worst = 0.0;
+  for (int t = 0; t < 2; ++t)
+    for (int m = 0; m < 128; ++m)
+      for (int n = 0; n < 128; ++n) {
+        long double ref = 0, mag = 0;
+        const double* a = &A[((size_t)t * 128 + m) * K];
+        const double* b = &B[((size_t)t * 128 + n) * K];
+        for (int k = 0; k < K; ++k) { ref += (long double)a[k] * b[k]; mag += fabsl((long double)a[k] * b[k]); }
+        const double e = (double)(fabsl((long double)C[((size_t)t * 128 + m) * 128 + n] - ref) / mag);
+        if (e > worst) worst = e;
+      }
+  cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  float ms_full, ms_pre;
+  CK(cudaEventRecord(e0));
+  for (int r = 0; r < 3; ++r) emul_kernel<S><<<grid, 256, smem>>>(dA, dB, dC, K, 1, derr);
+  CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
+  CK(cudaEventElapsedTime(&ms_full, e0, e1));
+  CK(cudaEventRecord(e0));
+  for (int r = 0; r < 3; ++r) emul_kernel<S><<<grid, 256, smem>>>(dA, dB, dC, K, 1 << 20, derr);     // slices of block 0 reused
+  CK(cudaEventRecord(e1)); CK(cudaDeviceSynchronize());
+  CK(cudaEventElapsedTime(&ms_pre, e0, e1));
+  const double fl = 3.0 * grid * 2.0 * 128 * 128 * K;
+  printf("%s\"s%d\": {\"timeout\": %d, \"max_err_over_sum_abs\": %.3e, \"tflops_fp64_equiv_with_slicing\": %.2f, "
+         "\"tflops_fp64_equiv_resident_slices\": %.2f}", first ? "" : ", ", S, err, worst, fl / (ms_full * 1e-3) / 1e12,
+         fl / (ms_pre * 1e-3) / 1e12);
+  CK(cudaFree(dA)); CK(cudaFree(dB)); CK(cudaFree(dC));
+}
+
+int main(int argc, char** argv) {
+  const char* mode = argc > 1 ? argv[1] : "check";
+  printf("{");
+  int rc = 0;
+  if (!strcmp(mode, "check")) rc = run_check();
+  else if (!strcmp(mode, "rate")) { printf("\"rate\": {"); run_rate<64>(true); run_rate<128>(false); run_rate<256>(false); printf("}"); }
+  else if (!strcmp(mode, "emul")) { printf("\"emul\": {"); run_emul<6>(true); run_emul<7>(false); run_emul<8>(false); printf("}"); }
+  printf("}\n");
+  return rc;
+}
