@@ -310,6 +310,10 @@ def run_ours(args):
                            "parallelism": f"experts sharded x{world}, no collective on the hot path",
                            "l2": "256 MB flush written between steps; per-step working set "
                                  f"{int(collect['fit'][-1]['slots'])} slot matrices >> 126 MB L2",
+                           "arithmetic": "FP64 throughout; the K^-1 tile products of the gradient are FP64 values split "
+                                         "into 7 exact int8 slices and multiplied on the int8 tensor path (tcgen05, "
+                                         "error 5e-14 of sum|a||b|); GPSAT_B200_LAUUM=dmma runs them as FP64 mma.sync"
+                                         if os.environ.get("GPSAT_B200_LAUUM", "i8") != "dmma" else "FP64 mma.sync throughout",
                            "mean_evals_per_expert": float(nev.mean()), "max_evals_per_expert": int(nev.max()),
                            "ticks_per_fit": int(collect["fit"][-1]["ticks"]), "slots": int(collect["fit"][-1]["slots"]),
                            "status_counts": {"ok": int(st[0]), "not_pd": int(st[1]), "linesearch": int(st[2]), "maxiter": int(st[3])}},

@@ -66,7 +66,11 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
   CUDA_TRY(cudaEventCreate(&h->e.ev1));
   CUDA_TRY(cudaMallocHost(&h->e.h_counters, 4 * sizeof(int)));
   if (engine_setup_kernels()) { delete h; return 1; }
-  if (const char* lp = getenv("GPSAT_B200_LAUUM")) h->e.i8_lauum = strcmp(lp, "dmma") != 0;
+  if (const char* lp = getenv("GPSAT_B200_LAUUM")) {
+    h->e.i8_lauum = strcmp(lp, "dmma") != 0;
+    h->e.i8_persistent = strcmp(lp, "i8p") == 0;
+  }
+  h->e.num_sms = prop.multiProcessorCount;
   *out = h;
   return 0;
 }

@@ -36,6 +36,9 @@ struct Engine {
   // optional per-kernel timing (gpsat_engine_set_profile)
   // K^-1 tile products of the gradient on the int8 tensor path (i8mma.cuh); GPSAT_B200_LAUUM=dmma turns it off
   bool i8_lauum = true;
+  bool i8_persistent = false;       // GPSAT_B200_LAUUM=i8p: warp-specialised persistent variant (experimental, slower so far)
+  int num_sms = 148;
+  int cur_kind = GPSAT_MATERN32, cur_D = 3;     // kernel family / input dimension of the loaded batch
   DevBuf bUq;
   bool profile = false;
   std::vector<cudaEvent_t> evpool;
@@ -83,6 +86,11 @@ static int engine_setup_kernels() {
   CUDA_TRY(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STEP_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_I8_SMEM_BYTES));
+#define I8P_ATTR(K) \
+  CUDA_TRY(cudaFuncSetAttribute(lauum_grad_i8p_kernel<K, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_I8P_SMEM_BYTES)); \
+  CUDA_TRY(cudaFuncSetAttribute(lauum_grad_i8p_kernel<K, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_I8P_SMEM_BYTES));
+  I8P_ATTR(GPSAT_MATERN12) I8P_ATTR(GPSAT_MATERN32) I8P_ATTR(GPSAT_MATERN52) I8P_ATTR(GPSAT_RBF)
+#undef I8P_ATTR
   CUDA_TRY(cudaFuncSetAttribute(sgpr_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SGPR_GEMM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(vff_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, VFF_GRAD_SMEM_BYTES));
   return 0;
@@ -131,6 +139,7 @@ static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with
   CUDA_TRY(cudaMemcpyAsync(g.border.p, g.order.data(), E * 4, cudaMemcpyHostToDevice, g.stream));
   g.stats.h2d_bytes += (double)(E + 1) * 8 * (with_pred ? 2 : 1) + E * 4;
   out.kind = b->kernel; out.D = D; out.P = D + 2; out.E = E;
+  g.cur_kind = b->kernel; g.cur_D = D;
   out.off_n = g.boffn.as<int64_t>();
   out.off_m = with_pred ? g.boffm.as<int64_t>() : nullptr;
   out.order = g.border.as<int>();
@@ -203,6 +212,23 @@ static int choose_slots(Engine& g, int64_t E, int Tmax, int TRmax, int max_slots
   return (int)std::max<int64_t>(S, 1);
 }
 
+template <int KIND>
+static void launch_i8p_k(Engine& g, const SlotDesc* slots, int S, int ntile) {
+  const int grid = std::min(g.num_sms, ntile * S);
+  if (g.cur_D == 3)
+    lauum_grad_i8p_kernel<KIND, 3><<<grid, I8P_THREADS, LAUUM_I8P_SMEM_BYTES, g.stream>>>(slots, S, ntile);
+  else
+    lauum_grad_i8p_kernel<KIND, 0><<<grid, I8P_THREADS, LAUUM_I8P_SMEM_BYTES, g.stream>>>(slots, S, ntile);
+}
+static void launch_i8p(Engine& g, const SlotDesc* slots, int S, int ntile) {
+  switch (g.cur_kind) {
+    case GPSAT_MATERN12: launch_i8p_k<GPSAT_MATERN12>(g, slots, S, ntile); break;
+    case GPSAT_MATERN32: launch_i8p_k<GPSAT_MATERN32>(g, slots, S, ntile); break;
+    case GPSAT_MATERN52: launch_i8p_k<GPSAT_MATERN52>(g, slots, S, ntile); break;
+    default: launch_i8p_k<GPSAT_RBF>(g, slots, S, ntile); break;
+  }
+}
+
 // One blocked sweep over all occupied slots.
 static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, const SlotDesc* slots = nullptr,
                         bool with_lauum = true) {
@@ -227,7 +253,10 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, cons
     if (g.i8_lauum) {
       u_rowmax_kernel<<<dim3(Tmax * NB / 8, S), 256, 0, g.stream>>>(slots);
       u_slice_kernel<<<dim3(ntile, S), 256, 0, g.stream>>>(slots);
-      lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots);
+      if (g.i8_persistent)
+        launch_i8p(g, slots, S, ntile);
+      else
+        lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots);
       g.stats.kernel_launches += 3;
     } else {
       lauum_grad_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots);

@@ -101,6 +101,10 @@ __device__ __forceinline__ void tmem_ld_fence(uint32_t (&v)[16]) {
   asm volatile("" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]),
                     "+r"(v[8]), "+r"(v[9]), "+r"(v[10]), "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]) :: "memory");
 }
+// exact int32 -> double without a conversion instruction: 2^52 + 2^31 + v, then subtract the offset
+__device__ __forceinline__ double i32_to_f64(uint32_t v) {
+  return __hiloint2double(0x43300000, (int)(v ^ 0x80000000u)) - 4503601774854144.0;
+}
 __device__ __forceinline__ double pow2i(int p) { return __longlong_as_double((long long)(p + 1023) << 52); }
 
 // index of tile (j, k), k >= j, in the packed upper block triangle
@@ -205,7 +209,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   double* red = ac + NB;
   __shared__ __align__(8) uint64_t bars[2 * I8_NST + 1];            // full[NST], empty[NST], accumulators ready
   __shared__ uint32_t tmem_base;
-  __shared__ int exc[NB];
+  __shared__ double csd[NB];                                    // 2^e of the column block rows
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n = d.n, ld = d.ld;
   const int kend = lauum_kend(n);
@@ -217,7 +221,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   if (warp == 0) tmem_alloc(smem_u32(&tmem_base), 512);
   load_block_coords(d, i * NB, xr, ar, tid);      // ar / ac overwritten with alpha below
   load_block_coords(d, j * NB, xc, ac, tid);
-  if (tid < NB) exc[tid] = d.uex[j * NB + tid];
+  if (tid < NB) csd[tid] = pow2i(d.uex[j * NB + tid]);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -318,20 +322,18 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
           if (g < g1 - g0)
             tmem_ld16_nowait(tb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(g * NB + chalf * 64 + c), v[g]);
         tmem_ld_wait();
-        long long sum[16];
-#pragma unroll
-        for (int q = 0; q < 16; ++q) sum[q] = 0;
+        // Horner over the groups in FP64: every partial sum is an integer below 2^53, so this is exact
+        double sum[16];
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           if (g < g1 - g0) {
             tmem_ld_fence(v[g]);
 #pragma unroll
-            for (int q = 0; q < 16; ++q) sum[q] = sum[q] * 128 + (long long)(int32_t)v[g][q];
+            for (int q = 0; q < 16; ++q) sum[q] = g == 0 ? i32_to_f64(v[g][q]) : fma(sum[q], 128.0, i32_to_f64(v[g][q]));
           }
         }
 #pragma unroll
-        for (int q = 0; q < 16; ++q)
-          acc[c + q] = fma((double)sum[q] * rs, pow2i(exc[chalf * 64 + c + q]), acc[c + q]);
+        for (int q = 0; q < 16; ++q) acc[c + q] = fma(sum[q] * rs, csd[chalf * 64 + c + q], acc[c + q]);
       }
     }
     tc_fence_before();
@@ -362,6 +364,277 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
     for (int w8 = 0; w8 < 8; ++w8) v += red[w8 * 8 + tid];
     d.gpart[(size_t)t * (GPSAT_DMAX + 2) + tid] = v;
   }
+}
+
+// ---- persistent variant: warp-specialised, gradient reduction from registers -----------------------------
+// One CTA per SM walks the (slot, tile) list.  Warp 8 streams the slab planes, warp 9 issues the MMAs, warps
+// 0..7 drain the accumulators and reduce the tile against dK/dtheta straight from registers, so the
+// covariance-derivative epilogue of tile t runs while the tensor pipe works on tile t + 1.
+constexpr int I8P_THREADS = 320;
+constexpr int I8P_EPI = 256;
+constexpr int LAUUM_I8P_SMEM_BYTES = I8_PIPE_B + (SM_XY_D + 64) * 8 + 128;
+
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 256;\n" ::: "memory"); }
+
+__device__ __forceinline__ void tmem_ld8_nowait(uint32_t taddr, uint32_t (&v)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];\n"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7])
+               : "r"(taddr) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_fence8(uint32_t (&v)[8]) {
+  asm volatile("" : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]) :: "memory");
+}
+
+// work item w -> (slot, tile); false when the item is empty
+__device__ __forceinline__ bool i8p_item(const SlotDesc* __restrict__ slots, int w, int ntile_max, int& slot, int& t) {
+  slot = w / ntile_max;
+  t = w - slot * ntile_max;
+  const SlotDesc& d = slots[slot];
+  return d.expert >= 0 && t < d.T * (d.T + 1) / 2;
+}
+__device__ __forceinline__ void i8p_tile_ij(int t, int& i, int& j) {
+  i = (int)((sqrt(8.0 * t + 1.0) - 1.0) * 0.5);
+  while (i * (i + 1) / 2 > t) --i;
+  while ((i + 1) * (i + 2) / 2 <= t) ++i;
+  j = t - i * (i + 1) / 2;
+}
+
+// Gradient partial sums of one row of the Q tile held in registers: row gi, columns g0c + c0 .. + 63.
+// Same arithmetic as grad_tile_t, mapped one row per thread (column data are warp-wide broadcasts).
+template <int KIND, int DD>
+__device__ __forceinline__ void grad_row_t(const SlotDesc& d, int gi, int g0r, int g0c, int c0, const double* xrow,
+                                           double arv, const double* xc, const double* ac, const double (&acc)[64],
+                                           double* part) {
+  const int n = d.n, D = d.D;
+  constexpr int ND = DD > 0 ? DD : GPSAT_DMAX;
+  double pd[ND], pk = 0.0, pn = 0.0;
+#pragma unroll
+  for (int dd = 0; dd < ND; ++dd) pd[dd] = 0.0;
+  const bool interior = g0r + NB <= n && g0r > g0c;
+  if (gi < n) {
+#pragma unroll
+    for (int q = 0; q < 64; ++q) {
+      const int c = c0 + q, gj = g0c + c;
+      if (interior || gj <= gi) {
+        const double aa = arv * ac[c];
+        const double qv = aa - (acc[q] - aa);          // the tile holds Ks^-1 + alpha alpha^T
+        const double wq = (gi == gj) ? qv : 2.0 * qv;
+        double sd[ND], r2 = 0.0;
+#pragma unroll
+        for (int dd = 0; dd < ND; ++dd) {
+          const double tdd = (DD > 0 || dd < D) ? xrow[dd] - xc[dd * NB + c] : 0.0;
+          sd[dd] = tdd * tdd;
+          r2 += sd[dd];
+        }
+        double ku, gu;
+        kunit_gunit_of_r2<KIND>(r2, ku, gu);
+        const double wg = wq * gu;
+#pragma unroll
+        for (int dd = 0; dd < ND; ++dd) pd[dd] = fma(wg, sd[dd], pd[dd]);
+        pk = fma(wq, ku, pk);
+        if (gi == gj) pn += qv;
+      }
+    }
+  }
+#pragma unroll
+  for (int dd = 0; dd < GPSAT_DMAX; ++dd) part[dd] = dd < ND ? pd[dd < ND ? dd : 0] : 0.0;
+  part[GPSAT_DMAX] = pk;
+  part[GPSAT_DMAX + 1] = pn;
+}
+
+template <int KIND, int DD>
+__global__ void __launch_bounds__(I8P_THREADS, 1) lauum_grad_i8p_kernel(const SlotDesc* __restrict__ slots, int S,
+                                                                       int ntile_max) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  double* xr = reinterpret_cast<double*>(smem_raw + I8_PIPE_B);
+  double* xc = xr + NB * GPSAT_DMAX;
+  double* ar = xc + NB * GPSAT_DMAX;
+  double* ac = ar + NB;
+  double* red = ac + NB;
+  // full[NST], empty[NST], accumulators ready (MMA -> epilogue), accumulators drained (epilogue -> MMA)
+  __shared__ __align__(8) uint64_t bars[2 * I8_NST + 2];
+  __shared__ uint32_t tmem_base;
+  __shared__ double csd[NB];                                    // 2^e of the column block rows
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int b = 0; b < 2 * I8_NST + 1; ++b) mbar_init(smem_u32(&bars[b]), 1);
+    mbar_init(smem_u32(&bars[2 * I8_NST + 1]), I8P_EPI / 32);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_base), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tb = tmem_base;
+  const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[I8_NST]);
+  const uint32_t accfull = smem_u32(&bars[2 * I8_NST]), accfree = smem_u32(&bars[2 * I8_NST + 1]);
+  const uint32_t pipe_s = smem_u32(smem_raw);
+  const int W = S * ntile_max;
+  bool ok = true;
+
+  if (warp == 8) {
+    // ---- producer ----
+    if (lane == 0) {
+      int it = 0;
+      for (int w = blockIdx.x; w < W && ok; w += gridDim.x) {
+        int slot, t, i, j;
+        if (!i8p_item(slots, w, ntile_max, slot, t)) continue;
+        const SlotDesc& d = slots[slot];
+        i8p_tile_ij(t, i, j);
+        const int T = d.T;
+        const bool same = i == j;
+        const int last_slabs = (lauum_kend(d.n) - (T - 1) * NB + I8_SLAB_K - 1) / I8_SLAB_K;
+        for (int pass = 0; pass < 2 && ok; ++pass) {
+          const int np = pass == 0 ? 4 : I8_S;
+          for (int kb = i; kb < T && ok; ++kb) {
+            const int8_t* ga = d.Uq + (size_t)utile_index(T, i, kb) * I8_S * I8_PLANE_B;
+            const int8_t* gb = d.Uq + (size_t)utile_index(T, j, kb) * I8_S * I8_PLANE_B;
+            const int nsl = kb == T - 1 ? last_slabs : NB / I8_SLAB_K;
+            for (int sl = 0; sl < nsl; ++sl, ++it) {
+              const int st = it % I8_NST;
+              if (it >= I8_NST) ok = ok && mbar_wait(empty0 + 8 * st, ((it / I8_NST) - 1) & 1);
+              if (!ok) break;
+              const uint32_t fb = full0 + 8 * st, sbase = pipe_s + st * I8_STAGE_B;
+              mbar_expect_tx(fb, (same ? np : 2 * np) * I8_SLAB_B);
+              bulk_g2s(sbase, ga + (size_t)sl * (I8_S * I8_SLAB_B), np * I8_SLAB_B, fb);
+              if (!same) bulk_g2s(sbase + I8_S * I8_SLAB_B, gb + (size_t)sl * (I8_S * I8_SLAB_B), np * I8_SLAB_B, fb);
+            }
+          }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 9) {
+    // ---- MMA issue ----
+    if (lane == 0) {
+      const uint64_t desc0 = umma_desc_kmajor(pipe_s, NB * 16, 128);
+      int it = 0, npass = 0;
+      for (int w = blockIdx.x; w < W && ok; w += gridDim.x) {
+        int slot, t, i, j;
+        if (!i8p_item(slots, w, ntile_max, slot, t)) continue;
+        const SlotDesc& d = slots[slot];
+        i8p_tile_ij(t, i, j);
+        const int T = d.T;
+        const bool same = i == j;
+        const int last_slabs = (lauum_kend(d.n) - (T - 1) * NB + I8_SLAB_K - 1) / I8_SLAB_K;
+        const int nslabs = (T - 1 - i) * (NB / I8_SLAB_K) + last_slabs;
+        for (int pass = 0; pass < 2 && ok; ++pass, ++npass) {
+          if (npass > 0) ok = ok && mbar_wait(accfree, (npass - 1) & 1);      // previous pass drained
+          tc_fence_after();
+          for (int sl = 0; sl < nslabs && ok; ++sl, ++it) {
+            const int st = it % I8_NST;
+            ok = ok && mbar_wait(full0 + 8 * st, (it / I8_NST) & 1);
+            if (!ok) break;
+            tc_fence_after();
+            const uint64_t adesc = desc0 + (uint64_t)((st * I8_STAGE_B) >> 4);
+            const uint64_t bdesc = same ? adesc : adesc + (uint64_t)((I8_S * I8_SLAB_B) >> 4);
+            const uint32_t acc0 = sl == 0 ? 0u : 1u;
+            if (pass == 0) {
+#pragma unroll
+              for (int g = 0; g < 4; ++g)
+#pragma unroll
+                for (int s = 0; s <= g; ++s)
+                  umma_i8(tb + (uint32_t)(g * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
+                          bdesc + (uint64_t)((g - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
+            } else {
+#pragma unroll
+              for (int g = 4; g < I8_S; ++g)
+#pragma unroll
+                for (int s = 0; s <= g; ++s)
+                  if (s <= I8_S - 1 && g - s <= I8_S - 1)
+                    umma_i8(tb + (uint32_t)((g - 4) * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
+                            bdesc + (uint64_t)((g - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
+            }
+            umma_commit(empty0 + 8 * st);
+          }
+          umma_commit(accfull);
+        }
+      }
+    }
+    __syncwarp();
+  } else {
+    // ---- epilogue warps 0..7: drain both passes, reduce against dK/dtheta from registers ----
+    const int row = (warp & 3) * 32 + lane, chalf = warp >> 2;
+    const uint32_t trow = tb + ((uint32_t)((warp & 3) * 32) << 16);
+    int npass = 0;
+    for (int w = blockIdx.x; w < W; w += gridDim.x) {
+      int slot, t, i, j;
+      if (!i8p_item(slots, w, ntile_max, slot, t)) continue;
+      const SlotDesc& d = slots[slot];
+      i8p_tile_ij(t, i, j);
+      const int n = d.n, ld = d.ld;
+      epi_bar_sync();                                  // the previous tile is done with xr / xc / ar / ac / red
+      load_block_coords(d, i * NB, xr, ar, tid);
+      load_block_coords(d, j * NB, xc, ac, tid);
+      if (tid < NB) csd[tid] = pow2i(d.uex[j * NB + tid]);
+      epi_bar_sync();
+      if (tid < NB) {
+        const int gi = i * NB + tid, gj = j * NB + tid;
+        ar[tid] = (gi < n) ? -d.A[(size_t)gi * ld + n] : 0.0;
+        ac[tid] = (gj < n) ? -d.A[(size_t)gj * ld + n] : 0.0;
+      }
+      epi_bar_sync();
+      double xrow[GPSAT_DMAX];
+#pragma unroll
+      for (int dd = 0; dd < GPSAT_DMAX; ++dd) xrow[dd] = dd < d.D ? xr[dd * NB + row] : 0.0;
+      const double arv = ar[row];
+      const int exrow = d.uex[i * NB + row];
+      double acc[64];
+#pragma unroll
+      for (int q = 0; q < 64; ++q) acc[q] = 0.0;
+#pragma unroll 1
+      for (int pass = 0; pass < 2; ++pass, ++npass) {
+        const int ng = pass == 0 ? 4 : I8_S - 4;
+        if (tid == 0) ok = ok && mbar_wait(accfull, npass & 1);     // one poller; the other warps sleep in the barrier
+        epi_bar_sync();
+        tc_fence_after();
+        {
+          const double rs = pow2i(exrow - 12 - 7 * (pass * 4 + ng - 1));
+#pragma unroll
+          for (int c = 0; c < 64; c += 8) {
+            uint32_t v[4][8];
+#pragma unroll
+            for (int g = 0; g < 4; ++g)
+              if (g < ng) tmem_ld8_nowait(trow + (uint32_t)(g * NB + chalf * 64 + c), v[g]);
+            tmem_ld_wait();
+            double sum[8];
+#pragma unroll
+            for (int g = 0; g < 4; ++g) {
+              if (g < ng) {
+                tmem_ld_fence8(v[g]);
+#pragma unroll
+                for (int q = 0; q < 8; ++q) sum[q] = g == 0 ? i32_to_f64(v[g][q]) : fma(sum[q], 128.0, i32_to_f64(v[g][q]));
+              }
+            }
+#pragma unroll
+            for (int q = 0; q < 8; ++q) acc[c + q] = fma(sum[q] * rs, csd[chalf * 64 + c + q], acc[c + q]);
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(accfree);
+      }
+      double part[GPSAT_DMAX + 2];
+      const int gi = i * NB + row;
+      grad_row_t<KIND, DD>(d, gi, i * NB, j * NB, chalf * 64, xrow, arv, xc, ac, acc, part);
+#pragma unroll
+      for (int p = 0; p < GPSAT_DMAX + 2; ++p) {
+        double v = part[p];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) red[warp * 8 + p] = v;
+      }
+      epi_bar_sync();
+      if (tid < GPSAT_DMAX + 2) {
+        double v = 0.0;
+        for (int w8 = 0; w8 < 8; ++w8) v += red[w8 * 8 + tid];
+        d.gpart[(size_t)t * (GPSAT_DMAX + 2) + tid] = v;
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tb, 512);
 }
 
 }  // namespace gpsat

@@ -6,7 +6,7 @@ OUT=gpurun_out
 set -x
 python tools/ncu_target.py 296 800 1200 2 > $OUT/${TAG}_i8_plain.log 2>&1 || exit 1
 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"lauum|u_slice|u_rowmax" --csv --log-file $OUT/${TAG}_i8_launches.csv python tools/ncu_target.py 296 800 1200 2 > $OUT/ncu_il.log 2>&1
-for k in lauum_grad_i8_kernel u_slice_kernel; do
+for k in lauum_grad_i8p_kernel; do
   ncu --set full --clock-control none --import-source on -k regex:$k -s 1 -c 1 -o /tmp/${TAG}_$k python tools/ncu_target.py 296 800 1200 2 > $OUT/ncu_$k.log 2>&1
   ncu -i /tmp/${TAG}_$k.ncu-rep --page raw --csv > /tmp/${k}_raw.csv 2>/dev/null
   python - <<PY > $OUT/${TAG}_${k}_raw_selected.txt
