@@ -23,6 +23,17 @@ int gpsat_engine_set_lauum_path(gpsat_engine* h, int path) {
   return 0;
 }
 
+int gpsat_engine_i8_phases(gpsat_engine* h, uint64_t* out8, int reset) {
+  REQUIRE(h != nullptr && out8 != nullptr, "NULL argument");
+  CUDA_TRY(cudaStreamSynchronize(h->e.stream));
+  CUDA_TRY(cudaMemcpyFromSymbol(out8, g_i8_phase, 8 * sizeof(uint64_t)));
+  if (reset) {
+    uint64_t z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    CUDA_TRY(cudaMemcpyToSymbol(g_i8_phase, z, sizeof(z)));
+  }
+  return 0;
+}
+
 int gpsat_engine_i8_timeouts(gpsat_engine* h, int* out) {
   REQUIRE(h != nullptr && out != nullptr, "NULL argument");
   CUDA_TRY(cudaStreamSynchronize(h->e.stream));

@@ -34,6 +34,14 @@ constexpr int LAUUM_I8_SMEM_BYTES = I8_PIPE_B + (SM_XY_D + 64) * 8 + 128;
 constexpr int I8_EXP_CLAMP = 400;
 
 __device__ int g_i8_timeout = 0;                 // set when a bounded barrier wait gives up (debug aid)
+// cycles per phase of lauum_grad_i8_kernel summed over CTAs (thread 0's clock): prologue, pass-0 MMAs, drain 0,
+// pass-1 MMAs, drain 1, Q tile store, gradient reduction, tile count.  Built with -DGPSAT_I8_PHASES only.
+__device__ unsigned long long g_i8_phase[8];
+#ifdef GPSAT_I8_PHASES
+#define I8_PHASE(k) do { if (tid == 0) { long long now_ = clock64(); atomicAdd(&g_i8_phase[k], (unsigned long long)(now_ - tphase)); tphase = now_; } } while (0)
+#else
+#define I8_PHASE(k) do { } while (0)
+#endif
 
 // ---- PTX wrappers ---------------------------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -212,6 +220,9 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   __shared__ double csd[NB];                                    // 2^e of the column block rows
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int n = d.n, ld = d.ld;
+#ifdef GPSAT_I8_PHASES
+  long long tphase = clock64();
+#endif
   const int kend = lauum_kend(n);
 
   if (tid == 0) {
@@ -243,6 +254,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   double acc[64];
 #pragma unroll
   for (int q = 0; q < 64; ++q) acc[q] = 0.0;
+  I8_PHASE(0);
   int it = 0;                                     // slabs issued so far (producer and MMA thread count alike)
   bool ok = true;
 #pragma unroll 1
@@ -310,6 +322,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    I8_PHASE(1 + 2 * pass);
     if (ok) {
       // drain: sum_g G_g 2^(-7 g) in int64 (exact), one conversion per element
       const double rs = pow2i(exrow - 12 - 7 * (g1 - 1));
@@ -339,6 +352,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    I8_PHASE(2 + 2 * pass);
   }
   // Q tile (Ks^-1 + alpha alpha^T) into shared memory; the pipeline stages are idle now
   {
@@ -348,6 +362,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   }
   __syncthreads();
   if (warp == 0) tmem_dealloc(tb, 512);
+  I8_PHASE(5);
 
   double part[GPSAT_DMAX + 2];
   grad_tile(d, i * NB, j * NB, xr, xc, ar, ac, Cs, tid, part);
@@ -364,6 +379,10 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
     for (int w8 = 0; w8 < 8; ++w8) v += red[w8 * 8 + tid];
     d.gpart[(size_t)t * (GPSAT_DMAX + 2) + tid] = v;
   }
+  I8_PHASE(6);
+#ifdef GPSAT_I8_PHASES
+  if (tid == 0) atomicAdd(&g_i8_phase[7], 1ull);
+#endif
 }
 
 // ---- persistent variant: warp-specialised, gradient reduction from registers -----------------------------

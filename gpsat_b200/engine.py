@@ -167,6 +167,12 @@ class Engine:
         tcgen05 tensor path; ``"dmma"``: FP64 ``mma.sync``.  Both give FP64-level results."""
         _lib.check(self._lib.gpsat_engine_set_lauum_path(self._h, {"dmma": 0, "i8": 1}[path]))
 
+    def i8_phases(self, reset: bool = True):
+        """Cycles per phase of the int8-path gradient kernel (development builds with -DGPSAT_I8_PHASES)."""
+        out = (C.c_uint64 * 8)()
+        _lib.check(self._lib.gpsat_engine_i8_phases(self._h, out, int(reset)))
+        return [int(v) for v in out]
+
     def i8_timeouts(self) -> int:
         """1 if a bounded barrier wait of the int8 path ever gave up (results invalid), else 0."""
         out = C.c_int(0)

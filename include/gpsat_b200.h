@@ -139,6 +139,10 @@ int gpsat_engine_set_profile(gpsat_engine* eng, int on);
 int gpsat_engine_set_lauum_path(gpsat_engine* eng, int path);
 /* out = 1 if a bounded barrier wait of the int8 path ever gave up (a bug indicator; results invalid). */
 int gpsat_engine_i8_timeouts(gpsat_engine* eng, int* out);
+/* Cycle counts per phase of the int8-path gradient kernel summed over its CTAs (all zero unless the library was
+ * built with -DGPSAT_I8_PHASES; a development aid): prologue, pass-0 MMAs, drain 0, pass-1 MMAs, drain 1,
+ * Q tile store, gradient reduction, tiles. */
+int gpsat_engine_i8_phases(gpsat_engine* eng, uint64_t* out8, int reset);
 void gpsat_fit_options_default(gpsat_fit_options* opt);
 
 /* lml[e] = log marginal likelihood, grad[e][P] = d lml / d theta (constrained space). */
