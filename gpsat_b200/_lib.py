@@ -23,7 +23,7 @@ STATUS_OK, STATUS_NOT_PD, STATUS_LINESEARCH, STATUS_MAXITER, STATUS_BAD_INPUT = 
 
 EXPORTED_SYMBOLS = (
     "gpsat_version", "gpsat_last_error", "gpsat_device_name", "gpsat_engine_create", "gpsat_engine_destroy",
-    "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_engine_set_lauum_path",
+    "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_engine_set_lauum_path", "gpsat_engine_set_step_path",
     "gpsat_engine_i8_timeouts", "gpsat_engine_i8_phases", "gpsat_fit_options_default",
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
     "gpsat_sgpr_elbo", "gpsat_sgpr_predict", "gpsat_sgpr_fit",
@@ -90,6 +90,7 @@ def load():
     lib.gpsat_engine_stream.restype = vp
     lib.gpsat_engine_set_profile.argtypes = [vp, C.c_int]
     lib.gpsat_engine_set_lauum_path.argtypes = [vp, C.c_int]
+    lib.gpsat_engine_set_step_path.argtypes = [vp, C.c_int]
     lib.gpsat_engine_i8_timeouts.argtypes = [vp, C.POINTER(C.c_int)]
     lib.gpsat_engine_i8_phases.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
     lib.gpsat_fit_options_default.argtypes = [C.POINTER(FitOptions)]

@@ -45,6 +45,9 @@ struct SlotDesc {
   int ldpre;
   int8_t* Uq;            // int8 slice planes of the upper block triangle (i8mma.cuh), nullptr = DMMA lauum
   int* uex;              // [T*NB] row scale exponents of the planes
+  int8_t* Lq;            // int8 slice planes of the strict lower block triangle (step_kernel.cuh), nullptr = DMMA potrf
+  int8_t* Uq8;           // same for U = L^-T with a-priori row scales (trtri main loop), nullptr = DMMA trtri
+  double ynorm2;         // |y|^2 (a-priori scale of the observation row of the factor)
   double inv_ls[GPSAT_DMAX];
   double var;            // kernel variance
   double noise;          // likelihood variance

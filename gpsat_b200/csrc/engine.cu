@@ -21,9 +21,9 @@
 #include "lbfgs.cuh"
 #include "tiles.cuh"
 #include "diag_kernel.cuh"
-#include "step_kernel.cuh"
 #include "lauum_kernel.cuh"
 #include "i8mma.cuh"
+#include "step_kernel.cuh"
 
 namespace gpsat {
 
@@ -57,6 +57,7 @@ struct BatchDev {
   const double* y;
   const double* Xs;
   const int* order;         // experts sorted by n, descending
+  const double* ynorm2;     // [E] |y|^2 per expert
 };
 
 struct FitDev {
@@ -81,8 +82,24 @@ struct FitDev {
 // Slot-private scratch carved from the workspace; constant for the lifetime of a call.
 struct SlotMem {
   double* A; double* Wd; double* Ld; double* logdet; double* quad; double* gpart; int* notpd;
-  int8_t* Uq; int* uex;
+  int8_t* Uq; int* uex; int8_t* Lq; int8_t* Uq8;
 };
+
+// |y|^2 per expert in a fixed summation order (one CTA of 128 threads per expert)
+__global__ void __launch_bounds__(128) ynorm_kernel(const int64_t* __restrict__ off_n, const double* __restrict__ y,
+                                                    double* __restrict__ out) {
+  __shared__ double red[4];
+  const int e = blockIdx.x, tid = threadIdx.x;
+  const double* ye = y + off_n[e];
+  const int n = (int)(off_n[e + 1] - off_n[e]);
+  double s = 0.0;
+  for (int k = tid; k < n; k += 128) s = fma(ye[k], ye[k], s);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if ((tid & 31) == 0) red[tid >> 5] = s;
+  __syncthreads();
+  if (tid == 0) out[e] = (red[0] + red[1]) + (red[2] + red[3]);
+}
 
 }  // namespace gpsat
 #include "sgpr_kernels.cuh"
@@ -160,6 +177,7 @@ __device__ __forceinline__ void slot_set_expert(SlotDesc& d, const SlotMem& mem,
   d.gpart = mem.gpart; d.notpd = mem.notpd;
   d.pre = nullptr; d.pre_s = nullptr; d.ldpre = 0;
   d.Uq = mem.Uq; d.uex = mem.uex;
+  d.Lq = mem.Lq; d.Uq8 = mem.Uq8; d.ynorm2 = b.ynorm2 ? b.ynorm2[e] : 0.0;
   *d.notpd = 0;
   *d.quad = 0.0;
 }

@@ -23,6 +23,13 @@ int gpsat_engine_set_lauum_path(gpsat_engine* h, int path) {
   return 0;
 }
 
+int gpsat_engine_set_step_path(gpsat_engine* h, int path) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  REQUIRE(path == GPSAT_STEP_DMMA || path == GPSAT_STEP_I8, "unknown step path");
+  h->e.i8_step = path == GPSAT_STEP_I8;
+  return 0;
+}
+
 int gpsat_engine_i8_phases(gpsat_engine* h, uint64_t* out8, int reset) {
   REQUIRE(h != nullptr && out8 != nullptr, "NULL argument");
   CUDA_TRY(cudaStreamSynchronize(h->e.stream));
@@ -81,6 +88,7 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
     h->e.i8_lauum = strcmp(lp, "dmma") != 0;
     h->e.i8_persistent = strcmp(lp, "i8p") == 0;
   }
+  if (const char* sp = getenv("GPSAT_B200_STEP")) h->e.i8_step = strcmp(sp, "i8") == 0;
   h->e.num_sms = prop.multiProcessorCount;
   *out = h;
   return 0;
@@ -93,7 +101,7 @@ int gpsat_engine_destroy(gpsat_engine* h) {
   cudaStreamSynchronize(g.stream);
   for (cudaEvent_t ev : g.evpool) cudaEventDestroy(ev);
   for (DevBuf* b : {&g.bX, &g.by, &g.bXs, &g.boffn, &g.boffm, &g.border, &g.btheta, &g.bmisc, &g.bslots,
-                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov, &g.bZ, &g.bsg, &g.bUq})
+                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov, &g.bZ, &g.bsg, &g.bUq, &g.bLq, &g.bUq8, &g.bynorm})
     b->release();
   if (g.h_counters) cudaFreeHost(g.h_counters);
   cudaEventDestroy(g.ev0); cudaEventDestroy(g.ev1);

@@ -40,6 +40,9 @@ struct Engine {
   int num_sms = 148;
   int cur_kind = GPSAT_MATERN32, cur_D = 3;     // kernel family / input dimension of the loaded batch
   DevBuf bUq;
+  // potrf main loop of step_kernel on the int8 tensor path (step_kernel.cuh); GPSAT_B200_STEP=i8|dmma
+  bool i8_step = false;
+  DevBuf bLq, bUq8, bynorm;
   bool profile = false;
   std::vector<cudaEvent_t> evpool;
   std::vector<int> evtype;          // kernel type of event pair k (events 2k, 2k+1)
@@ -158,6 +161,13 @@ static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with
       out.Xs = g.bXs.as<double>();
     }
   }
+  out.ynorm2 = nullptr;
+  if (g.i8_step && E > 0) {
+    if (g.bynorm.ensure(E * 8)) return 1;
+    ynorm_kernel<<<(unsigned)E, 128, 0, g.stream>>>(out.off_n, out.y, g.bynorm.as<double>());
+    g.stats.kernel_launches++;
+    out.ynorm2 = g.bynorm.as<double>();
+  }
   return 0;
 }
 
@@ -165,6 +175,10 @@ static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with
 static size_t i8_slot_bytes(int Tmax) {
   return (size_t)Tmax * (Tmax + 1) / 2 * I8_S * I8_PLANE_B + (size_t)Tmax * NB * sizeof(int);
 }
+// planes of the strict lower block triangle (all tile rows, tile columns 0 .. Tmax-2 are ever read)
+static size_t i8l_slot_bytes(int TRmax) { return (size_t)TRmax * (TRmax - 1) / 2 * I8L_TILE_B; }
+static size_t i8u_slot_bytes(int Tmax) { return (size_t)Tmax * (Tmax + 1) / 2 * I8L_TILE_B; }
+static bool i8_step_usable(const Engine& g, int Tmax, int TRmax) { return g.i8_step && Tmax >= 2 && TRmax <= I8L_MAX_T; }
 
 static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out, bool with_grad = true) {
   const int ld = Tmax * NB;
@@ -180,6 +194,12 @@ static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out
   const bool i8 = g.i8_lauum && with_grad;
   const size_t uq_b = i8_slot_bytes(Tmax);
   if (i8 && g.bUq.ensure(uq_b * S)) return 1;
+  const bool i8l = i8_step_usable(g, Tmax, TRmax);
+  const size_t lq_b = i8l_slot_bytes(TRmax);
+  if (i8l && g.bLq.ensure(lq_b * S)) return 1;
+  const bool i8u = i8l && with_grad;
+  const size_t uq8_b = i8u_slot_bytes(Tmax);
+  if (i8u && g.bUq8.ensure(uq8_b * S)) return 1;
   std::vector<SlotMem> mems(S);
   for (int s = 0; s < S; ++s) {
     double* sd = g.bside.as<double>() + side_d * s;
@@ -193,6 +213,8 @@ static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out
     m.notpd = reinterpret_cast<int*>(m.gpart + ntile * PG);
     m.Uq = i8 ? g.bUq.as<int8_t>() + uq_b * s : nullptr;
     m.uex = i8 ? reinterpret_cast<int*>(m.Uq + (size_t)Tmax * (Tmax + 1) / 2 * I8_S * I8_PLANE_B) : nullptr;
+    m.Lq = i8l ? g.bLq.as<int8_t>() + lq_b * s : nullptr;
+    m.Uq8 = i8u ? g.bUq8.as<int8_t>() + uq8_b * s : nullptr;
   }
   CUDA_TRY(cudaMemcpyAsync(g.bmems.p, mems.data(), sizeof(SlotMem) * S, cudaMemcpyHostToDevice, g.stream));
   CUDA_TRY(cudaStreamSynchronize(g.stream));   // `mems` is a stack-lifetime source
@@ -205,7 +227,8 @@ static int choose_slots(Engine& g, int64_t E, int Tmax, int TRmax, int max_slots
   cudaMemGetInfo(&free_b, &total_b);
   size_t per = (size_t)TRmax * NB * Tmax * NB * 8 + (size_t)2 * Tmax * NB * NB * 8 + (1 << 16);
   if (g.i8_lauum) per += i8_slot_bytes(Tmax);
-  size_t avail = (size_t)((free_b + g.bA.cap + g.bside.cap + g.bUq.cap) * 0.80);
+  if (i8_step_usable(g, Tmax, TRmax)) per += i8l_slot_bytes(TRmax) + i8u_slot_bytes(Tmax);
+  size_t avail = (size_t)((free_b + g.bA.cap + g.bside.cap + g.bUq.cap + g.bLq.cap + g.bUq8.cap) * 0.80);
   int64_t S = max_slots > 0 ? max_slots : 592;      // 4 x 148 SMs: amortises the per-step launches
   S = std::min<int64_t>(S, E);
   S = std::min<int64_t>(S, (int64_t)(avail / per));

@@ -10,11 +10,131 @@
 //   4. (potrf)     S_rr -= out out^T, lower triangle only, strip-mapped; coalesced update
 //   5. (tile (i+1, i) only)  S_{i+1,i+1} is now final: factor it in place (diag_factor_tile), so the
 //                  serial diagonal factorisation overlaps the other tiles of the step
+//
+// int8 tensor path for the potrf main loop (slots with d.Lq != nullptr): every finished tile L_ri is also
+// stored as 8 exact int8 slice planes (same error-free splitting and plane layout as i8mma.cuh) with an
+// A-PRIORI row scale - row r of the augmented factor satisfies |L_rk| <= |row r| <= sqrt(K_rr), known before
+// the factorisation - so that later tiles accumulate sum_k L_rk L_ik^T over the whole k range in TMEM
+// (tcgen05.mma kind::i8) and drain once per pass.  Two passes: slice-pair groups g = s + t = 0..3 (10 MMAs per
+// 32-wide slab) and 4..7 (26 MMAs); pairs with s + t >= 8 are dropped (2^-56 of the row scales, the level of
+// the FP64 accumulation error of the DMMA loop).  The DMMA loop remains for the trtri tiles, for slots without
+// planes (sparse / Fourier-feature models, GPSAT_B200_STEP=dmma) and is the reference the tests compare with.
 #pragma once
 #include "tiles.cuh"
+#include "i8slice.cuh"
 #include "diag_kernel.cuh"
 
 namespace gpsat {
+
+// Cs = -sum_{k < i NB} L[rowblk][k] L[i][k]^T on the int8 tensor path (see the header comment).  `pipe` is the
+// 192 KB area that holds Cs and the W stages afterwards.  All 256 threads call it; ends with a CTA barrier.
+// is_pot == false: the trtri sum  Cs = +sum_{j NB <= k < i NB} U[rowblk][k] L[i][k]^T  (A planes from d.Uq8).
+__device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk, int i, unsigned char* pipe, double* Cs,
+                                                  uint64_t* bars, uint32_t* tmem_slot, double* csd, int tid,
+                                                  bool is_pot = true) {
+  const int warp = tid >> 5, lane = tid & 31;
+  if (tid == 0) {
+    for (int b = 0; b < 2 * I8L_NST + 1; ++b) mbar_init(smem_u32(&bars[b]), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (warp == 0) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (tid < NB) csd[tid] = pow2i(lrow_exp(d, i * NB + tid));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tb = *tmem_slot;
+  const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[I8L_NST]), accb = smem_u32(&bars[2 * I8L_NST]);
+  const uint32_t pipe_s = smem_u32(pipe);
+  const uint64_t desc0 = umma_desc_kmajor(pipe_s, NB * 16, 128);
+  const int row = (warp & 3) * 32 + lane, chalf = warp >> 2;        // accumulator row, 64-column half
+  const int exrow = is_pot ? lrow_exp(d, rowblk * NB + row) : urow_exp(d);
+  constexpr int SPB = NB / I8_SLAB_K;                               // slabs per 128-block of k
+  const int nslabs = (is_pot ? i : i - rowblk) * SPB;
+  const int8_t* ga0 = is_pot ? d.Lq + (size_t)ltile_index(rowblk, 0) * I8L_TILE_B
+                             : d.Uq8 + (size_t)utile_index(d.T, rowblk, rowblk) * I8L_TILE_B;
+  const int8_t* gb0 = d.Lq + (size_t)ltile_index(i, is_pot ? 0 : rowblk) * I8L_TILE_B;
+
+  double acc[64];
+#pragma unroll
+  for (int q = 0; q < 64; ++q) acc[q] = 0.0;
+  bool ok = true;
+#pragma unroll 1
+  for (int pass = 0; pass < 2; ++pass) {
+    const int np = pass == 0 ? 4 : I8L_S;                     // planes per operand this pass
+    if (tid == 0) {
+      // ---- producer: one bulk copy per operand and slab (tiles (r, 0..i-1) are consecutive in the packing) ----
+      for (int sl = 0; sl < nslabs; ++sl) {
+        const int itp = pass * nslabs + sl, st = itp % I8L_NST;
+        if (itp >= I8L_NST) ok = ok && mbar_wait(empty0 + 8 * st, ((itp / I8L_NST) - 1) & 1);
+        if (!ok) break;
+        const uint32_t fb = full0 + 8 * st, sbase = pipe_s + st * I8L_STAGE_B;
+        mbar_expect_tx(fb, 2 * np * I8_SLAB_B);
+        bulk_g2s(sbase, ga0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
+        bulk_g2s(sbase + I8L_OPER_B, gb0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
+      }
+    } else if (tid == 32) {
+      // ---- MMA issue: all slice pairs of the pass for every slab ----
+      for (int sl = 0; sl < nslabs; ++sl) {
+        const int itm = pass * nslabs + sl, st = itm % I8L_NST;
+        ok = ok && mbar_wait(full0 + 8 * st, (itm / I8L_NST) & 1);
+        if (!ok) break;
+        tc_fence_after();
+        const uint64_t adesc = desc0 + (uint64_t)((st * I8L_STAGE_B) >> 4);
+        const uint64_t bdesc = adesc + (uint64_t)(I8L_OPER_B >> 4);
+        const uint32_t acc0 = sl == 0 ? 0u : 1u;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const int gg = pass * 4 + g;
+#pragma unroll
+          for (int s = 0; s < I8L_S; ++s)
+            if (s <= gg)
+              umma_i8(tb + (uint32_t)(g * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
+                      bdesc + (uint64_t)((gg - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
+        }
+        umma_commit(empty0 + 8 * st);
+      }
+      umma_commit(accb);
+      ok = mbar_wait(accb, pass) && ok;       // only this thread polls; the others sleep in the barrier below
+    }
+    __syncwarp();
+    ok = __all_sync(0xffffffffu, ok);         // warp-uniform: tcgen05.ld below is warp-collective
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    if (ok) {
+      // drain: Horner over the four groups of the pass in FP64 (partial sums are integers below 2^53: exact)
+      const double rs = pow2i(exrow - 12 - 7 * (pass * 4 + 3));
+#pragma unroll
+      for (int c = 0; c < 64; c += 16) {
+        uint32_t v[4][16];
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          tmem_ld16_nowait(tb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(g * NB + chalf * 64 + c), v[g]);
+        tmem_ld_wait();
+        double sum[16];
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          tmem_ld_fence(v[g]);
+#pragma unroll
+          for (int q = 0; q < 16; ++q) sum[q] = g == 0 ? i32_to_f64(v[g][q]) : fma(sum[q], 128.0, i32_to_f64(v[g][q]));
+        }
+#pragma unroll
+        for (int q = 0; q < 16; ++q) acc[c + q] = fma(sum[q] * rs, csd[chalf * 64 + c + q], acc[c + q]);
+      }
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+  }
+  if (warp == 0) tmem_dealloc(tb, 512);
+  {
+    double* crow = Cs + row * LDC + chalf * 64;
+    const double sg = is_pot ? -1.0 : 1.0;
+#pragma unroll
+    for (int q = 0; q < 64; q += 2) *reinterpret_cast<double2*>(crow + q) = make_double2(sg * acc[q], sg * acc[q + 1]);
+  }
+  __syncthreads();
+}
 
 // acc[strip rows][c] = sum_{k <= c} Cs[row][k] * W[c][k];  W (row-major 128 x 128, global) is
 // streamed through NWSTAGE B-only stages.  Each warp reads only its own strip of Cs.
@@ -61,7 +181,11 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
   const bool is_pot = x < npot;
   const int rowblk = is_pot ? (i + 1 + x) : (x - npot);   // r (potrf) or j (trtri)
 
-  extern __shared__ double smem[];
+  extern __shared__ __align__(128) double smem_step[];
+  double* smem = smem_step;
+  __shared__ __align__(8) uint64_t bars[2 * I8L_NST + 1];
+  __shared__ uint32_t tmem_slot;
+  __shared__ double csd[NB];
   double* Cs = smem;                       // aliases the pipeline stages
   double* wst = smem + SM_TILE_D;
   double* xr = wst + SM_WST_D;
@@ -76,7 +200,15 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
   const double* Wg = d.Wd + (size_t)i * NB * NB;
 
   // ---- 1. main loop (slab loads first, the coordinate loads hide behind them) ----
-  {
+  const bool use_i8 = d.Lq != nullptr && i > 0 && (is_pot || d.Uq8 != nullptr);
+  if (use_i8) {
+    if (is_pot) {
+      load_block_coords(d, rowblk * NB, xr, yr, tid);
+      load_block_coords(d, i * NB, xc, yc, tid);
+    }
+    potrf_mainloop_i8(d, rowblk, i, reinterpret_cast<unsigned char*>(smem), Cs, bars, &tmem_slot, csd, tid, is_pot);
+    wmult_prefetch(Wg, wst, tid);      // W_ii streams in under the epilogue
+  } else {
     Acc acc;
     acc_zero(acc);
     const double* Ag = d.A + (size_t)rowblk * NB * ld;
@@ -113,7 +245,22 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
         *reinterpret_cast<double2*>(Og + (size_t)rf * 8 * ld + cf * 8) =
             make_double2(sign * out.c[rf][cf][0], sign * out.c[rf][cf][1]);
   }
-  if (!is_pot || rowblk >= d.T) return;
+  if (!is_pot) {
+    if (d.Uq8 == nullptr || i + 1 >= d.T) return;
+    // later trtri steps read U_ji on the int8 path
+    double* Cw = Cs + (16 * strip + lr) * LDC + 2 * lk;
+#pragma unroll
+    for (int rf = 0; rf < 2; ++rf)
+#pragma unroll
+      for (int cf = 0; cf < 16; ++cf)
+        *reinterpret_cast<double2*>(Cw + rf * 8 * LDC + cf * 8) = make_double2(-out.c[rf][cf][0], -out.c[rf][cf][1]);
+    __syncthreads();
+    slice_tile_l(d, rowblk * NB, Cs, d.Uq8 + (size_t)utile_index(d.T, rowblk, i) * I8L_TILE_B, tid, true);
+    return;
+  }
+  const bool syrk = rowblk < d.T;                          // block row has a diagonal tile to update
+  const bool slice = d.Lq != nullptr && i + 1 < d.T;       // later steps read this tile on the int8 path
+  if (!syrk && !slice) return;
 
   // ---- 4. S_rr -= L_ri L_ri^T  (running Schur complement of the diagonal tile of block row r) ----
   // every warp read only its own strip of Cs in phase 3, so it may overwrite that strip now
@@ -126,6 +273,8 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
         *reinterpret_cast<double2*>(Cw + rf * 8 * LDC + cf * 8) = make_double2(out.c[rf][cf][0], out.c[rf][cf][1]);
   }
   __syncthreads();
+  if (slice) slice_tile_l(d, rowblk * NB, Cs, d.Lq + (size_t)ltile_index(rowblk, i) * I8L_TILE_B, tid);
+  if (!syrk) return;
   AccStrip sy;
   acc_zero(sy);
   {

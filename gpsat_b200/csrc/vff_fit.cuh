@@ -58,7 +58,7 @@ __device__ __forceinline__ void vff_set_expert(VffDesc& d, SgprDesc& sd, SlotDes
   s.gpart = nullptr;
   s.notpd = reinterpret_cast<int*>(s.quad + 2);
   s.pre = d.Pm; s.pre_s = d.KusT; s.ldpre = d.Mp;
-  s.Uq = nullptr; s.uex = nullptr;
+  s.Uq = nullptr; s.uex = nullptr; s.Lq = nullptr; s.Uq8 = nullptr; s.ynorm2 = 0.0;
   s.var = 0.0; s.noise = 0.0;
 }
 

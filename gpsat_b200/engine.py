@@ -167,6 +167,10 @@ class Engine:
         tcgen05 tensor path; ``"dmma"``: FP64 ``mma.sync``.  Both give FP64-level results."""
         _lib.check(self._lib.gpsat_engine_set_lauum_path(self._h, {"dmma": 0, "i8": 1}[path]))
 
+    def set_step_path(self, path: str):
+        """'i8' (int8 tensor path for the potrf main loop) or 'dmma' (FP64 mma.sync)."""
+        _lib.check(self._lib.gpsat_engine_set_step_path(self._h, {"dmma": 0, "i8": 1}[path]))
+
     def i8_phases(self, reset: bool = True):
         """Cycles per phase of the int8-path gradient kernel (development builds with -DGPSAT_I8_PHASES)."""
         out = (C.c_uint64 * 8)()

@@ -137,6 +137,15 @@ int gpsat_engine_set_profile(gpsat_engine* eng, int on);
 #define GPSAT_LAUUM_DMMA 0
 #define GPSAT_LAUUM_I8 1
 int gpsat_engine_set_lauum_path(gpsat_engine* eng, int path);
+/* How the potrf tiles of the sweep (the Cholesky GPflow runs inside GPR.log_marginal_likelihood / predict_f,
+ * gpflow_models.py:229-230, 337) accumulate sum_k L_rk L_ik^T:
+ *   GPSAT_STEP_DMMA FP64 mma.sync
+ *   GPSAT_STEP_I8   8 exact int8 slices per value with a-priori row scales on the tcgen05 tensor path
+ *                   (error at the level of the FP64 accumulation error)
+ * The environment variable GPSAT_B200_STEP=i8|dmma selects the path at engine creation. */
+#define GPSAT_STEP_DMMA 0
+#define GPSAT_STEP_I8 1
+int gpsat_engine_set_step_path(gpsat_engine* eng, int path);
 /* out = 1 if a bounded barrier wait of the int8 path ever gave up (a bug indicator; results invalid). */
 int gpsat_engine_i8_timeouts(gpsat_engine* eng, int* out);
 /* Cycle counts per phase of the int8-path gradient kernel summed over its CTAs (all zero unless the library was
