@@ -64,6 +64,23 @@ def fp64_peak_tflops():
         return 37.1, "fallback: 148 SM x 64 FMA/clk x 2 x 1.965 GHz"
 
 
+def arithmetic_note():
+    step = os.environ.get("GPSAT_B200_STEP", "i8") != "dmma"
+    lauum = os.environ.get("GPSAT_B200_LAUUM", "i8") != "dmma"
+    if not step and not lauum:
+        return "FP64 mma.sync throughout"
+    parts = []
+    if step:
+        parts.append("the k-sums of the potrf / trtri tiles are FP64 values split into 8 exact int8 slices with a-priori "
+                     "row scales and multiplied on the int8 tensor path (tcgen05, TMEM accumulators; truncation at "
+                     "2^-56 of the row scales, the level of the FP64 accumulation error)")
+    if lauum:
+        parts.append("the K^-1 tile products of the gradient use 7 slices (error 5e-14 of sum|a||b|)")
+    return ("FP64 data and results; " + "; ".join(parts) + "; covariance evaluation, diagonal-tile factorisation, "
+            "C W^T / SYRK epilogues, L-BFGS and prediction reductions in FP64; GPSAT_B200_STEP=dmma "
+            "GPSAT_B200_LAUUM=dmma run everything as FP64 mma.sync")
+
+
 class ClockSampler:
     """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
@@ -264,7 +281,8 @@ def run_ours(args):
         traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], tj["source"]
     except Exception:
         pass
-    roofline = {"bound": "tensor", "kernel": "step_kernel (FP64 DMMA potrf/trtri tiles + fused diagonal factorisation)",
+    roofline = {"bound": "tensor", "kernel": "step_kernel (potrf/trtri tiles: int8-sliced tcgen05 main loops, FP64 DMMA epilogues, fused diagonal factorisation)"
+                if os.environ.get("GPSAT_B200_STEP", "i8") != "dmma" else "step_kernel (FP64 DMMA potrf/trtri tiles + fused diagonal factorisation)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                 "traffic_source": traffic_src, "peak_source": peak_src,
                 "launches": int(n_step), "avg_launch_ms": ms_step / max(n_step, 1),
@@ -310,10 +328,7 @@ def run_ours(args):
                            "parallelism": f"experts sharded x{world}, no collective on the hot path",
                            "l2": "256 MB flush written between steps; per-step working set "
                                  f"{int(collect['fit'][-1]['slots'])} slot matrices >> 126 MB L2",
-                           "arithmetic": "FP64 throughout; the K^-1 tile products of the gradient are FP64 values split "
-                                         "into 7 exact int8 slices and multiplied on the int8 tensor path (tcgen05, "
-                                         "error 5e-14 of sum|a||b|); GPSAT_B200_LAUUM=dmma runs them as FP64 mma.sync"
-                                         if os.environ.get("GPSAT_B200_LAUUM", "i8") != "dmma" else "FP64 mma.sync throughout",
+                           "arithmetic": arithmetic_note(),
                            "mean_evals_per_expert": float(nev.mean()), "max_evals_per_expert": int(nev.max()),
                            "ticks_per_fit": int(collect["fit"][-1]["ticks"]), "slots": int(collect["fit"][-1]["slots"]),
                            "status_counts": {"ok": int(st[0]), "not_pd": int(st[1]), "linesearch": int(st[2]), "maxiter": int(st[3])}},

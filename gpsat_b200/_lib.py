@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgpsat_b200.so")
+# GPSAT_B200_LIB: an instrumented development build (tools/step_phases.py); the default is the in-tree library
+LIB_PATH = os.environ.get("GPSAT_B200_LIB") or os.path.join(_HERE, "libgpsat_b200.so")
 
 MEM_HOST = 0
 MEM_DEVICE = 1
@@ -24,7 +25,7 @@ STATUS_OK, STATUS_NOT_PD, STATUS_LINESEARCH, STATUS_MAXITER, STATUS_BAD_INPUT = 
 EXPORTED_SYMBOLS = (
     "gpsat_version", "gpsat_last_error", "gpsat_device_name", "gpsat_engine_create", "gpsat_engine_destroy",
     "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_engine_set_lauum_path", "gpsat_engine_set_step_path",
-    "gpsat_engine_i8_timeouts", "gpsat_engine_i8_phases", "gpsat_fit_options_default",
+    "gpsat_engine_i8_timeouts", "gpsat_engine_i8_phases", "gpsat_engine_step_phases", "gpsat_fit_options_default",
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
     "gpsat_sgpr_elbo", "gpsat_sgpr_predict", "gpsat_sgpr_fit",
     "gpsat_vff_elbo", "gpsat_vff_predict", "gpsat_vff_fit",
@@ -93,6 +94,7 @@ def load():
     lib.gpsat_engine_set_step_path.argtypes = [vp, C.c_int]
     lib.gpsat_engine_i8_timeouts.argtypes = [vp, C.POINTER(C.c_int)]
     lib.gpsat_engine_i8_phases.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
+    lib.gpsat_engine_step_phases.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
     lib.gpsat_fit_options_default.argtypes = [C.POINTER(FitOptions)]
     lib.gpsat_fit_options_default.restype = None
     lib.gpsat_gpr_lml_grad.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp]

@@ -223,9 +223,9 @@ __device__ __noinline__ void diag_factor_tile(const SlotDesc& d, int i, double* 
       Ut[(size_t)r * ld + c] = uv;
     }
   }
-  // later trtri tiles read U_ii on the int8 path
-  if (d.Uq8 != nullptr && i + 1 < d.T)
-    slice_tile_udiag(d, Cs, wdiag, d.Uq8 + (size_t)utile_index(d.T, i, i) * I8L_TILE_B, tid);
+  // later trtri tiles and the gradient's K^-1 products read U_ii on the int8 path
+  if (d.Uq8 != nullptr)
+    slice_tile_udiag(d, ncol, Cs, wdiag, d.Uq8 + (size_t)utile_index(d.T, i, i) * I8L_TILE_B, tid);
 }
 
 // Stand-alone launch: tile (0,0) of every slot (evaluates the covariance itself); the later

@@ -41,6 +41,17 @@ int gpsat_engine_i8_phases(gpsat_engine* h, uint64_t* out8, int reset) {
   return 0;
 }
 
+int gpsat_engine_step_phases(gpsat_engine* h, uint64_t* out32, int reset) {
+  REQUIRE(h != nullptr && out32 != nullptr, "NULL argument");
+  CUDA_TRY(cudaStreamSynchronize(h->e.stream));
+  CUDA_TRY(cudaMemcpyFromSymbol(out32, g_step_phase, 32 * sizeof(uint64_t)));
+  if (reset) {
+    uint64_t z[32] = {};
+    CUDA_TRY(cudaMemcpyToSymbol(g_step_phase, z, sizeof(z)));
+  }
+  return 0;
+}
+
 int gpsat_engine_i8_timeouts(gpsat_engine* h, int* out) {
   REQUIRE(h != nullptr && out != nullptr, "NULL argument");
   CUDA_TRY(cudaStreamSynchronize(h->e.stream));
@@ -88,7 +99,8 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
     h->e.i8_lauum = strcmp(lp, "dmma") != 0;
     h->e.i8_persistent = strcmp(lp, "i8p") == 0;
   }
-  if (const char* sp = getenv("GPSAT_B200_STEP")) h->e.i8_step = strcmp(sp, "i8") == 0;
+  if (const char* sp = getenv("GPSAT_B200_STEP")) h->e.i8_step = strcmp(sp, "dmma") != 0;
+  if (const char* dp = getenv("GPSAT_B200_DIAGSUM")) h->e.i8_diag_sum = strcmp(dp, "0") != 0;
   h->e.num_sms = prop.multiProcessorCount;
   *out = h;
   return 0;

@@ -41,7 +41,9 @@ struct Engine {
   int cur_kind = GPSAT_MATERN32, cur_D = 3;     // kernel family / input dimension of the loaded batch
   DevBuf bUq;
   // potrf main loop of step_kernel on the int8 tensor path (step_kernel.cuh); GPSAT_B200_STEP=i8|dmma
-  bool i8_step = false;
+  bool i8_step = true;
+  bool i8_diag_sum = true;          // GPSAT_B200_DIAGSUM=0: per-tile SYRK + RED instead of the one-go int8 Schur complement
+  bool lauum_planes8 = false;       // set by engine_alloc_slots: lauum_grad_i8_kernel reads d.Uq8
   DevBuf bLq, bUq8, bynorm;
   bool profile = false;
   std::vector<cudaEvent_t> evpool;
@@ -176,9 +178,10 @@ static size_t i8_slot_bytes(int Tmax) {
   return (size_t)Tmax * (Tmax + 1) / 2 * I8_S * I8_PLANE_B + (size_t)Tmax * NB * sizeof(int);
 }
 // planes of the strict lower block triangle (all tile rows, tile columns 0 .. Tmax-2 are ever read)
-static size_t i8l_slot_bytes(int TRmax) { return (size_t)TRmax * (TRmax - 1) / 2 * I8L_TILE_B; }
+static size_t i8l_slot_bytes(int TRmax) { return std::max<size_t>((size_t)TRmax * (TRmax - 1) / 2 * I8L_TILE_B, 16); }
 static size_t i8u_slot_bytes(int Tmax) { return (size_t)Tmax * (Tmax + 1) / 2 * I8L_TILE_B; }
-static bool i8_step_usable(const Engine& g, int Tmax, int TRmax) { return g.i8_step && Tmax >= 2 && TRmax <= I8L_MAX_T; }
+// (independent of the batch composition except for the size cap, so an expert gives the same bits alone or in a batch)
+static bool i8_step_usable(const Engine& g, int Tmax, int TRmax) { return g.i8_step && TRmax <= I8L_MAX_T; }
 
 static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out, bool with_grad = true) {
   const int ld = Tmax * NB;
@@ -191,15 +194,17 @@ static int engine_alloc_slots(Engine& g, int S, int Tmax, int TRmax, int& ld_out
   if (g.bA.ensure(a_d * 8 * S) || g.bside.ensure(side_d * 8 * S) || g.bslots.ensure(sizeof(SlotDesc) * S) ||
       g.bmems.ensure(sizeof(SlotMem) * S))
     return 1;
-  const bool i8 = g.i8_lauum && with_grad;
-  const size_t uq_b = i8_slot_bytes(Tmax);
-  if (i8 && g.bUq.ensure(uq_b * S)) return 1;
   const bool i8l = i8_step_usable(g, Tmax, TRmax);
   const size_t lq_b = i8l_slot_bytes(TRmax);
   if (i8l && g.bLq.ensure(lq_b * S)) return 1;
   const bool i8u = i8l && with_grad;
   const size_t uq8_b = i8u_slot_bytes(Tmax);
   if (i8u && g.bUq8.ensure(uq8_b * S)) return 1;
+  // the gradient's K^-1 products read the sweep's planes when there are any; otherwise they slice U themselves
+  g.lauum_planes8 = i8u && g.i8_lauum && !g.i8_persistent;
+  const bool i8 = g.i8_lauum && with_grad && !g.lauum_planes8;
+  const size_t uq_b = i8_slot_bytes(Tmax);
+  if (i8 && g.bUq.ensure(uq_b * S)) return 1;
   std::vector<SlotMem> mems(S);
   for (int s = 0; s < S; ++s) {
     double* sd = g.bside.as<double>() + side_d * s;
@@ -266,7 +271,8 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, cons
     int ntile = (TRmax - 1 - i) + (do_inv ? i : 0);
     if (ntile > 0) {
       ProfScope ps(g, PROF_STEP);
-      step_kernel<<<dim3(S, ntile), GPSAT_THREADS, STEP_SMEM_BYTES, g.stream>>>(slots, i, do_inv ? 1 : 0);
+      step_kernel<<<S * ntile, GPSAT_THREADS, STEP_SMEM_BYTES, g.stream>>>(slots, i, do_inv ? 1 : 0, S, ntile,
+                                                                                    g.i8_diag_sum ? 1 : 0);
       g.stats.kernel_launches++;
     }
   }
@@ -274,13 +280,18 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, cons
     ProfScope ps(g, PROF_LAUUM);
     const int ntile = Tmax * (Tmax + 1) / 2;
     if (g.i8_lauum) {
-      u_rowmax_kernel<<<dim3(Tmax * NB / 8, S), 256, 0, g.stream>>>(slots);
-      u_slice_kernel<<<dim3(ntile, S), 256, 0, g.stream>>>(slots);
-      if (g.i8_persistent)
-        launch_i8p(g, slots, S, ntile);
-      else
-        lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots);
-      g.stats.kernel_launches += 3;
+      if (g.lauum_planes8) {
+        lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots, 1);
+        g.stats.kernel_launches++;
+      } else {
+        u_rowmax_kernel<<<dim3(Tmax * NB / 8, S), 256, 0, g.stream>>>(slots);
+        u_slice_kernel<<<dim3(ntile, S), 256, 0, g.stream>>>(slots);
+        if (g.i8_persistent)
+          launch_i8p(g, slots, S, ntile);
+        else
+          lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots, 0);
+        g.stats.kernel_launches += 3;
+      }
     } else {
       lauum_grad_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots);
       g.stats.kernel_launches++;

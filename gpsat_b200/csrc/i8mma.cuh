@@ -27,8 +27,9 @@ constexpr int I8_PLANE_B = NB * NB;              // bytes per plane and tile
 constexpr int I8_SLAB_K = 32;                    // k per pipeline stage = one MMA
 constexpr int I8_SLAB_B = NB * I8_SLAB_K;        // bytes per plane and slab
 constexpr int I8_NST = 3;
-constexpr int I8_STAGE_B = 2 * I8_S * I8_SLAB_B;           // A planes then B planes: 56 KB
-constexpr int I8_PIPE_B = I8_NST * I8_STAGE_B;             // 168 KB, aliased by the Q tile afterwards
+constexpr int I8_SP = 8;                                   // plane capacity per operand of a stage
+constexpr int I8_STAGE_B = 2 * I8_SP * I8_SLAB_B;          // A planes then B planes: 64 KB
+constexpr int I8_PIPE_B = I8_NST * I8_STAGE_B;             // 192 KB, aliased by the Q tile afterwards
 static_assert(I8_PIPE_B >= SM_TILE_D * 8, "Q tile must fit in the pipeline stages");
 constexpr int LAUUM_I8_SMEM_BYTES = I8_PIPE_B + (SM_XY_D + 64) * 8 + 128;
 constexpr int I8_EXP_CLAMP = 400;
@@ -195,7 +196,10 @@ __global__ void __launch_bounds__(256) u_slice_kernel(const SlotDesc* __restrict
 }
 
 // ---- lauum_grad_i8_kernel: same contract as lauum_grad_kernel, tile product on the int8 path -----------
-__global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const SlotDesc* __restrict__ slots) {
+// planes8 != 0: the operands are the planes step_kernel / diag_factor_tile wrote during the sweep (d.Uq8: 8 planes
+// per value of which the first 7 are read, one a-priori scale for all rows, the -alpha column stored as zeros, so
+// the tile is Ks^-1 alone) instead of the planes of u_slice_kernel (d.Uq, row scales d.uex).
+__global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const SlotDesc* __restrict__ slots, int planes8) {
   const SlotDesc& d = slots[blockIdx.y];
   if (d.expert < 0) return;
   const int T = d.T;
@@ -232,7 +236,20 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   if (warp == 0) tmem_alloc(smem_u32(&tmem_base), 512);
   load_block_coords(d, i * NB, xr, ar, tid);      // ar / ac overwritten with alpha below
   load_block_coords(d, j * NB, xc, ac, tid);
-  if (tid < NB) csd[tid] = pow2i(d.uex[j * NB + tid]);
+  const int8_t* Ubase = planes8 ? d.Uq8 : d.Uq;
+  const size_t tile_b = planes8 ? (size_t)8 * I8_PLANE_B : (size_t)I8_S * I8_PLANE_B;
+  const size_t slab_b = planes8 ? (size_t)8 * I8_SLAB_B : (size_t)I8_S * I8_SLAB_B;
+  // planes read per value: 7 (2^-49 of the scale) unless the a-priori scale may sit far above the entries of U
+  // (|U_rr| = 1 / L_rr >= 1 / sqrt(var + noise) against the bound 1 / sqrt(noise)), then all 8
+  const int S = (planes8 && d.var > 255.0 * d.noise) ? 8 : I8_S;
+  int eu = 0;
+  if (planes8) {      // a-priori scale of the sweep's planes: |U| <= 1 / sqrt(noise) (urow_exp in i8slice.cuh)
+    double b2 = 1.0 / d.noise;
+    if (!(b2 > 1e-280)) b2 = 1e-280;
+    if (!(b2 < 1e280)) b2 = 1e280;
+    eu = ((int)((__double_as_longlong(b2) >> 52) & 0x7ff) - 1022 + 1) >> 1;
+  }
+  if (tid < NB) csd[tid] = pow2i(planes8 ? eu : d.uex[j * NB + tid]);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -246,7 +263,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   const uint32_t pipe_s = smem_u32(pipe);
   const uint64_t desc0 = umma_desc_kmajor(pipe_s, NB * 16, 128);
   const int row = (warp & 3) * 32 + lane, chalf = warp >> 2;        // accumulator row, 64-column half
-  const int exrow = d.uex[i * NB + row];
+  const int exrow = planes8 ? eu : d.uex[i * NB + row];
   // slabs of the last k block (columns >= kend hold zero planes and are skipped)
   const int last_slabs = (kend - (T - 1) * NB + I8_SLAB_K - 1) / I8_SLAB_K;
   const int nslabs = (T - 1 - i) * (NB / I8_SLAB_K) + last_slabs;
@@ -259,14 +276,14 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   bool ok = true;
 #pragma unroll 1
   for (int pass = 0; pass < 2; ++pass) {
-    const int np = pass == 0 ? 4 : I8_S;                      // planes per operand this pass
-    const int g0 = pass * 4, g1 = min(g0 + 4, I8_S);          // groups s + t = g of this pass
+    const int np = pass == 0 ? 4 : S;                         // planes per operand this pass
+    const int g0 = pass * 4, g1 = min(g0 + 4, S);             // groups s + t = g of this pass
     if (tid == 0) {
       // ---- producer: bulk copies of the slab planes ----
       int itp = it;
       for (int kb = i; kb < T && ok; ++kb) {
-        const int8_t* ga = d.Uq + (size_t)utile_index(T, i, kb) * I8_S * I8_PLANE_B;
-        const int8_t* gb = d.Uq + (size_t)utile_index(T, j, kb) * I8_S * I8_PLANE_B;
+        const int8_t* ga = Ubase + (size_t)utile_index(T, i, kb) * tile_b;
+        const int8_t* gb = Ubase + (size_t)utile_index(T, j, kb) * tile_b;
         const int nsl = kb == T - 1 ? last_slabs : NB / I8_SLAB_K;
         for (int sl = 0; sl < nsl; ++sl, ++itp) {
           const int st = itp % I8_NST;
@@ -274,8 +291,8 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
           if (!ok) break;
           const uint32_t fb = full0 + 8 * st, sbase = pipe_s + st * I8_STAGE_B;
           mbar_expect_tx(fb, (same ? np : 2 * np) * I8_SLAB_B);
-          bulk_g2s(sbase, ga + (size_t)sl * (I8_S * I8_SLAB_B), np * I8_SLAB_B, fb);
-          if (!same) bulk_g2s(sbase + I8_S * I8_SLAB_B, gb + (size_t)sl * (I8_S * I8_SLAB_B), np * I8_SLAB_B, fb);
+          bulk_g2s(sbase, ga + (size_t)sl * slab_b, np * I8_SLAB_B, fb);
+          if (!same) bulk_g2s(sbase + I8_SP * I8_SLAB_B, gb + (size_t)sl * slab_b, np * I8_SLAB_B, fb);
         }
       }
     } else if (tid == 32) {
@@ -291,7 +308,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
           tc_fence_after();
           // descriptors differ only in the start address field (units of 16 bytes, low word)
           const uint64_t adesc = desc0 + (uint64_t)((st * I8_STAGE_B) >> 4);
-          const uint64_t bdesc = same ? adesc : adesc + (uint64_t)((I8_S * I8_SLAB_B) >> 4);
+          const uint64_t bdesc = same ? adesc : adesc + (uint64_t)((I8_SP * I8_SLAB_B) >> 4);
           const uint32_t acc0 = first ? 0u : 1u;
           if (pass == 0) {
 #pragma unroll
@@ -302,10 +319,10 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
                         bdesc + (uint64_t)((g - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
           } else {
 #pragma unroll
-            for (int g = 4; g < I8_S; ++g)
+            for (int g = 4; g < I8_SP; ++g)
 #pragma unroll
               for (int s = 0; s <= g; ++s)
-                if (s <= I8_S - 1 && g - s <= I8_S - 1)
+                if (g < S && s < S && g - s < S)
                   umma_i8(tb + (uint32_t)((g - 4) * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
                           bdesc + (uint64_t)((g - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
           }
@@ -365,7 +382,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   I8_PHASE(5);
 
   double part[GPSAT_DMAX + 2];
-  grad_tile(d, i * NB, j * NB, xr, xc, ar, ac, Cs, tid, part);
+  grad_tile(d, i * NB, j * NB, xr, xc, ar, ac, Cs, tid, part, planes8 ? 0.0 : 1.0);
 #pragma unroll
   for (int p = 0; p < GPSAT_DMAX + 2; ++p) {
     double v = part[p];

@@ -77,19 +77,26 @@ __device__ __forceinline__ void slice_tile_f(FV val, FS sc_of_row, int8_t* plane
   }
 }
 
-// The tile held in Cs ([128][LDC]) as a tile of L (per-row scales of rows g0r ..) or of U (one scale).
-__device__ __forceinline__ void slice_tile_l(const SlotDesc& d, int g0r, const double* Cs, int8_t* planes, int tid,
-                                             bool is_u = false) {
-  const int eu = urow_exp(d);
+// The tile held in Cs ([128][LDC]) as a tile of L (per-row scales of rows g0r ..).
+__device__ __forceinline__ void slice_tile_l(const SlotDesc& d, int g0r, const double* Cs, int8_t* planes, int tid) {
   slice_tile_f([&](int r, int c) { return Cs[r * LDC + c]; },
-               [&](int r) { return pow2i(6 - (is_u ? eu : lrow_exp(d, g0r + r))); }, planes, tid);
+               [&](int r) { return pow2i(6 - lrow_exp(d, g0r + r)); }, planes, tid);
 }
 
-// Diagonal tile U_ii = W_ii^T after diag_factor_tile: strict upper part in Cs, diagonal in wdiag, zero below.
-__device__ __forceinline__ void slice_tile_udiag(const SlotDesc& d, const double* Cs, const double* wdiag, int8_t* planes,
-                                                 int tid) {
+// The tile held in Cs as tile (.., column block at g0c) of U: one scale; columns >= n (the -alpha column of the
+// augmented inverse and the padding) are stored as zeros, so products of planes give Ks^-1 without alpha alpha^T.
+__device__ __forceinline__ void slice_tile_u(const SlotDesc& d, int g0c, const double* Cs, int8_t* planes, int tid) {
   const double sc = pow2i(6 - urow_exp(d));
-  slice_tile_f([&](int r, int c) { return c > r ? Cs[r * LDC + c] : (c == r ? wdiag[r] : 0.0); },
+  const int ncol = d.n - g0c;
+  slice_tile_f([&](int r, int c) { return c < ncol ? Cs[r * LDC + c] : 0.0; }, [&](int) { return sc; }, planes, tid);
+}
+
+// Diagonal tile U_ii = W_ii^T after diag_factor_tile: strict upper part in Cs, diagonal in wdiag, zero below;
+// rows / columns >= ncol (augmentation) are stored as zeros.
+__device__ __forceinline__ void slice_tile_udiag(const SlotDesc& d, int ncol, const double* Cs, const double* wdiag,
+                                                 int8_t* planes, int tid) {
+  const double sc = pow2i(6 - urow_exp(d));
+  slice_tile_f([&](int r, int c) { return c >= ncol ? 0.0 : (c > r ? Cs[r * LDC + c] : (c == r ? wdiag[r] : 0.0)); },
                [&](int) { return sc; }, planes, tid);
 }
 

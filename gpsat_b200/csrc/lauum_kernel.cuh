@@ -16,7 +16,7 @@ namespace gpsat {
 template <int KIND, int DD>
 __device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c, const double* xr, const double* xc,
                                             const double* ar, const double* ac, const double* Cs, int tid,
-                                            double* part) {
+                                            double* part, double aac) {
   const int n = d.n, D = d.D;
   const int c = tid & (NB - 1);
   const int gj = g0c + c;
@@ -32,7 +32,7 @@ __device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c,
 #pragma unroll 4
     for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
       const double aa = ar[r] * acv;
-      const double wq = 2.0 * (aa - (Cs[r * LDC + c] - aa));
+      const double wq = 2.0 * (aa - (Cs[r * LDC + c] - aac * aa));
       double sd[ND], r2 = 0.0;
 #pragma unroll
       for (int dd = 0; dd < ND; ++dd) {
@@ -53,8 +53,8 @@ __device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c,
       const int gi = g0r + r;
       if (gi >= n || gj > gi) continue;
       const double aa = ar[r] * acv;
-      // the tile holds Ks^-1 + alpha alpha^T (column n of U is -alpha)
-      const double q = aa - (Cs[r * LDC + c] - aa);
+      // aac = 1: the tile holds Ks^-1 + alpha alpha^T (column n of U is -alpha); aac = 0: Ks^-1 alone
+      const double q = aa - (Cs[r * LDC + c] - aac * aa);
       const double wq = (gi == gj) ? q : 2.0 * q;
       double sd[ND], r2 = 0.0;
 #pragma unroll
@@ -79,24 +79,25 @@ __device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c,
 }
 
 __device__ __noinline__ void grad_tile(const SlotDesc& d, int g0r, int g0c, const double* xr, const double* xc,
-                                       const double* ar, const double* ac, const double* Cs, int tid, double* part) {
+                                       const double* ar, const double* ac, const double* Cs, int tid, double* part,
+                                       double aac = 1.0) {
   const bool d3 = d.D == 3;
   switch (d.kind) {
     case GPSAT_MATERN12:
-      if (d3) grad_tile_t<GPSAT_MATERN12, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
-      else grad_tile_t<GPSAT_MATERN12, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      if (d3) grad_tile_t<GPSAT_MATERN12, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part, aac);
+      else grad_tile_t<GPSAT_MATERN12, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part, aac);
       break;
     case GPSAT_MATERN32:
-      if (d3) grad_tile_t<GPSAT_MATERN32, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
-      else grad_tile_t<GPSAT_MATERN32, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      if (d3) grad_tile_t<GPSAT_MATERN32, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part, aac);
+      else grad_tile_t<GPSAT_MATERN32, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part, aac);
       break;
     case GPSAT_MATERN52:
-      if (d3) grad_tile_t<GPSAT_MATERN52, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
-      else grad_tile_t<GPSAT_MATERN52, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      if (d3) grad_tile_t<GPSAT_MATERN52, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part, aac);
+      else grad_tile_t<GPSAT_MATERN52, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part, aac);
       break;
     default:
-      if (d3) grad_tile_t<GPSAT_RBF, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
-      else grad_tile_t<GPSAT_RBF, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part);
+      if (d3) grad_tile_t<GPSAT_RBF, 3>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part, aac);
+      else grad_tile_t<GPSAT_RBF, 0>(d, g0r, g0c, xr, xc, ar, ac, Cs, tid, part, aac);
       break;
   }
 }

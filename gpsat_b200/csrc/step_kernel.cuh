@@ -1,6 +1,5 @@
 // step_kernel(i): all off-diagonal work of block column i for every expert in flight.
-//   blockIdx.x = slot, blockIdx.y = tile within the step (x fastest: the tile-0 CTAs of all slots,
-//   which also factor the next diagonal tile, are dispatched first):
+//   x = tile within the step (see the kernel for the CTA -> (slot, x) map):
 //     [0, TR-1-i)            potrf tile (r, i), r = i + 1 + x
 //     [TR-1-i, TR-1-i + i)   trtri tile (j, i), j = x - (TR-1-i)      (only when do_inv)
 // Phases of one CTA (256 threads, one 128 x 128 output tile):
@@ -26,19 +25,39 @@
 
 namespace gpsat {
 
+// cycles per phase of step_kernel summed over CTAs (thread 0's clock), potrf tiles in [0, 16), trtri tiles in
+// [16, 32): 0 prologue, 1 main loop (int8: pass 0), 2 drain 0, 3 pass 1, 4 drain 1, 5 C tile store, 6 covariance,
+// 7 C W^T, 8 stores + slicing, 9 SYRK + Schur update, 10 diagonal factorisation, 15 tiles.  -DGPSAT_STEP_PHASES only.
+__device__ unsigned long long g_step_phase[32];
+#ifdef GPSAT_STEP_PHASES
+#define STEP_PHASE(k) do { if (tid == 0) { long long now_ = clock64(); atomicAdd(&g_step_phase[phbase + (k)], (unsigned long long)(now_ - tphase)); tphase = now_; } } while (0)
+#else
+#define STEP_PHASE(k) do { } while (0)
+#endif
+
 // Cs = -sum_{k < i NB} L[rowblk][k] L[i][k]^T on the int8 tensor path (see the header comment).  `pipe` is the
 // 192 KB area that holds Cs and the W stages afterwards.  All 256 threads call it; ends with a CTA barrier.
-// is_pot == false: the trtri sum  Cs = +sum_{j NB <= k < i NB} U[rowblk][k] L[i][k]^T  (A planes from d.Uq8).
+// mode I8M_TRTRI: the trtri sum  Cs = +sum_{j NB <= k < i NB} U[rowblk][k] L[i][k]^T  (A planes from d.Uq8).
+// mode I8M_DIAG:  Cs = -sum_{k < i NB} L[rowblk][k] L[rowblk][k]^T, the part of the Schur complement of diagonal
+// tile rowblk that earlier steps produced (one operand, read once).
+// A CTA may call it twice (tile, then diagonal sum): `first` says whether TMEM is to be allocated and the barriers
+// are fresh, `last` whether TMEM is released.
+enum { I8M_POTRF = 0, I8M_TRTRI = 1, I8M_DIAG = 2 };
 __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk, int i, unsigned char* pipe, double* Cs,
                                                   uint64_t* bars, uint32_t* tmem_slot, double* csd, int tid,
-                                                  bool is_pot = true) {
+                                                  int mode, bool first, bool last, long long& tphase, int phbase) {
+  const bool is_pot = mode != I8M_TRTRI;
+  const bool same = mode == I8M_DIAG;
   const int warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
-    for (int b = 0; b < 2 * I8L_NST + 1; ++b) mbar_init(smem_u32(&bars[b]), 1);
+    for (int b = 0; b < 2 * I8L_NST + 1; ++b) {
+      if (!first) asm volatile("mbarrier.inval.shared::cta.b64 [%0];\n" :: "r"(smem_u32(&bars[b])) : "memory");
+      mbar_init(smem_u32(&bars[b]), 1);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
-  if (warp == 0) tmem_alloc(smem_u32(tmem_slot), 512);
-  if (tid < NB) csd[tid] = pow2i(lrow_exp(d, i * NB + tid));
+  if (first && warp == 0) tmem_alloc(smem_u32(tmem_slot), 512);
+  if (tid < NB) csd[tid] = pow2i(lrow_exp(d, (same ? rowblk : i) * NB + tid));
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -52,12 +71,13 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
   const int nslabs = (is_pot ? i : i - rowblk) * SPB;
   const int8_t* ga0 = is_pot ? d.Lq + (size_t)ltile_index(rowblk, 0) * I8L_TILE_B
                              : d.Uq8 + (size_t)utile_index(d.T, rowblk, rowblk) * I8L_TILE_B;
-  const int8_t* gb0 = d.Lq + (size_t)ltile_index(i, is_pot ? 0 : rowblk) * I8L_TILE_B;
+  const int8_t* gb0 = same ? ga0 : d.Lq + (size_t)ltile_index(i, is_pot ? 0 : rowblk) * I8L_TILE_B;
 
   double acc[64];
 #pragma unroll
   for (int q = 0; q < 64; ++q) acc[q] = 0.0;
   bool ok = true;
+  STEP_PHASE(0);
 #pragma unroll 1
   for (int pass = 0; pass < 2; ++pass) {
     const int np = pass == 0 ? 4 : I8L_S;                     // planes per operand this pass
@@ -68,9 +88,9 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
         if (itp >= I8L_NST) ok = ok && mbar_wait(empty0 + 8 * st, ((itp / I8L_NST) - 1) & 1);
         if (!ok) break;
         const uint32_t fb = full0 + 8 * st, sbase = pipe_s + st * I8L_STAGE_B;
-        mbar_expect_tx(fb, 2 * np * I8_SLAB_B);
+        mbar_expect_tx(fb, (same ? 1 : 2) * np * I8_SLAB_B);
         bulk_g2s(sbase, ga0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
-        bulk_g2s(sbase + I8L_OPER_B, gb0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
+        if (!same) bulk_g2s(sbase + I8L_OPER_B, gb0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
       }
     } else if (tid == 32) {
       // ---- MMA issue: all slice pairs of the pass for every slab ----
@@ -80,7 +100,7 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
         if (!ok) break;
         tc_fence_after();
         const uint64_t adesc = desc0 + (uint64_t)((st * I8L_STAGE_B) >> 4);
-        const uint64_t bdesc = adesc + (uint64_t)(I8L_OPER_B >> 4);
+        const uint64_t bdesc = same ? adesc : adesc + (uint64_t)(I8L_OPER_B >> 4);
         const uint32_t acc0 = sl == 0 ? 0u : 1u;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
@@ -101,6 +121,7 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    STEP_PHASE(1 + 2 * pass);
     if (ok) {
       // drain: Horner over the four groups of the pass in FP64 (partial sums are integers below 2^53: exact)
       const double rs = pow2i(exrow - 12 - 7 * (pass * 4 + 3));
@@ -125,8 +146,9 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
+    STEP_PHASE(2 + 2 * pass);
   }
-  if (warp == 0) tmem_dealloc(tb, 512);
+  if (last && warp == 0) tmem_dealloc(tb, 512);
   {
     double* crow = Cs + row * LDC + chalf * 64;
     const double sg = is_pot ? -1.0 : 1.0;
@@ -134,6 +156,7 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
     for (int q = 0; q < 64; q += 2) *reinterpret_cast<double2*>(crow + q) = make_double2(sg * acc[q], sg * acc[q + 1]);
   }
   __syncthreads();
+  STEP_PHASE(5);
 }
 
 // acc[strip rows][c] = sum_{k <= c} Cs[row][k] * W[c][k];  W (row-major 128 x 128, global) is
@@ -171,12 +194,17 @@ __device__ __forceinline__ void wmult_strip(AccStrip& acc, const double* Cs, con
 }
 
 __global__ void __launch_bounds__(GPSAT_THREADS, 1)
-step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
-  const SlotDesc& d = slots[blockIdx.x];
+step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv, int S, int ntile, int diag_sum) {
+  // 1-D grid of S * ntile CTAs.  The first S are tile 0 of every slot (the long ones: they also factor the next
+  // diagonal tile); the others follow slot by slot, so that the tiles of one slot - which all read block row i
+  // of L - run at the same time and share it in L2.
+  int slot, x;
+  if ((int)blockIdx.x < S) { slot = blockIdx.x; x = 0; }
+  else { const int id = blockIdx.x - S; slot = id / (ntile - 1); x = 1 + id - slot * (ntile - 1); }
+  const SlotDesc& d = slots[slot];
   if (d.expert < 0 || i >= d.T) return;
   const int npot = d.TR - 1 - i;
   const int ninv = do_inv ? i : 0;
-  const int x = blockIdx.y;
   if (x >= npot + ninv) return;
   const bool is_pot = x < npot;
   const int rowblk = is_pot ? (i + 1 + x) : (x - npot);   // r (potrf) or j (trtri)
@@ -198,6 +226,13 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
   const int strip = strip_of_warp(warp);
   const int ld = d.ld;
   const double* Wg = d.Wd + (size_t)i * NB * NB;
+#ifdef GPSAT_STEP_PHASES
+  long long tphase = clock64();
+  const int phbase = is_pot ? 0 : 16;
+#else
+  long long tphase = 0;
+  const int phbase = 0;
+#endif
 
   // ---- 1. main loop (slab loads first, the coordinate loads hide behind them) ----
   const bool use_i8 = d.Lq != nullptr && i > 0 && (is_pot || d.Uq8 != nullptr);
@@ -206,11 +241,15 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
       load_block_coords(d, rowblk * NB, xr, yr, tid);
       load_block_coords(d, i * NB, xc, yc, tid);
     }
-    potrf_mainloop_i8(d, rowblk, i, reinterpret_cast<unsigned char*>(smem), Cs, bars, &tmem_slot, csd, tid, is_pot);
+    // the CTA of tile (i + 1, i) runs the int8 loop a second time for the diagonal tile's Schur complement
+    potrf_mainloop_i8(d, rowblk, i, reinterpret_cast<unsigned char*>(smem), Cs, bars, &tmem_slot, csd, tid,
+                      is_pot ? I8M_POTRF : I8M_TRTRI, true, !(diag_sum && is_pot && x == 0 && rowblk < d.T), tphase,
+                      phbase);
     wmult_prefetch(Wg, wst, tid);      // W_ii streams in under the epilogue
   } else {
     Acc acc;
     acc_zero(acc);
+    STEP_PHASE(0);
     const double* Ag = d.A + (size_t)rowblk * NB * ld;
     const double* Bg = d.A + (size_t)i * NB * ld;
     const int kbeg = is_pot ? 0 : rowblk * NB;
@@ -221,20 +260,27 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
     }
     gemm_nt_mainloop(acc, Ag, Bg, ld, kbeg, i * NB, smem, tid, !is_pot);   // trtri: U_jj is upper triangular
     __syncthreads();   // coords visible; stages free
+    STEP_PHASE(1);
     wmult_prefetch(Wg, wst, tid);      // W_ii streams in under the epilogue
     // ---- 2. C to shared memory ----
     acc_to_smem(acc, Cs, tid, is_pot ? -1.0 : 1.0);
   }
   __syncthreads();
+  if (!use_i8) STEP_PHASE(5);
   if (is_pot) {
     add_aug_tile(d, rowblk * NB, i * NB, xr, xc, yc, Cs, tid, false);
     __syncthreads();
   }
+  STEP_PHASE(6);
 
   // ---- 3. out = C * W_ii^T ----
   AccStrip out;
   acc_zero(out);
   wmult_strip(out, Cs, Wg, wst, tid);
+  STEP_PHASE(7);
+#ifdef GPSAT_STEP_PHASES
+  if (tid == 0) atomicAdd(&g_step_phase[phbase + 15], 1ull);
+#endif
   const double sign = is_pot ? 1.0 : -1.0;
   {
     double* Og = d.A + ((size_t)rowblk * NB + 16 * strip + lr) * ld + (size_t)i * NB + 2 * lk;
@@ -246,8 +292,8 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
             make_double2(sign * out.c[rf][cf][0], sign * out.c[rf][cf][1]);
   }
   if (!is_pot) {
-    if (d.Uq8 == nullptr || i + 1 >= d.T) return;
-    // later trtri steps read U_ji on the int8 path
+    if (d.Uq8 == nullptr) return;
+    // later trtri steps and the gradient's K^-1 products read U_ji on the int8 path
     double* Cw = Cs + (16 * strip + lr) * LDC + 2 * lk;
 #pragma unroll
     for (int rf = 0; rf < 2; ++rf)
@@ -255,7 +301,8 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
       for (int cf = 0; cf < 16; ++cf)
         *reinterpret_cast<double2*>(Cw + rf * 8 * LDC + cf * 8) = make_double2(-out.c[rf][cf][0], -out.c[rf][cf][1]);
     __syncthreads();
-    slice_tile_l(d, rowblk * NB, Cs, d.Uq8 + (size_t)utile_index(d.T, rowblk, i) * I8L_TILE_B, tid, true);
+    slice_tile_u(d, i * NB, Cs, d.Uq8 + (size_t)utile_index(d.T, rowblk, i) * I8L_TILE_B, tid);
+    STEP_PHASE(8);
     return;
   }
   const bool syrk = rowblk < d.T;                          // block row has a diagonal tile to update
@@ -274,7 +321,11 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
   }
   __syncthreads();
   if (slice) slice_tile_l(d, rowblk * NB, Cs, d.Lq + (size_t)ltile_index(rowblk, i) * I8L_TILE_B, tid);
-  if (!syrk) return;
+  STEP_PHASE(8);
+  // With planes the Schur complement of a diagonal tile is formed in one go by the CTA that factors it (below),
+  // so the other tiles of the block row neither update nor touch S_rr.
+  const bool diag_i8 = diag_sum && d.Lq != nullptr;
+  if (!syrk || (diag_i8 && x != 0)) return;
   AccStrip sy;
   acc_zero(sy);
   {
@@ -303,13 +354,27 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
     const int c = tid & (NB - 1);
     if (x == 0) {
       // ---- 5. rowblk == i + 1: the Schur complement is complete; factor the next diagonal tile ----
-      if (i > 0) {
+      if (i > 0 && diag_i8) {
+        // park -L_ri L_ri^T in the slot matrix, form -sum_{k<i} L_rk L_rk^T on the int8 path, add K_rr
+#pragma unroll 16
+        for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
+          if (c <= r) Sg[(size_t)r * ld + c] = Cs[r * LDC + c];
+        __syncthreads();
+        potrf_mainloop_i8(d, rowblk, i, reinterpret_cast<unsigned char*>(smem), Cs, bars, &tmem_slot, csd, tid,
+                          I8M_DIAG, false, true, tphase, phbase);
+#pragma unroll 16
+        for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
+          if (c <= r) Cs[r * LDC + c] += Sg[(size_t)r * ld + c];
+        add_aug_tile(d, rowblk * NB, rowblk * NB, xr, xr, yr, Cs, tid, true);
+      } else if (i > 0) {
 #pragma unroll 16
         for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
           if (c <= r) Cs[r * LDC + c] += Sg[(size_t)r * ld + c];
       }
       __syncthreads();
+      STEP_PHASE(9);
       diag_factor_tile(d, rowblk, Cs, wst, tid);    // scratch: the W stages + coordinate arrays
+      STEP_PHASE(10);
       return;
     }
     if (i == 0) {
@@ -323,6 +388,7 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv) {
         if (c <= r) atomicAdd(Sg + (size_t)r * ld + c, Cs[r * LDC + c]);
     }
   }
+  STEP_PHASE(9);
 }
 
 }  // namespace gpsat

@@ -177,6 +177,13 @@ class Engine:
         _lib.check(self._lib.gpsat_engine_i8_phases(self._h, out, int(reset)))
         return [int(v) for v in out]
 
+    def step_phases(self, reset: bool = True):
+        """Cycles per phase of step_kernel (development builds with -DGPSAT_STEP_PHASES): potrf tiles [0, 16),
+        trtri tiles [16, 32)."""
+        out = (C.c_uint64 * 32)()
+        _lib.check(self._lib.gpsat_engine_step_phases(self._h, out, int(reset)))
+        return [int(v) for v in out]
+
     def i8_timeouts(self) -> int:
         """1 if a bounded barrier wait of the int8 path ever gave up (results invalid), else 0."""
         out = C.c_int(0)

@@ -152,6 +152,9 @@ int gpsat_engine_i8_timeouts(gpsat_engine* eng, int* out);
  * built with -DGPSAT_I8_PHASES; a development aid): prologue, pass-0 MMAs, drain 0, pass-1 MMAs, drain 1,
  * Q tile store, gradient reduction, tiles. */
 int gpsat_engine_i8_phases(gpsat_engine* eng, uint64_t* out8, int reset);
+/* Same for step_kernel (library built with -DGPSAT_STEP_PHASES): potrf tiles in out32[0..15], trtri tiles in
+ * out32[16..31]; see g_step_phase in gpsat_b200/csrc/step_kernel.cuh for the phase list. */
+int gpsat_engine_step_phases(gpsat_engine* eng, uint64_t* out32, int reset);
 void gpsat_fit_options_default(gpsat_fit_options* opt);
 
 /* lml[e] = log marginal likelihood, grad[e][P] = d lml / d theta (constrained space). */

@@ -391,3 +391,51 @@ def test_i8_gradient_path_matches_dmma_path(engine, kind, D):
         np.testing.assert_allclose(g1[e], g0[e], rtol=1e-10, atol=1e-11 * scale)
         v, g = gpr.lml_and_grad(kind, X, y, theta[e])
         np.testing.assert_allclose(g1[e], g, rtol=1e-7, atol=1e-8 * np.abs(g).max())
+
+
+@pytest.mark.parametrize("kind,D,noise", [("Matern32", 3, None), ("RBF", 2, None), ("Matern12", 1, None),
+                                          ("Matern52", 3, 1e-4)])
+def test_i8_step_path_matches_dmma_path(engine, kind, D, noise):
+    """The potrf / trtri main loops on the int8 tensor path (8 exact slices with a-priori row scales,
+    step_kernel.cuh) against the FP64 mma.sync loops and against the oracle: experts of 2..11 tile rows, ragged
+    sizes around the tile edges, prediction rows, and a badly conditioned case (noise 1e-4, condition ~1e6)
+    where the a-priori scale of U = L^-T is far above its typical entries."""
+    rng = np.random.default_rng(177 + D)
+    ns = [129, 200, 256, 257, 383, 640, 1000, 1300]
+    experts = [_expert(rng, n, D, m=37 + (n % 200)) for n in ns]
+    b = _batch(kind, experts, with_pred=True)
+    theta = np.stack([_theta(rng, D) for _ in ns])
+    if noise is not None:
+        theta[:, -1] = noise
+    out = {}
+    try:
+        for path in ("dmma", "i8"):
+            engine.set_step_path(path)
+            lml, g, st = engine.lml_grad(b, theta)
+            p = engine.predict(b, theta)
+            L, U = engine.factor_debug(kind, experts[3][0], experts[3][1], theta[3])
+            out[path] = (lml, g, st, p, L, U)
+    finally:
+        engine.set_step_path("i8")
+    assert engine.i8_timeouts() == 0
+    (lml0, g0, st0, p0, L0, U0), (lml1, g1, st1, p1, L1, U1) = out["dmma"], out["i8"]
+    assert np.all(st0 == 0) and np.all(st1 == 0)
+    assert not np.array_equal(lml0, lml1)                  # the two paths really are different arithmetic
+    # factor of the 257-observation expert: elementwise against the row scales the slicing uses
+    np.testing.assert_allclose(L1, L0, rtol=0, atol=1e-12 * np.abs(L0).max())
+    np.testing.assert_allclose(U1, U0, rtol=0, atol=1e-10 * np.abs(U0).max())
+    loose = noise is not None                              # condition number ~1e6: the oracle itself moves at 1e-9
+    np.testing.assert_allclose(lml1, lml0, rtol=1e-9 if loose else 1e-11)
+    off = b.off_m
+    for e, (X, y, Xs) in enumerate(experts):
+        scale = np.abs(g0[e]).max()
+        np.testing.assert_allclose(g1[e], g0[e], rtol=1e-6 if loose else 1e-8, atol=(1e-7 if loose else 1e-9) * scale)
+        v, g = gpr.lml_and_grad(kind, X, y, theta[e])
+        assert abs(lml1[e] - v) <= 1e-8 * abs(v)
+        np.testing.assert_allclose(g1[e], g, rtol=1e-5 if loose else 1e-7, atol=(1e-6 if loose else 1e-8) * np.abs(g).max())
+        pr = gpr.predict(kind, X, y, theta[e], Xs)
+        sl = slice(off[e], off[e + 1])
+        tol = 1e-6 if loose else 1e-8
+        np.testing.assert_allclose(p1["f*"][sl], pr["f*"], rtol=tol, atol=tol * np.abs(pr["f*"]).max())
+        np.testing.assert_allclose(p1["f*_var"][sl], pr["f*_var"], rtol=tol, atol=tol * theta[e][D])
+        np.testing.assert_allclose(p1["f*"][sl], p0["f*"][sl], rtol=tol / 10, atol=tol / 10 * np.abs(pr["f*"]).max())
