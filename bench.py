@@ -166,7 +166,7 @@ def run_reference(args):
                              "sample": f"{sample} experts of {spec.name} per step, NumPy/SciPy oracle, "
                                        f"one process per core, 1 BLAS thread each"},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def run_ours(args):
@@ -281,11 +281,35 @@ def run_ours(args):
         traffic, traffic_src = tj["dram_bytes_read"] + tj["dram_bytes_write"], tj["source"]
     except Exception:
         pass
+    # executed int8 work of the sliced k-sums: 36 slice-pair MMAs of 2 * 128^3 ops per k-block of a
+    # potrf / trtri / diagonal-sum tile
+    int8 = None
+    if os.environ.get("GPSAT_B200_STEP", "i8") != "dmma":
+        T = np.ceil((n + 1) / 128.0)
+        TR = np.ceil((n + 1 + m) / 128.0)
+        kb_pot = T * (T - 1) * (T - 2) / 6.0
+        kb_tr = (T - 1) * T * (T + 1) / 6.0
+        kb_dg = np.maximum((T - 1) * (T - 2) / 2.0, 0.0)
+        kb_pred = kb_pot + (TR - T) * T * (T - 1) / 2.0 + kb_dg
+        ops = args.steps * 2.0 * 128.0 ** 3 * 36.0 * float(np.sum(nev * (kb_pot + kb_tr + kb_dg)) + np.sum(kb_pred))
+        try:
+            pk = json.load(open(os.path.join(ROOT, "profiles", "r01f_i8_rate.json")))
+            i8peak = float(pk["rate"]["n128"]["int8_tops"]) / 1e3
+        except Exception:
+            i8peak = 3.48
+        int8 = {"achieved": ops / (ms_step * 1e-3) / 1e15, "peak": i8peak, "unit": "POP/s",
+                "frac": ops / (ms_step * 1e-3) / 1e15 / i8peak,
+                "note": "executed int8 tensor ops of step_kernel's sliced k-sums / its CUDA-event time (which also holds "
+                        "the FP64 epilogues); peak = measured tcgen05 kind::i8 rate at M = N = 128 (profiles/r01f_i8_rate.json)"}
     roofline = {"bound": "tensor", "kernel": "step_kernel (potrf/trtri tiles: int8-sliced tcgen05 main loops, FP64 DMMA epilogues, fused diagonal factorisation)"
                 if os.environ.get("GPSAT_B200_STEP", "i8") != "dmma" else "step_kernel (FP64 DMMA potrf/trtri tiles + fused diagonal factorisation)",
                 "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak, "traffic": traffic,
                 "traffic_source": traffic_src, "peak_source": peak_src,
                 "launches": int(n_step), "avg_launch_ms": ms_step / max(n_step, 1),
+                "int8_tensor": int8,
+                "note": "achieved = algorithmic FP64 flops / kernel time, peak = measured FP64 (DMMA) pipe peak; with the "
+                        "k-sums on the int8 tensor path the fraction is an FP64-equivalent rate and may exceed 1"
+                        if int8 else None,
                 "whole_job_tflops": total_flops / (ms_total * 1e-3) / 1e12,
                 "whole_job_frac": total_flops / (ms_total * 1e-3) / 1e12 / peak,
                 "kernel_share_of_step": {"step_kernel": ms_step / ms_total, "lauum_grad_kernel": ms_lauum / ms_total,
@@ -335,13 +359,27 @@ def run_ours(args):
                 "lml_grad_evals_per_s": world * float(nev.sum()) * args.steps / (ms_total * 1e-3),
                 "roofline": roofline, "cpu_baseline": cpu_baseline, "e2e": e2e, "gpu_launches": int(launches),
                 "clocks": clk}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+def emit(line):
+    """The one JSON line goes to the real stdout; everything else printed to fd 1 during the run (NCCL's version
+    banner, library chatter) was redirected to stderr in main()."""
+    _REAL_STDOUT.write(json.dumps(line) + "\n")
+    _REAL_STDOUT.flush()
+
+
+_REAL_STDOUT = sys.stdout
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
