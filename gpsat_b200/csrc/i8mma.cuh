@@ -234,8 +234,6 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   if (warp == 0) tmem_alloc(smem_u32(&tmem_base), 512);
-  load_block_coords(d, i * NB, xr, ar, tid);      // ar / ac overwritten with alpha below
-  load_block_coords(d, j * NB, xc, ac, tid);
   const int8_t* Ubase = planes8 ? d.Uq8 : d.Uq;
   const size_t tile_b = planes8 ? (size_t)8 * I8_PLANE_B : (size_t)I8_S * I8_PLANE_B;
   const size_t slab_b = planes8 ? (size_t)8 * I8_SLAB_B : (size_t)I8_S * I8_SLAB_B;
@@ -253,11 +251,6 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  for (int r = tid; r < NB; r += GPSAT_THREADS) {
-    int gi = i * NB + r, gj = j * NB + r;
-    ar[r] = (gi < n) ? -d.A[(size_t)gi * ld + n] : 0.0;
-    ac[r] = (gj < n) ? -d.A[(size_t)gj * ld + n] : 0.0;
-  }
   const uint32_t tb = tmem_base;
   const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[I8_NST]), accb = smem_u32(&bars[2 * I8_NST]);
   const uint32_t pipe_s = smem_u32(pipe);
@@ -332,6 +325,16 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
       }
       umma_commit(accb);
       ok = mbar_wait(accb, pass) && ok;       // only this thread polls; the others sleep in the barrier below
+    } else if (pass == 0 && tid >= 64) {
+      // warps 2..7 are idle during the loop: they fetch what the gradient reduction needs (coordinates, alpha)
+      constexpr int NT = GPSAT_THREADS - 64;
+      load_block_coords(d, i * NB, xr, ar, tid - 64, NT);      // ar / ac overwritten with alpha by the same threads
+      load_block_coords(d, j * NB, xc, ac, tid - 64, NT);
+      for (int r = tid - 64; r < NB; r += NT) {
+        int gi = i * NB + r, gj = j * NB + r;
+        ar[r] = (gi < n) ? -d.A[(size_t)gi * ld + n] : 0.0;
+        ac[r] = (gj < n) ? -d.A[(size_t)gj * ld + n] : 0.0;
+      }
     }
     it += nslabs;
     __syncwarp();

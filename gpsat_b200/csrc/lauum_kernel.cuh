@@ -28,48 +28,70 @@ __device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c,
 #pragma unroll
   for (int dd = 0; dd < ND; ++dd) pd[dd] = 0.0;
   if (g0r + NB <= n && g0r > g0c) {
-    // interior off-diagonal tile: every element counts twice, no bounds, no diagonal
-#pragma unroll 4
-    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
-      const double aa = ar[r] * acv;
-      const double wq = 2.0 * (aa - (Cs[r * LDC + c] - aac * aa));
-      double sd[ND], r2 = 0.0;
+    // interior off-diagonal tile: every element counts twice, no bounds, no diagonal.  Batches of 4 rows keep 4
+    // independent exp / sqrt chains in flight per thread.
+    constexpr int UB = 4, RS = GPSAT_THREADS / NB;
+#pragma unroll 1
+    for (int r0 = tid >> 7; r0 < NB; r0 += RS * UB) {
+      double wq[UB], sd[UB][ND], ku[UB], gu[UB];
 #pragma unroll
-      for (int dd = 0; dd < ND; ++dd) {
-        double t = (DD > 0 || dd < D) ? xr[dd * NB + r] - cc.x[dd] : 0.0;
-        sd[dd] = t * t;
-        r2 += sd[dd];
+      for (int u = 0; u < UB; ++u) {
+        const int r = r0 + RS * u;
+        const double aa = ar[r] * acv;
+        wq[u] = 2.0 * (aa - (Cs[r * LDC + c] - aac * aa));
+        double r2 = 0.0;
+#pragma unroll
+        for (int dd = 0; dd < ND; ++dd) {
+          double t = (DD > 0 || dd < D) ? xr[dd * NB + r] - cc.x[dd] : 0.0;
+          sd[u][dd] = t * t;
+          r2 += sd[u][dd];
+        }
+        kunit_gunit_of_r2<KIND>(r2, ku[u], gu[u]);
       }
-      double ku, gu;
-      kunit_gunit_of_r2<KIND>(r2, ku, gu);
-      const double wg = wq * gu;
 #pragma unroll
-      for (int dd = 0; dd < ND; ++dd) pd[dd] = fma(wg, sd[dd], pd[dd]);
-      pk = fma(wq, ku, pk);
+      for (int u = 0; u < UB; ++u) {
+        const double wg = wq[u] * gu[u];
+#pragma unroll
+        for (int dd = 0; dd < ND; ++dd) pd[dd] = fma(wg, sd[u][dd], pd[dd]);
+        pk = fma(wq[u], ku[u], pk);
+      }
     }
   } else if (gj < n) {
-#pragma unroll 2
-    for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
-      const int gi = g0r + r;
-      if (gi >= n || gj > gi) continue;
-      const double aa = ar[r] * acv;
-      // aac = 1: the tile holds Ks^-1 + alpha alpha^T (column n of U is -alpha); aac = 0: Ks^-1 alone
-      const double q = aa - (Cs[r * LDC + c] - aac * aa);
-      const double wq = (gi == gj) ? q : 2.0 * q;
-      double sd[ND], r2 = 0.0;
+    // diagonal tiles and the tiles of the last block row: same batches, dead elements (rows >= n, columns above
+    // the diagonal) enter with weight zero; batches that are dead for the whole warp are skipped
+    constexpr int UB = 4, RS = GPSAT_THREADS / NB;
+    const int wc0 = g0c + (c & ~31);                 // first column of this warp
+#pragma unroll 1
+    for (int r0 = tid >> 7; r0 < NB; r0 += RS * UB) {
+      if (g0r + r0 >= n) break;
+      if (g0r + r0 + RS * (UB - 1) < wc0) continue;
+      double wq[UB], qd[UB], sd[UB][ND], ku[UB], gu[UB];
 #pragma unroll
-      for (int dd = 0; dd < ND; ++dd) {
-        double t = (DD > 0 || dd < D) ? xr[dd * NB + r] - cc.x[dd] : 0.0;
-        sd[dd] = t * t;
-        r2 += sd[dd];
+      for (int u = 0; u < UB; ++u) {
+        const int r = r0 + RS * u, gi = g0r + r;
+        const bool live = gi < n && gj <= gi;
+        const double aa = ar[r] * acv;
+        // aac = 1: the tile holds Ks^-1 + alpha alpha^T (column n of U is -alpha); aac = 0: Ks^-1 alone
+        const double q = aa - (Cs[r * LDC + c] - aac * aa);
+        wq[u] = live ? ((gi == gj) ? q : 2.0 * q) : 0.0;
+        qd[u] = (live && gi == gj) ? q : 0.0;
+        double r2 = 0.0;
+#pragma unroll
+        for (int dd = 0; dd < ND; ++dd) {
+          double t = (DD > 0 || dd < D) ? xr[dd * NB + r] - cc.x[dd] : 0.0;
+          sd[u][dd] = t * t;
+          r2 += sd[u][dd];
+        }
+        kunit_gunit_of_r2<KIND>(r2, ku[u], gu[u]);
       }
-      double ku, gu;
-      kunit_gunit_of_r2<KIND>(r2, ku, gu);
-      const double wg = wq * gu;
 #pragma unroll
-      for (int dd = 0; dd < ND; ++dd) pd[dd] = fma(wg, sd[dd], pd[dd]);
-      pk = fma(wq, ku, pk);
-      if (gi == gj) pn += q;
+      for (int u = 0; u < UB; ++u) {
+        const double wg = wq[u] * gu[u];
+#pragma unroll
+        for (int dd = 0; dd < ND; ++dd) pd[dd] = fma(wg, sd[u][dd], pd[dd]);
+        pk = fma(wq[u], ku[u], pk);
+        pn += qd[u];
+      }
     }
   }
 #pragma unroll

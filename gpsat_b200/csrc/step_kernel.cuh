@@ -45,7 +45,9 @@ __device__ unsigned long long g_step_phase[32];
 enum { I8M_POTRF = 0, I8M_TRTRI = 1, I8M_DIAG = 2 };
 __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk, int i, unsigned char* pipe, double* Cs,
                                                   uint64_t* bars, uint32_t* tmem_slot, double* csd, int tid,
-                                                  int mode, bool first, bool last, long long& tphase, int phbase) {
+                                                  int mode, bool first, bool last, long long& tphase, int phbase,
+                                                  double* xr = nullptr, double* xc = nullptr, double* yr = nullptr,
+                                                  double* yc = nullptr) {
   const bool is_pot = mode != I8M_TRTRI;
   const bool same = mode == I8M_DIAG;
   const int warp = tid >> 5, lane = tid & 31;
@@ -115,6 +117,10 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
       }
       umma_commit(accb);
       ok = mbar_wait(accb, pass) && ok;       // only this thread polls; the others sleep in the barrier below
+    } else if (pass == 0 && xr != nullptr && tid >= 64) {
+      // warps 2..7 have nothing to do during the loop: they fetch the coordinates the covariance epilogue needs
+      load_block_coords(d, rowblk * NB, xr, yr, tid - 64, GPSAT_THREADS - 64);
+      load_block_coords(d, i * NB, xc, yc, tid - 64, GPSAT_THREADS - 64);
     }
     __syncwarp();
     ok = __all_sync(0xffffffffu, ok);         // warp-uniform: tcgen05.ld below is warp-collective
@@ -237,14 +243,10 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv, int S, int nt
   // ---- 1. main loop (slab loads first, the coordinate loads hide behind them) ----
   const bool use_i8 = d.Lq != nullptr && i > 0 && (is_pot || d.Uq8 != nullptr);
   if (use_i8) {
-    if (is_pot) {
-      load_block_coords(d, rowblk * NB, xr, yr, tid);
-      load_block_coords(d, i * NB, xc, yc, tid);
-    }
     // the CTA of tile (i + 1, i) runs the int8 loop a second time for the diagonal tile's Schur complement
     potrf_mainloop_i8(d, rowblk, i, reinterpret_cast<unsigned char*>(smem), Cs, bars, &tmem_slot, csd, tid,
                       is_pot ? I8M_POTRF : I8M_TRTRI, true, !(diag_sum && is_pot && x == 0 && rowblk < d.T), tphase,
-                      phbase);
+                      phbase, is_pot ? xr : nullptr, xc, yr, yc);
     wmult_prefetch(Wg, wst, tid);      // W_ii streams in under the epilogue
   } else {
     Acc acc;

@@ -199,9 +199,11 @@ __device__ __forceinline__ void gemm_nt_mainloop(Acc& acc, const double* Ag, con
 // xs[dim][row] (structure of arrays: a warp reading 32 consecutive rows of one dimension is
 // conflict-free, a warp reading one row is a broadcast); yv[128] gets the observation values of
 // the block (0 outside [0, n)).
-__device__ __forceinline__ void load_block_coords(const SlotDesc& d, int g0, double* xs, double* yv, int tid) {
+// (tid, nthr): the threads that take part, numbered from 0 (default: the whole CTA).
+__device__ __forceinline__ void load_block_coords(const SlotDesc& d, int g0, double* xs, double* yv, int tid,
+                                                  int nthr = GPSAT_THREADS) {
   const int D = d.D, n = d.n, m = d.m;
-  for (int idx = tid; idx < NB * D; idx += GPSAT_THREADS) {
+  for (int idx = tid; idx < NB * D; idx += nthr) {
     int row = idx / D, dd = idx - row * D;
     int g = g0 + row;
     double v = 0.0;
@@ -209,7 +211,7 @@ __device__ __forceinline__ void load_block_coords(const SlotDesc& d, int g0, dou
     else if (g > n && g < n + 1 + m) v = d.Xs[(size_t)(g - n - 1) * D + dd] * d.inv_ls[dd];
     xs[dd * NB + row] = v;
   }
-  for (int row = tid; row < NB; row += GPSAT_THREADS) {
+  for (int row = tid; row < NB; row += nthr) {
     int g = g0 + row;
     yv[row] = (g < n) ? d.y[g] : 0.0;
   }
@@ -263,25 +265,61 @@ __device__ __forceinline__ void add_aug_tile_t(const SlotDesc& d, int g0r, int g
   if (rows_plain && g0c + NB <= n) {
     const double var = d.var;
     if (g0r != g0c) {
-#pragma unroll 4
-      for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
-        Cs[r * LDC + c] += var * kunit_of_r2<KIND>(cc.r2(xr, r, d.D));
+      // batches of 8 rows: the 8 kernel values are independent dependency chains (the read-modify-write of Cs
+      // would otherwise serialise the iterations: one ~36-instruction FP64 chain at a time per warp)
+      constexpr int UB = 8, RS = GPSAT_THREADS / NB;
+#pragma unroll 1
+      for (int r0 = tid >> 7; r0 < NB; r0 += RS * UB) {
+        double v[UB];
+#pragma unroll
+        for (int u = 0; u < UB; ++u) v[u] = var * kunit_of_r2<KIND>(cc.r2(xr, r0 + RS * u, d.D));
+#pragma unroll
+        for (int u = 0; u < UB; ++u) Cs[(r0 + RS * u) * LDC + c] += v[u];
+      }
     } else {
+      // diagonal tile of observation rows: + noise on the diagonal; with lower_only the batches that lie above
+      // the diagonal for the whole warp are skipped
       const double noise = d.noise;
-#pragma unroll 4
-      for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
-        if (lower_only && c > r) continue;
-        double v = var * kunit_of_r2<KIND>(cc.r2(xr, r, d.D));
-        Cs[r * LDC + c] += (r == c) ? v + noise : v;
+      constexpr int UB = 8, RS = GPSAT_THREADS / NB;
+      const int wc0 = c & ~31;
+#pragma unroll 1
+      for (int r0 = tid >> 7; r0 < NB; r0 += RS * UB) {
+        if (lower_only && r0 + RS * (UB - 1) < wc0) continue;
+        double v[UB];
+#pragma unroll
+        for (int u = 0; u < UB; ++u) v[u] = var * kunit_of_r2<KIND>(cc.r2(xr, r0 + RS * u, d.D));
+#pragma unroll
+        for (int u = 0; u < UB; ++u) {
+          const int r = r0 + RS * u;
+          if (!(lower_only && c > r)) Cs[r * LDC + c] += (r == c) ? v[u] + noise : v[u];
+        }
       }
     }
     return;
   }
+  // tiles that contain the observation row, prediction rows next to padding, or identity columns: the kernel value
+  // is formed for every element (coordinates outside the data are zeros) and then selected, so that the batches stay
+  // branch-free
   const double ycv = yc[c];
-#pragma unroll 2
-  for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
-    if (lower_only && c > r) continue;
-    Cs[r * LDC + c] += aug_value<KIND, DD>(d, g0r + r, g0c + c, r, xr, cc, ycv);
+  const double var = d.var, noise = d.noise;
+  const int gc = g0c + c, nm = n + 1 + d.m;
+  constexpr int UB = 8, RS = GPSAT_THREADS / NB;
+  const int wc0 = c & ~31;
+#pragma unroll 1
+  for (int r0 = tid >> 7; r0 < NB; r0 += RS * UB) {
+    if (lower_only && r0 + RS * (UB - 1) < wc0) continue;
+    double v[UB];
+#pragma unroll
+    for (int u = 0; u < UB; ++u) v[u] = var * kunit_of_r2<KIND>(cc.r2(xr, r0 + RS * u, d.D));
+#pragma unroll
+    for (int u = 0; u < UB; ++u) {
+      const int r = r0 + RS * u, gr = g0r + r;
+      double w = (gr == gc) ? v[u] + noise : v[u];
+      if (gr >= nm) w = 0.0;
+      if (gr == n) w = ycv;
+      if (gc >= n) w = (gr == gc && gr > n) ? 1.0 : 0.0;
+      if (!(lower_only && c > r)) Cs[r * LDC + c] += w;
+    }
   }
 }
 

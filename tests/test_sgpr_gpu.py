@@ -174,6 +174,12 @@ def test_sgpr_model_driver_sequence(engine, golden_dir):
     from gpsat_b200.models import B200SGPRModel
     g = np.load(os.path.join(golden_dir, "kat_localexperts.npz"))
     eps = float(g["eps"])
+    # The inducing points are the first rows of a shuffle drawn from numpy's global generator, as in the reference
+    # (gpflow_models.py:816-819).  With M = N = 50 and the 1e-6 jitter this ELBO is flat to rounding at the optimum,
+    # and whether L-BFGS ends with "converged" or "abnormal line search" there depends on the summation order, i.e.
+    # on the shuffle (about 5 of 24 orders end abnormal, with either exp implementation; the lengthscale is right in
+    # all of them).  Fix the order so that the reference's own `assert result` is reproducible.
+    np.random.seed(0)
     m = B200SGPRModel(coords=g["x_train"].copy(), obs=g["y_train"].copy(), kernel="Matern32",
                       num_inducing_points=50, noise_variance=eps ** 2, verbose=False)
     assert m.param_names == ["lengthscales", "kernel_variance", "likelihood_variance", "inducing_points"]
