@@ -182,7 +182,9 @@ __device__ __forceinline__ void wmult_strip(AccStrip& acc, const double* Cs, con
   const int strip = strip_of_warp(warp);
   constexpr int NSL = NB / KC;
   const double* ap = Cs + (16 * strip + lr) * LDC + lk;
-#pragma unroll 1
+  // fully unrolled: the first live column fragment of every k block (kb >> 1) becomes a compile-time constant, so
+  // the B loads of a k block are issued together instead of one predicated load in front of each pair of DMMAs
+#pragma unroll
   for (int s = 0; s < NSL; ++s) {
     cp_async_wait<NWSTAGE - 2>();
     __syncthreads();
