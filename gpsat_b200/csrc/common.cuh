@@ -47,6 +47,8 @@ struct SlotDesc {
   int* uex;              // [T*NB] row scale exponents of the planes
   int8_t* Lq;            // int8 slice planes of the strict lower block triangle (step_kernel.cuh), nullptr = DMMA potrf
   int8_t* Uq8;           // same for U = L^-T with a-priori row scales (trtri main loop), nullptr = DMMA trtri
+  int8_t* Lq_mem;        // the slot's plane storage; Lq / Uq8 point at it for evaluations the precision rule admits
+  int8_t* Uq8_mem;       //   (slot_set_theta in engine.cu) and are nullptr otherwise: FP64 mma.sync for that evaluation
   double ynorm2;         // |y|^2 (a-priori scale of the observation row of the factor)
   double inv_ls[GPSAT_DMAX];
   double var;            // kernel variance

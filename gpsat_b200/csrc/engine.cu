@@ -58,6 +58,7 @@ struct BatchDev {
   const double* Xs;
   const int* order;         // experts sorted by n, descending
   const double* ynorm2;     // [E] |y|^2 per expert
+  double i8_rho_max;        // precision rule: int8-sliced k-sums only while (var + noise) / noise <= this (0 = always)
 };
 
 struct FitDev {
@@ -177,15 +178,23 @@ __device__ __forceinline__ void slot_set_expert(SlotDesc& d, const SlotMem& mem,
   d.gpart = mem.gpart; d.notpd = mem.notpd;
   d.pre = nullptr; d.pre_s = nullptr; d.ldpre = 0;
   d.Uq = mem.Uq; d.uex = mem.uex;
-  d.Lq = mem.Lq; d.Uq8 = mem.Uq8; d.ynorm2 = b.ynorm2 ? b.ynorm2[e] : 0.0;
+  d.Lq = d.Lq_mem = mem.Lq; d.Uq8 = d.Uq8_mem = mem.Uq8; d.ynorm2 = b.ynorm2 ? b.ynorm2[e] : 0.0;
   *d.notpd = 0;
   *d.quad = 0.0;
 }
 
-__device__ __forceinline__ void slot_set_theta(SlotDesc& d, const double* theta) {
+// Precision rule of the int8-sliced k-sums (i8slice.cuh): their truncation is 2^-56 of A-PRIORI row bounds
+// (|L_rk| <= sqrt(var + noise), |U_rk| <= 1 / sqrt(noise), |L^-1 y| <= |y| / sqrt(noise)), so against the entries
+// themselves the accuracy falls with rho = (var + noise) / noise.  Evaluations with rho above rho_max take the FP64
+// mma.sync loops instead (the FP64 tiles are always stored, so the choice is free per slot and per evaluation).
+// The threshold comes from the measured envelope, profiles/r02_precision_envelope.md.
+__device__ __forceinline__ void slot_set_theta(SlotDesc& d, const double* theta, double rho_max) {
   for (int k = 0; k < d.D; ++k) d.inv_ls[k] = 1.0 / theta[k];
   d.var = theta[d.D];
   d.noise = theta[d.D + 1];
+  const bool ok = !(rho_max > 0.0) || (d.var + d.noise <= rho_max * d.noise);
+  d.Lq = ok ? d.Lq_mem : nullptr;
+  d.Uq8 = ok ? d.Uq8_mem : nullptr;
 }
 
 // lml and d lml / d theta from the sweep's by-products (fixed summation order => reproducible)
@@ -220,7 +229,7 @@ __device__ void fit_begin_expert(SlotDesc& d, const SlotMem& mem, LbfgsState& st
     if (f.trainable[q]) x0[np++] = transform_inv(f.tkind[q], f.ta[q], f.tb[q], f.theta[q]);
   }
   lbfgs_init(&st, np, x0);
-  slot_set_theta(d, f.theta + (size_t)e * P);
+  slot_set_theta(d, f.theta + (size_t)e * P, b.i8_rho_max);
 }
 
 __global__ void fit_init_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, FitDev f, int S, int ld) {
@@ -330,7 +339,7 @@ __global__ void lbfgs_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, F
     else d.expert = -1;
   } else {
     fit_theta_trial(f, st, e, P, theta);
-    slot_set_theta(d, theta);
+    slot_set_theta(d, theta, b.i8_rho_max);
     *d.notpd = 0;
     *d.quad = 0.0;
   }
@@ -348,7 +357,7 @@ __global__ void eval_init_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev 
   if (base + s < b.E) {
     int e = b.order[base + s];
     slot_set_expert(slots[s], mems[s], b, e, with_pred, ld);
-    slot_set_theta(slots[s], theta + (size_t)e * b.P);
+    slot_set_theta(slots[s], theta + (size_t)e * b.P, b.i8_rho_max);
   } else {
     slots[s].expert = -1;
   }

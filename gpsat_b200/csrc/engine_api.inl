@@ -54,10 +54,26 @@ int gpsat_engine_step_phases(gpsat_engine* h, uint64_t* out32, int reset) {
 
 int gpsat_engine_i8_timeouts(gpsat_engine* h, int* out) {
   REQUIRE(h != nullptr && out != nullptr, "NULL argument");
-  CUDA_TRY(cudaStreamSynchronize(h->e.stream));
-  CUDA_TRY(cudaMemcpyFromSymbol(out, g_i8_timeout, sizeof(int)));
+  *out = (int)h->e.i8_timeouts_seen;
   return 0;
 }
+
+int gpsat_engine_debug_set_i8_spin_limit(gpsat_engine* h, int polls) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  CUDA_TRY(cudaSetDevice(h->e.device));
+  CUDA_TRY(cudaStreamSynchronize(h->e.stream));
+  CUDA_TRY(cudaMemcpyToSymbol(g_i8_spin_limit, &polls, sizeof(int)));
+  return 0;
+}
+
+int gpsat_engine_set_precision_rule(gpsat_engine* h, double rho_max) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  REQUIRE(rho_max >= 0.0, "rho_max must be >= 0 (0 = int8-sliced arithmetic at any conditioning)");
+  h->e.i8_rho_max = rho_max;
+  return 0;
+}
+
+double gpsat_engine_precision_rule_default(void) { return I8_RHO_MAX_DEFAULT; }
 
 void gpsat_fit_options_default(gpsat_fit_options* o) {
   o->pgtol = 1e-5;
@@ -93,7 +109,7 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
   CUDA_TRY(cudaStreamCreateWithFlags(&h->e.stream, cudaStreamNonBlocking));
   CUDA_TRY(cudaEventCreate(&h->e.ev0));
   CUDA_TRY(cudaEventCreate(&h->e.ev1));
-  CUDA_TRY(cudaMallocHost(&h->e.h_counters, 4 * sizeof(int)));
+  CUDA_TRY(cudaMallocHost(&h->e.h_counters, 8 * sizeof(int)));
   if (engine_setup_kernels()) { delete h; return 1; }
   if (const char* lp = getenv("GPSAT_B200_LAUUM")) {
     h->e.i8_lauum = strcmp(lp, "dmma") != 0;
@@ -101,6 +117,7 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
   }
   if (const char* sp = getenv("GPSAT_B200_STEP")) h->e.i8_step = strcmp(sp, "dmma") != 0;
   if (const char* dp = getenv("GPSAT_B200_DIAGSUM")) h->e.i8_diag_sum = strcmp(dp, "0") != 0;
+  if (const char* rp = getenv("GPSAT_B200_RHO_MAX")) h->e.i8_rho_max = std::max(0.0, atof(rp));
   h->e.num_sms = prop.multiProcessorCount;
   *out = h;
   return 0;
@@ -143,13 +160,24 @@ static void begin_call(Engine& g) {
   g.evtype.clear();
   cudaEventRecord(g.ev0, g.stream);
 }
+// Every product call ends here.  A bounded barrier wait of the int8 pipeline that gave up (mbar_wait in i8mma.cuh)
+// left unfinished accumulators in some tile: the call fails instead of returning them.
 static int end_call(Engine& g) {
+  CUDA_TRY(cudaMemcpyFromSymbolAsync(g.h_counters + 4, g_i8_timeout, sizeof(int), 0, cudaMemcpyDeviceToHost, g.stream));
   CUDA_TRY(cudaEventRecord(g.ev1, g.stream));
   CUDA_TRY(cudaStreamSynchronize(g.stream));
   float ms = 0.f;
   CUDA_TRY(cudaEventElapsedTime(&ms, g.ev0, g.ev1));
   g.stats.gpu_ms = ms;
   if (g.profile) prof_collect(g);
+  if (g.h_counters[4] != 0) {
+    const int zero = 0;
+    cudaMemcpyToSymbol(g_i8_timeout, &zero, sizeof(int));
+    g.i8_timeouts_seen++;
+    g_last_error = "gpsat: a barrier wait of the int8 tensor pipeline timed out; the results of this call are invalid "
+                   "(per-expert outputs must not be used)";
+    return 3;
+  }
   return 0;
 }
 

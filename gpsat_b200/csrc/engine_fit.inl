@@ -102,10 +102,11 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   int evals = 0;
   for (;;) {
     CUDA_TRY(cudaMemcpyAsync(g.h_counters, fd.counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyFromSymbolAsync(g.h_counters + 4, g_i8_timeout, sizeof(int), 0, cudaMemcpyDeviceToHost, g.stream));
     CUDA_TRY(cudaStreamSynchronize(g.stream));
     const int occupied = g.h_counters[1], Tcur = g.h_counters[2];
     evals = g.h_counters[3];
-    if (occupied == 0) break;
+    if (occupied == 0 || g.h_counters[4] != 0) break;      // done, or an int8 pipeline time-out (end_call reports it)
     CUDA_TRY(cudaMemsetAsync(fd.counters + 1, 0, 2 * sizeof(int), g.stream));
     if (launch_sweep(g, S, Tcur, Tcur, true)) return 1;
     {
@@ -118,7 +119,7 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   g.stats.evals = evals; g.stats.slots = S;
   if (fit_fetch(g, mem, E, P, fd, theta_io, objective, lml, n_evals, n_iters, status)) return 1;
   CUDA_TRY(cudaGetLastError());
-  if (end_call(g)) return 1;
+  if (int rc = end_call(g)) return rc;
   // flops: n^3 per evaluation (needs per-expert counts, which are on the host only in HOST mode)
   if (!dev) for (int64_t e = 0; e < E; ++e) g.stats.sweep_flops += (double)n_evals[e] * (double)g.hn[e] * g.hn[e] * g.hn[e];
   return 0;

@@ -1,6 +1,10 @@
 // Host-side engine: memory, launch sequences, C ABI.  Included at the end of engine.cu.
 namespace gpsat {
 
+// Default of the precision rule (slot_set_theta in engine.cu): the measured envelope behind it is
+// profiles/r02_precision_envelope.md.
+constexpr double I8_RHO_MAX_DEFAULT = 4096.0;
+
 struct DevBuf {
   void* p = nullptr;
   size_t cap = 0;
@@ -26,7 +30,8 @@ struct Engine {
   int device = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  int* h_counters = nullptr;          // pinned [4]
+  int* h_counters = nullptr;          // pinned [8]: [0..3] fit counters, [4] int8-pipeline time-out flag of the last call
+  int64_t i8_timeouts_seen = 0;       // calls that failed with a time-out since the engine was created
   DevBuf bX, by, bXs, boffn, boffm, border, btheta, bmisc, bslots, bmems, bA, bside, bstates, bout, bcov, bZ, bsg;
   gpsat_stats stats{};
   // host copy of the current batch shape
@@ -44,6 +49,8 @@ struct Engine {
   bool i8_step = true;
   bool i8_diag_sum = true;          // GPSAT_B200_DIAGSUM=0: per-tile SYRK + RED instead of the one-go int8 Schur complement
   bool lauum_planes8 = false;       // set by engine_alloc_slots: lauum_grad_i8_kernel reads d.Uq8
+  // precision rule (slot_set_theta in engine.cu): evaluations with (var + noise) / noise above this run on FP64 mma.sync
+  double i8_rho_max = I8_RHO_MAX_DEFAULT;
   DevBuf bLq, bUq8, bynorm;
   bool profile = false;
   std::vector<cudaEvent_t> evpool;
@@ -164,6 +171,7 @@ static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with
     }
   }
   out.ynorm2 = nullptr;
+  out.i8_rho_max = g.i8_rho_max;
   if (g.i8_step && E > 0) {
     if (g.bynorm.ensure(E * 8)) return 1;
     ynorm_kernel<<<(unsigned)E, 128, 0, g.stream>>>(out.off_n, out.y, g.bynorm.as<double>());
@@ -283,6 +291,10 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, cons
       if (g.lauum_planes8) {
         lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots, 1);
         g.stats.kernel_launches++;
+        if (g.i8_rho_max > 0.0) {      // slots the precision rule took off the planes for this evaluation
+          lauum_grad_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots, 1);
+          g.stats.kernel_launches++;
+        }
       } else {
         u_rowmax_kernel<<<dim3(Tmax * NB / 8, S), 256, 0, g.stream>>>(slots);
         u_slice_kernel<<<dim3(ntile, S), 256, 0, g.stream>>>(slots);
@@ -293,7 +305,7 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, cons
         g.stats.kernel_launches += 3;
       }
     } else {
-      lauum_grad_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots);
+      lauum_grad_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots, 0);
       g.stats.kernel_launches++;
     }
   }

@@ -64,7 +64,7 @@ int gpsat_local_select(gpsat_engine* h, int64_t N, int32_t C, const double* data
     g.stats.d2h_bytes += (double)total * 8;
   }
   CUDA_TRY(cudaGetLastError());
-  if (end_call(g)) return 1;
+  if (int rc = end_call(g)) return rc;
   if (idx)
     for (int64_t e = 0; e < E; ++e) REQUIRE(counts[e] == off[e + 1] - off[e], "off does not match the selection counts");
   return 0;

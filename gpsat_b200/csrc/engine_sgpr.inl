@@ -269,7 +269,7 @@ int gpsat_sgpr_fit(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off
   g.stats.evals = evals; g.stats.slots = S;
   if (fit_fetch(g, mem, E, P, fd, theta_io, objective, elbo, n_evals, n_iters, status)) return 1;
   CUDA_TRY(cudaGetLastError());
-  if (end_call(g)) return 1;
+  if (int rc = end_call(g)) return rc;
   if (mem != GPSAT_MEM_DEVICE)
     for (int64_t e = 0; e < E; ++e) g.stats.sweep_flops += (double)n_evals[e] * sgpr_flops(g, off_z, e, true, false);
   return 0;

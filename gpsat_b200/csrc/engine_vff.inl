@@ -257,7 +257,7 @@ int gpsat_vff_fit(gpsat_engine* h, const gpsat_batch* batch, const gpsat_vff_dom
   g.stats.evals = evals; g.stats.slots = S;
   if (fit_fetch(g, mem, E, P, fd, theta_io, objective, elbo, n_evals, n_iters, status)) return 1;
   CUDA_TRY(cudaGetLastError());
-  if (end_call(g)) return 1;
+  if (int rc = end_call(g)) return rc;
   if (mem != GPSAT_MEM_DEVICE)
     for (int64_t e = 0; e < E; ++e) {
       const double M = (double)vff_M(dom, e, batch->D);

@@ -34,7 +34,9 @@ static_assert(I8_PIPE_B >= SM_TILE_D * 8, "Q tile must fit in the pipeline stage
 constexpr int LAUUM_I8_SMEM_BYTES = I8_PIPE_B + (SM_XY_D + 64) * 8 + 128;
 constexpr int I8_EXP_CLAMP = 400;
 
-__device__ int g_i8_timeout = 0;                 // set when a bounded barrier wait gives up (debug aid)
+__device__ int g_i8_timeout = 0;                 // set when a bounded barrier wait gives up; every product call reads
+                                                 // and clears it (end_call in engine_api.inl) and fails if it is set
+__constant__ int g_i8_spin_limit = 1 << 22;       // polls before a wait gives up (gpsat_engine_debug_set_i8_spin_limit)
 // cycles per phase of lauum_grad_i8_kernel summed over CTAs (thread 0's clock): prologue, pass-0 MMAs, drain 0,
 // pass-1 MMAs, drain 1, Q tile store, gradient reduction, tile count.  Built with -DGPSAT_I8_PHASES only.
 __device__ unsigned long long g_i8_phase[8];
@@ -75,11 +77,18 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
 }
 // bounded: a wait that never completes sets g_i8_timeout and returns false instead of hanging the GPU
 __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
-  for (int spin = 0; spin < (1 << 22); ++spin) {
+  // limit <= 0 (test hook): the wait completes normally and is then REPORTED as timed out, so the host-side error
+  // path runs end to end without abandoning a pipeline that still has bulk copies and MMAs in flight
+  const int limit = g_i8_spin_limit;
+  const int polls = limit > 0 ? limit : (1 << 22);
+  for (int spin = 0; spin < polls; ++spin) {
     uint32_t done;
     asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}\n"
                  : "=r"(done) : "r"(bar), "r"(parity) : "memory");
-    if (done) return true;
+    if (done) {
+      if (limit <= 0) g_i8_timeout = 1;
+      return true;
+    }
   }
   g_i8_timeout = 1;
   return false;
@@ -202,6 +211,7 @@ __global__ void __launch_bounds__(256) u_slice_kernel(const SlotDesc* __restrict
 __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const SlotDesc* __restrict__ slots, int planes8) {
   const SlotDesc& d = slots[blockIdx.y];
   if (d.expert < 0) return;
+  if (planes8 && d.Uq8 == nullptr) return;      // precision rule: this evaluation is lauum_grad_kernel's (FP64 mma.sync)
   const int T = d.T;
   const int t = blockIdx.x;
   if (t >= T * (T + 1) / 2) return;

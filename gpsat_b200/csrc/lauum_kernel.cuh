@@ -124,9 +124,10 @@ __device__ __noinline__ void grad_tile(const SlotDesc& d, int g0r, int g0c, cons
   }
 }
 
-__global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const SlotDesc* __restrict__ slots) {
+// skip_planes != 0: slots whose evaluation runs on the int8 planes (d.Uq8 set) belong to lauum_grad_i8_kernel.
+__global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_kernel(const SlotDesc* __restrict__ slots, int skip_planes) {
   const SlotDesc& d = slots[blockIdx.y];
-  if (d.expert < 0) return;
+  if (d.expert < 0 || (skip_planes && d.Uq8 != nullptr)) return;
   const int T = d.T;
   const int t = blockIdx.x;
   if (t >= T * (T + 1) / 2) return;

@@ -164,7 +164,9 @@ class Engine:
 
     def set_lauum_path(self, path: str):
         """``"i8"`` (default): K^-1 tile products of the gradient by error-free int8 slicing on the
-        tcgen05 tensor path; ``"dmma"``: FP64 ``mma.sync``.  Both give FP64-level results."""
+        tcgen05 tensor path; ``"dmma"``: FP64 ``mma.sync``.  The int8 slices are taken against a-priori
+        bounds, so they match FP64 only while (var + noise) / noise stays moderate: see
+        :meth:`set_precision_rule` (on by default) and ``profiles/r02_precision_envelope.md``."""
         _lib.check(self._lib.gpsat_engine_set_lauum_path(self._h, {"dmma": 0, "i8": 1}[path]))
 
     def set_step_path(self, path: str):
@@ -185,10 +187,21 @@ class Engine:
         return [int(v) for v in out]
 
     def i8_timeouts(self) -> int:
-        """1 if a bounded barrier wait of the int8 path ever gave up (results invalid), else 0."""
+        """Number of calls that failed (raised) because a bounded barrier wait of the int8 pipeline gave up."""
         out = C.c_int(0)
         _lib.check(self._lib.gpsat_engine_i8_timeouts(self._h, C.byref(out)))
         return int(out.value)
+
+    def debug_set_i8_spin_limit(self, polls: int):
+        """Test hook: polls after which a barrier wait of the int8 pipeline gives up (default 2**22)."""
+        _lib.check(self._lib.gpsat_engine_debug_set_i8_spin_limit(self._h, int(polls)))
+
+    def set_precision_rule(self, rho_max=True):
+        """Per expert and evaluation: int8-sliced k-sums only while ``(var + noise) / noise <= rho_max``,
+        FP64 ``mma.sync`` above.  ``True`` = the library default, ``False`` / 0 = rule off."""
+        if rho_max is True:
+            rho_max = float(self._lib.gpsat_engine_precision_rule_default())
+        _lib.check(self._lib.gpsat_engine_set_precision_rule(self._h, float(rho_max or 0.0)))
 
     @property
     def stream_ptr(self) -> int:

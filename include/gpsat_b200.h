@@ -24,8 +24,9 @@
  *   - `mem` says where the data arrays live: GPSAT_MEM_HOST (the engine copies in and out on its
  *     own stream) or GPSAT_MEM_DEVICE (device pointers of the engine's device; nothing is copied).
  *     off_n / off_m are always host pointers.
- *   - every function returns 0 on success, non-zero on API misuse or a CUDA error
- *     (gpsat_last_error() gives the text); numerical trouble is reported per expert in status[].
+ *   - every function returns 0 on success, non-zero on API misuse (2), a CUDA error (1) or an internal
+ *     pipeline time-out (3; the outputs of that call are invalid); gpsat_last_error() gives the text.
+ *     Numerical trouble is reported per expert in status[].
  *   - a handle is bound to one device and one stream and is not thread-safe; use one handle per
  *     host thread / GPU rank.  No global mutable state besides the last-error string.
  */
@@ -146,8 +147,25 @@ int gpsat_engine_set_lauum_path(gpsat_engine* eng, int path);
 #define GPSAT_STEP_DMMA 0
 #define GPSAT_STEP_I8 1
 int gpsat_engine_set_step_path(gpsat_engine* eng, int path);
-/* out = 1 if a bounded barrier wait of the int8 path ever gave up (a bug indicator; results invalid). */
+/* Precision rule of the int8-sliced arithmetic.  The slices are taken against a-priori row bounds
+ * (sqrt(var + noise) for L, 1 / sqrt(noise) for U = L^-T), so relative to the entries themselves the accuracy
+ * falls with rho = (kernel_variance + likelihood_variance) / likelihood_variance.  Every objective evaluation
+ * whose rho exceeds rho_max runs its k-sums and K^-1 products as FP64 mma.sync instead - chosen per expert and
+ * per evaluation on the device, because the optimiser moves theta.  rho_max = 0 turns the rule off (int8-sliced
+ * at any conditioning; for measurements only).  Default: gpsat_engine_precision_rule_default(), from the envelope
+ * measured against an extended-precision oracle (profiles/r02_precision_envelope.md); the environment variable
+ * GPSAT_B200_RHO_MAX overrides it at engine creation.  GPflow's own floor of the likelihood variance is 1e-6
+ * (gpflow_models.py:404-411), i.e. rho up to 1e7 is reachable through the reference's API. */
+int gpsat_engine_set_precision_rule(gpsat_engine* eng, double rho_max);
+double gpsat_engine_precision_rule_default(void);
+/* A bounded barrier wait of the int8 tensor pipeline that gives up makes the call that ran it FAIL (non-zero
+ * return, gpsat_last_error() says so; per-expert outputs of that call must not be used).  out = number of calls
+ * that failed that way since the engine was created. */
 int gpsat_engine_i8_timeouts(gpsat_engine* eng, int* out);
+/* Test hook: number of polls after which such a wait gives up (default 2^22, i.e. seconds).  polls <= 0: every
+ * wait completes normally and is then reported as timed out (exercises the failure path of the calls without
+ * abandoning a pipeline that has copies in flight).  Process-wide. */
+int gpsat_engine_debug_set_i8_spin_limit(gpsat_engine* eng, int polls);
 /* Cycle counts per phase of the int8-path gradient kernel summed over its CTAs (all zero unless the library was
  * built with -DGPSAT_I8_PHASES; a development aid): prologue, pass-0 MMAs, drain 0, pass-1 MMAs, drain 1,
  * Q tile store, gradient reduction, tiles. */

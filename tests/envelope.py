@@ -1,0 +1,84 @@
+"""Cases of the conditioning sweep: which noise / signal-variance / size / duplicate-row
+regimes the default (int8-sliced) arithmetic, the FP64 mma.sync path and a LAPACK float64 implementation can hold
+to the 1e-8 parity bar, measured against the extended-precision oracle (oracle/longdouble_gpr.c).
+
+Shared by oracle/make_envelope_golden.py (writes tests/golden/precision_envelope.npz, CPU only),
+tests/test_gpu_parity.py::test_i8_precision_envelope and tools/precision_envelope.py.
+Everything is seeded with numpy.random.default_rng, so the GPU box regenerates the same inputs bit for bit.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+# GPflow's floor of the Gaussian likelihood variance is 1e-6 (gpflow_models.py:404-411); the sweep sits just above
+NOISES = (1e-2, 1e-4, 1e-6 + 1e-9)
+VARS = (0.05, 1.0, 10.0)
+SIZES = (1000, 2000, 4000)
+KINDS = ("Matern32", "RBF")
+M_PRED = 32
+LS = (3.0, 3.5, 4.0)
+
+
+def cases(sizes=SIZES):
+    out = []
+    for kind in KINDS:
+        for n in sizes:
+            for noise in NOISES:
+                for var in VARS:
+                    out.append(dict(name=f"{kind}-n{n}-s{noise:.0e}-v{var:g}", kind=kind, n=n, noise=noise, var=var,
+                                    dup=0.10, D=3, seed=len(out)))
+    return out
+
+
+def _rff(rng, kind, X, ls, var, nfeat=384):
+    z = rng.standard_normal((nfeat, X.shape[1]))
+    if kind == "RBF":
+        omega = z / np.asarray(ls)[None, :]
+    else:
+        nu = {"Matern12": 0.5, "Matern32": 1.5, "Matern52": 2.5}[kind]
+        omega = z * np.sqrt(2 * nu / rng.chisquare(2 * nu, size=(nfeat, 1))) / np.asarray(ls)[None, :]
+    phase = rng.uniform(0, 2 * np.pi, nfeat)
+    w = rng.standard_normal(nfeat)
+    return np.sqrt(2.0 * var / nfeat) * (np.cos(X @ omega.T + phase) @ w)
+
+
+def make_case(c):
+    """(X [n, 3], y [n], Xs [M_PRED, 3], theta [5]) of one sweep case: c2-like geometry in scaled units (x, y in
+    [-6, 6], t whole days in [-4, 4]), observations drawn from the model at theta (so y^T Ks^-1 y ~ n), and `dup`
+    of the rows exact coordinate duplicates of other rows (repeat passes over the same bin)."""
+    rng = np.random.default_rng([2024, c["seed"]])
+    n = c["n"]
+    X = np.stack([rng.uniform(-6, 6, n), rng.uniform(-6, 6, n), rng.integers(-4, 5, n).astype(float)], axis=1)
+    ndup = int(c["dup"] * n)
+    if ndup:
+        dst = rng.choice(n, ndup, replace=False)
+        src = rng.choice(np.setdiff1d(np.arange(n), dst), ndup, replace=True)
+        X[dst] = X[src]
+    theta = np.array([*LS, c["var"], c["noise"]])
+    y = _rff(rng, c["kind"], X, LS, c["var"]) + np.sqrt(c["noise"]) * rng.standard_normal(n)
+    Xs = np.stack([rng.uniform(-5, 5, M_PRED), rng.uniform(-5, 5, M_PRED), np.zeros(M_PRED)], axis=1)
+    return X, y, Xs, theta
+
+
+def smoke_case():
+    """The reference's own ill-conditioned smoke (test_numerical_stability.py:15-75): a 20 x 20 grid in unscaled
+    metre coordinates (+-1000 km), RBF with lengthscales 50 000 m, noise variance 0.1, kernel variance 1."""
+    xs = np.linspace(-1000000, 1000000, 20)
+    xm, ym = np.meshgrid(xs, xs)
+    rng = np.random.default_rng(42)
+    th = 0.5 + 0.3 * np.sin(xm / 500000) * np.cos(ym / 500000) + rng.normal(0, 0.1, xm.shape)
+    X = np.stack([xm.ravel() + rng.normal(0, 1e-6, xm.size), ym.ravel() + rng.normal(0, 1e-6, xm.size)], axis=1)
+    theta = np.array([50000.0, 50000.0, 1.0, 0.1])
+    Xs = np.stack([rng.uniform(-9e5, 9e5, M_PRED), rng.uniform(-9e5, 9e5, M_PRED)], axis=1)
+    return X, th.ravel(), Xs, theta
+
+
+def rel_errors(lml, grad, fmean, fvar, ref, theta):
+    """Error measures of one result against the extended-precision reference `ref` (dict lml, grad, fmean, fvar):
+    relative for the LML, relative to the largest component for the gradient, relative to max |f*| for the mean,
+    relative to the signal variance for f*_var (the prior variance the posterior variance is subtracted from)."""
+    D = len(theta) - 2
+    return dict(lml=abs(lml - ref["lml"]) / abs(ref["lml"]),
+                grad=float(np.max(np.abs(grad - ref["grad"])) / np.max(np.abs(ref["grad"]))),
+                fmean=float(np.max(np.abs(fmean - ref["fmean"])) / max(np.max(np.abs(ref["fmean"])), 1e-300)),
+                fvar=float(np.max(np.abs(fvar - ref["fvar"])) / theta[D]))
