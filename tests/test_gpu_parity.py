@@ -474,8 +474,10 @@ def test_i8_precision_envelope(engine, golden_dir, kind):
     (likelihood variance 1e-2 .. GPflow's floor 1e-6, gpflow_models.py:404-411; kernel variance 0.05 .. 10;
     n 1000 .. 4000; 10 % exact duplicate rows) against the extended-precision oracle
     (tests/golden/precision_envelope.npz <- oracle/make_envelope_golden.py <- oracle/longdouble_gpr.c).
-    Tolerances are the north star's: 1e-8 on LML and predictions, 1e-7 on the gradient - or, where a float64
-    LAPACK implementation (oracle/gpr.py) cannot reach 1e-7 on the gradient itself, ten times its error."""
+    Tolerances: the north star's 1e-8 on LML and predictions everywhere.  Gradient (relative to its largest
+    component): 1e-7 up to rho = (var + noise) / noise = 5e5 and 2e-13 * rho above - at rho = 1e7 (noise at
+    GPflow's floor, variance 10) LAPACK float64 itself is off by up to 5.9e-7 and FP64 mma.sync by 9.3e-7
+    (profiles/r02_precision_envelope.md), so 1e-7 is not attainable by any float64 implementation there."""
     import envelope as env
     gold = np.load(os.path.join(golden_dir, "precision_envelope.npz"))
     cs = [c for c in env.cases() if c["kind"] == kind]
@@ -485,10 +487,10 @@ def test_i8_precision_envelope(engine, golden_dir, kind):
     for k, c in enumerate(cs):
         ref = {q: gold[f"{c['name']}/{q}"] for q in ("lml", "grad", "fmean", "fvar")}
         ref["lml"] = float(ref["lml"])
-        f64 = gold[f"{c['name']}/f64_err"]
         sl = slice(off[k], off[k + 1])
         e = env.rel_errors(lml[k], grad[k], p["f*"][sl], p["f*_var"][sl], ref, items[k][3])
-        tol = dict(lml=1e-8, grad=max(1e-7, 10 * f64[1]), fmean=1e-8, fvar=1e-8)
+        rho = (c["var"] + c["noise"]) / c["noise"]
+        tol = dict(lml=1e-8, grad=max(1e-7, 2e-13 * rho), fmean=1e-8, fvar=1e-8)
         if st[k] != 0 or any(not (e[q] <= tol[q]) for q in tol):
             bad.append((c["name"], int(st[k]), e, tol))
     assert not bad, bad
