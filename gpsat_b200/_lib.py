@@ -30,8 +30,9 @@ EXPORTED_SYMBOLS = (
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
     "gpsat_sgpr_elbo", "gpsat_sgpr_predict", "gpsat_sgpr_fit",
     "gpsat_vff_elbo", "gpsat_vff_predict", "gpsat_vff_fit",
-    "gpsat_gaussian_smooth", "gpsat_glue_predictions", "gpsat_local_select",
+    "gpsat_gaussian_smooth", "gpsat_glue_predictions", "gpsat_local_select", "gpsat_local_select_count_noalloc",
 )
+NOALLOC_MAX_CHUNK_COUNTS = 1 << 20
 
 
 class Batch(C.Structure):
@@ -121,6 +122,8 @@ def load():
     lib.gpsat_glue_predictions.argtypes = [vp, C.c_int, C.c_int64, C.c_int64, vp, C.c_int, vp, vp, vp, C.c_int64, vp, vp]
     lib.gpsat_local_select.argtypes = [vp, C.c_int64, C.c_int32, vp, C.c_int64, C.c_int32, vp, C.c_int32,
                                        C.POINTER(SelectCond), vp, vp, vp]
+    lib.gpsat_local_select_count_noalloc.argtypes = [vp, C.c_int64, C.c_int32, vp, C.c_int64, C.c_int32, vp, C.c_int32,
+                                                     C.POINTER(SelectCond), vp]
     _lib = lib
     return lib
 

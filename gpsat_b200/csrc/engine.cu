@@ -405,3 +405,4 @@ __global__ void debug_extract_kernel(const SlotDesc* slots, double* Lout, double
 }  // namespace gpsat
 
 #include "engine_host.inl"
+#include "engine_noalloc.inl"

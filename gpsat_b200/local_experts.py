@@ -407,6 +407,32 @@ def select_all(engine, table: np.ndarray, locs: np.ndarray, conds: list):
     return counts, off, idx[:int(off[-1])]
 
 
+def select_count_noalloc(engine, table, locs, conds: list, counts):
+    """``gpsat_local_select_count_noalloc``: the counting pass of :func:`select_all` without any allocation inside
+    the library (no counterpart in the reference; see ``include/gpsat_b200.h``).  ``table`` [N, C], ``locs`` [E, CL]
+    (float64) and ``counts`` [E] (int64) are contiguous torch CUDA tensors on the engine's device, owned by the
+    caller; ``E * ceil(N / 1024)`` must not exceed ``_lib.NOALLOC_MAX_CHUNK_COUNTS``.  Calls that overlap on one
+    GPU race on the library's fixed scratch: one call at a time per device."""
+    import ctypes as C
+    import torch
+    from . import _lib
+    for t, dt in ((table, torch.float64), (locs, torch.float64), (counts, torch.int64)):
+        if not (t.is_cuda and t.is_contiguous() and t.dtype == dt):
+            raise ValueError("select_count_noalloc needs contiguous CUDA tensors (float64 table / locs, int64 counts)")
+    if counts.numel() != locs.shape[0]:
+        raise ValueError("counts needs one entry per expert location")
+    arr = (_lib.SelectCond * max(len(conds), 1))()
+    for q, (kind, op, cols, lcols, val) in enumerate(conds):
+        arr[q].kind, arr[q].op, arr[q].ncol, arr[q].val = kind, _OPS[op], len(cols), float(val)
+        for k in range(len(cols)):
+            arr[q].col[k], arr[q].loc_col[k] = int(cols[k]), int(lcols[k])
+    torch.cuda.current_stream(table.device).synchronize()     # inputs were produced on torch's stream
+    _lib.check(engine._lib.gpsat_local_select_count_noalloc(
+        engine._h, table.shape[0], table.shape[1], C.c_void_p(table.data_ptr()), locs.shape[0], locs.shape[1],
+        C.c_void_p(locs.data_ptr()), len(conds), arr, C.c_void_p(counts.data_ptr())))
+    return counts
+
+
 def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
     from .engine import RaggedBatch
     t0 = time.time()

@@ -299,6 +299,28 @@ int gpsat_local_select(gpsat_engine* eng, int64_t N, int32_t C, const double* da
                        const double* locs, int32_t ncond, const gpsat_select_cond* conds, int64_t* counts,
                        const int64_t* off, int64_t* idx);
 
+/* ---- allocation-free entry point -------------------------------------------------------------------
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ *
+ * The counting pass of gpsat_local_select (counts[e] = number of rows of the point table that satisfy every
+ * condition for expert e; same conditions, same kernels, same results) without any allocation: the function calls
+ * no cudaMalloc / cudaFree / cudaMallocHost and no allocating library routine.
+ *   - data [N][C], locs [E][CL] and counts [E] are DEVICE pointers of the engine's device, owned by the caller
+ *     (nothing is copied or staged; host pointers are rejected); conds is a host array as for gpsat_local_select.
+ *   - the per-(expert, 1024-point chunk) counters live in a fixed device array inside the library:
+ *     E * ceil(N / 1024) must not exceed GPSAT_NOALLOC_MAX_CHUNK_COUNTS (2^20 counters = 4 MiB, resident on every
+ *     GPU that loads the library until the process exits); larger problems are rejected with return code 2 and a
+ *     message - use gpsat_local_select for those.
+ *   - every call, from every engine and thread on a device, shares that one array, and it keeps the last call's
+ *     contents (harmless: each call overwrites every counter it reads, nothing needs to start at zero).  Calls
+ *     that overlap in time on the same GPU RACE on it: serialise them (one call at a time per device).
+ *   - N >= 1, 1 <= E < 65536.  The function returns after the engine's stream has drained, like the other calls. */
+#define GPSAT_NOALLOC_MAX_CHUNK_COUNTS (1 << 20)
+int gpsat_local_select_count_noalloc(gpsat_engine* eng, int64_t N, int32_t C, const double* data, int64_t E,
+                                     int32_t CL, const double* locs, int32_t ncond, const gpsat_select_cond* conds,
+                                     int64_t* counts);
+
 /* Test hook (single expert, host memory): dense factor of the augmented matrix.
  * Lout [(n+1)*(n+1)] row-major lower: rows < n = chol(K + s2 I), row n = (L^-1 y)^T, 1.
  * Uout [(n+1)*(n+1)] row-major upper: L_aug^-T (may be NULL). */
