@@ -41,7 +41,20 @@ WORKLOADS: Dict[str, WorkloadSpec] = {
     "c3": WorkloadSpec("c3_pan_arctic", 3000, 2000, 4000, 200, 1300, 500e3, 15, (25e3, 25e3, 1.0), (600e3, 600e3, 30.0)),
     # north-star run: 2048 experts x 2000 obs
     "ns": WorkloadSpec("ns_2048x2000", 2048, 2000, 2000, 400, 400, 400e3, 8, (50e3, 50e3, 1.0), (600e3, 600e3, 16.0)),
+    # c4  predict-only pass with smoothed hyper-parameters (GPSat/postprocessing.py:365-395): c3 experts at fixed theta
+    "c4": WorkloadSpec("c4_predict_only_smoothed", 3000, 2000, 4000, 200, 1300, 500e3, 15, (25e3, 25e3, 1.0), (600e3, 600e3, 30.0)),
+    # c5  GPflowSGPRModel large experts: ~20k observations, 500 inducing points (gpflow_models.py:704)
+    "c5": WorkloadSpec("c5_sgpr_20k_M500", 16, 20000, 20000, 200, 1300, 500e3, 15, (25e3, 25e3, 1.0), (600e3, 600e3, 30.0)),
 }
+SGPR_M = 500                                   # num_inducing_points default, gpflow_models.py:704
+FIXED_THETA = (4.0, 4.0, 5.0, 0.05, 0.005)     # the generating hyper-parameters: what c4 predicts at
+
+
+def inducing_points(X, index: int, seed: int = 0, M: int = SGPR_M):
+    """First M rows of a seeded shuffle of the coordinates (the reference shuffles unseeded,
+    gpflow_models.py:809-819, so parity needs Z passed in explicitly: SURVEY 7.3-7)."""
+    rng = np.random.default_rng([seed, int(index), 1])
+    return X[rng.permutation(len(X))[:M]].copy()
 
 
 def _rff_sample(rng, Xs, ls, var, nfeat=256):
@@ -77,6 +90,19 @@ def make_expert(spec: WorkloadSpec, index: int, seed: int = 0, with_pred: bool =
     xp, yp = disc(m, 0.66 * spec.radius)
     Xs = np.stack([xp, yp, np.zeros(m)], axis=1) / cs
     return X, obs, Xs
+
+
+def expert_sizes(spec: WorkloadSpec, indices, seed: int = 0, with_pred: bool = True):
+    """(n[], m[]) of the experts `indices` without generating their data (the first two draws of
+    :func:`make_expert`'s generator) - what the partitioner needs on every rank."""
+    n = np.empty(len(indices), np.int64)
+    m = np.zeros(len(indices), np.int64)
+    for k, e in enumerate(indices):
+        rng = np.random.default_rng([seed, int(e)])
+        n[k] = rng.integers(spec.n_lo, spec.n_hi + 1)
+        if with_pred:
+            m[k] = rng.integers(spec.m_lo, spec.m_hi + 1)
+    return n, m
 
 
 def make_batch(spec: WorkloadSpec, seed: int = 0, experts: Optional[range] = None, with_pred: bool = True) -> RaggedBatch:
