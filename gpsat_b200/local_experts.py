@@ -166,15 +166,45 @@ class LocalExpertOI:
     to predict at the expert location) and ``max_dist`` (``config_dataclasses.py:9-509``).
     """
 
-    def __init__(self, expert_locs: pd.DataFrame, data: pd.DataFrame, data_config: dict,
-                 model_config: Optional[dict] = None, pred_loc_config: Optional[dict] = None):
+    def __init__(self, expert_loc_config=None, data_config=None, model_config=None, pred_loc_config=None,
+                 local_expert_config=None):
+        """Two call forms.
+
+        Reference form (``GPSat/local_experts.py:142-222``):
+        ``LocalExpertOI(expert_loc_config, data_config, model_config, pred_loc_config)`` with dicts or the
+        dataclasses of :mod:`gpsat_b200.config_dataclasses` (or ``local_expert_config=ExperimentConfig``);
+        expert locations, observations and prediction locations are loaded through
+        :func:`gpsat_b200.config_dataclasses.load_table` (DataFrame / dict / csv / tsv / parquet / h5 sources).
+
+        In-memory form: ``LocalExpertOI(expert_locs_df, data_df, data_config, model_config, pred_loc_config)`` with
+        two DataFrames first."""
+        from . import config_dataclasses as cd
+        if isinstance(expert_loc_config, pd.DataFrame) and isinstance(data_config, pd.DataFrame):
+            expert_locs, data = expert_loc_config, data_config
+            data_config, model_config, pred_loc_config = model_config, pred_loc_config, local_expert_config
+            self.config = {}
+        else:
+            if local_expert_config is not None:
+                expert_loc_config = local_expert_config.expert_locs_config
+                data_config = local_expert_config.data_config
+                model_config = local_expert_config.model_config
+                pred_loc_config = local_expert_config.prediction_locs_config
+            plain = lambda c: c.to_dict_with_dataframe() if hasattr(c, "to_dict_with_dataframe") else (
+                c.to_dict() if hasattr(c, "to_dict") else dict(c or {}))
+            lc, dc, mc_, pc_ = plain(expert_loc_config), plain(data_config), plain(model_config), plain(pred_loc_config)
+            # what the reference stores as the "oi_config" of a run (local_experts.py:170-174, 873-884)
+            self.config = {"locations": cd._plain(lc), "data": cd._plain(dc), "model": cd._plain(mc_), "pred_loc": cd._plain(pc_)}
+            expert_locs = self._load_expert_locations(**lc)
+            data = cd.DataConfig(**{k: v for k, v in dc.items() if k in cd.DataConfig.__dataclass_fields__}).load()
+            data_config, model_config = dc, mc_
+            pred_loc_config = self._load_pred_loc(**pc_)
         self.expert_locs = expert_locs.reset_index(drop=True)
         self.data = data
         self.obs_col = data_config["obs_col"]
         self.coords_col = list(data_config["coords_col"])
-        self.local_select = data_config["local_select"]
+        self.local_select = data_config.get("local_select") or []
         mc = dict(model_config or {})
-        self.model_cls = resolve_model(mc.get("oi_model", "B200GPRModel"))
+        self.model_cls = resolve_model(mc.get("oi_model") or "B200GPRModel")
         self.load_params = mc.get("load_params")
         # replacement model for experts with few observations (local_experts.py:1021-1041)
         self.replacement_threshold = mc.get("replacement_threshold")
@@ -188,11 +218,48 @@ class LocalExpertOI:
         self.constraints = mc.get("constraints")
         self.optim_kwargs = dict(mc.get("optim_kwargs") or {})
         self.pred_kwargs = dict(mc.get("pred_kwargs") or {})
-        pts = mc.get("params_to_store", "all")
+        pts = mc.get("params_to_store") or "all"
         self.params_to_store = None if pts == "all" else pts
         pc = dict(pred_loc_config or {})
         self.pred_df = pc.get("df")
         self.max_dist = pc.get("max_dist")
+
+    @staticmethod
+    def _load_expert_locations(df=None, file=None, source=None, where=None, add_data_to_col=None, col_funcs=None,
+                               keep_cols=None, col_select=None, row_select=None, sort_by=None, reset_index=False,
+                               source_kwargs=None, verbose=False, **kwargs) -> pd.DataFrame:
+        """``LocalExpertOI.set_expert_locations`` (``local_experts.py:349-422``), legacy inputs included."""
+        from .config_dataclasses import load_table
+        if col_select is None and keep_cols is not None:
+            warnings.warn("\n'keep_cols' provided to set_expert_locations, use 'col_select' instead")
+            col_select = keep_cols
+        if source is None and df is not None:
+            warnings.warn("\n'df' was provided to set_expert_locations, use 'source' instead")
+            source = df
+        if source is None and file is not None:
+            warnings.warn("\n'file' was provided to set_expert_locations, use 'source' instead")
+            source = file
+        assert source is not None, "expert locations: no 'source' given"
+        locs = load_table(source, where=where, source_kwargs=source_kwargs, col_funcs=col_funcs, row_select=row_select,
+                          col_select=col_select, reset_index=reset_index, add_data_to_col=add_data_to_col, verbose=verbose)
+        if sort_by:
+            locs = locs.sort_values(sort_by)
+        return locs
+
+    @staticmethod
+    def _load_pred_loc(method="expert_loc", coords_col=None, df=None, df_file=None, max_dist=None, load_kwargs=None,
+                       X_out=None, **kwargs) -> dict:
+        """``PredictionLocations`` set-up (``GPSat/prediction_locations.py:50-206``): ``expert_loc`` predicts at the
+        expert location, ``from_dataframe`` / ``from_source`` at the rows of a table within ``max_dist``."""
+        from .config_dataclasses import load_table
+        if method == "expert_loc":
+            return {"df": None, "max_dist": None}
+        assert method in ("from_dataframe", "from_source"), f"pred_loc method '{method}' is not handled"
+        lk = dict(load_kwargs or {})
+        src = df if df is not None else (df_file if df_file is not None else lk.pop("source", None))
+        assert src is not None, "pred_loc: method is from_dataframe / from_source but no df, df_file or load_kwargs.source"
+        assert max_dist is not None, "pred_loc: max_dist is required with a prediction-location table"
+        return {"df": load_table(src, **lk), "max_dist": max_dist}
 
     @staticmethod
     def _scaled_constraints(constraints, init_params):
@@ -259,15 +326,45 @@ class LocalExpertOI:
             out[k] = v
         return out
 
+    def vectorisable(self) -> bool:
+        """The array-built path covers the exact model without a replacement model."""
+        return self.model_cls is B200GPRModel and self.replacement_threshold is None
+
     def run(self, store_path: Optional[str] = None, optimise: bool = True, predict: bool = True,
             min_obs: int = 3, table_suffix: str = "", config_id: int = 1,
-            device_select: bool = False) -> Dict[str, pd.DataFrame]:
+            device_select: Optional[bool] = False, store_every: int = 10, check_config_compatible: bool = True,
+            skip_valid_checks_on: Optional[list] = None, world: Optional[bool] = None) -> Dict[str, pd.DataFrame]:
         """All experts: select, fit, predict, tabulate.  Returns ``{table name: DataFrame}`` with the
         reference's tables (``preds``, ``run_details``, one per stored hyper-parameter), each name
         extended by ``table_suffix``.  ``device_select=True`` evaluates the selection rules of all
         experts in one GPU launch (``gpsat_local_select``) and builds the packed batch and the
         tables with array operations instead of one model instance and one DataFrame per expert
-        (exact-GPR model only); the tables are identical to the default path."""
+        (exact-GPR model only; ``None`` = whenever the configuration allows it); the tables are identical to the
+        default path.
+
+        ``store_every`` / ``check_config_compatible`` / ``skip_valid_checks_on`` are the reference's remaining
+        ``run`` arguments (``local_experts.py:761-790``): all experts are processed in one batch and stored once, so
+        ``store_every`` has no effect, and resuming into an existing store is GPSat's job (accepted, not acted on).
+
+        ``world``: under ``torchrun`` (``WORLD_SIZE`` > 1; ``None`` = detect) the experts are partitioned over the
+        ranks by ``parallel.lpt_partition`` on the selection counts, every rank runs its shard on its own GPU with
+        no communication, and one ``gather_object`` brings the tables to rank 0, which stores them and returns them
+        in the single-GPU order (other ranks return ``{}``).  Experts never interact, so the tables are bit-identical
+        to a single-GPU run."""
+        from . import parallel
+        rank, nranks, _ = parallel.dist_env()
+        if world is None:
+            world = nranks > 1
+        if device_select is None:
+            device_select = self.vectorisable()
+        if world and nranks > 1:
+            if not self.vectorisable():
+                raise NotImplementedError("multi-GPU runs use the array-built path: exact model (B200GPRModel) without a replacement model")
+            parallel.init_process_group()
+            tables = self._run_world(optimise, predict, min_obs, table_suffix, config_id, rank, nranks)
+            if rank == 0:
+                self._store(tables, store_path)
+            return tables
         if device_select:
             tables = self._run_vectorised(optimise, predict, min_obs, table_suffix, config_id)
             self._store(tables, store_path)
@@ -364,17 +461,86 @@ class LocalExpertOI:
         self._store(tables, store_path)
         return tables
 
-    @staticmethod
-    def _store(tables, store_path):
+    def _store(self, tables, store_path):
+        """``.h5`` paths: appended to an HDF5 store like the reference (``local_experts.py:499-550``; needs
+        PyTables) together with the ``oi_config`` table (``:873-884``).  Any other path is a directory that gets one
+        parquet file per table and ``oi_config.json``."""
         if store_path is None:
             return
-        try:
-            with pd.HDFStore(store_path, mode="a") as store:     # needs PyTables, like the reference
-                for k, v in tables.items():
-                    store.append(k, v, data_columns=True)
-        except ImportError as exc:
-            raise ImportError("writing result tables to HDF5 needs PyTables; call run(store_path=None) "
-                              "to get the tables as DataFrames") from exc
+        import json
+        cfg = json.dumps(getattr(self, "config", {}) or {}, default=str)
+        if str(store_path).endswith((".h5", ".hdf5")):
+            try:
+                with pd.HDFStore(store_path, mode="a") as store:     # needs PyTables, like the reference
+                    for k, v in tables.items():
+                        store.append(k, v, data_columns=True)
+                    store.append("oi_config", pd.DataFrame({"config": [cfg]}), min_itemsize={"config": max(len(cfg), 1)})
+            except ImportError as exc:
+                raise ImportError("writing result tables to HDF5 needs PyTables; give a directory as store_path "
+                                  "(parquet files) or call run(store_path=None) to get the tables as DataFrames") from exc
+            return
+        import os
+        os.makedirs(store_path, exist_ok=True)
+        for k, v in tables.items():
+            v.to_parquet(os.path.join(store_path, f"{k}.parquet"))
+        with open(os.path.join(store_path, "oi_config.json"), "w") as f:
+            f.write(cfg)
+
+    @staticmethod
+    def read_store(store_path) -> Dict[str, pd.DataFrame]:
+        """Tables of a directory store written by :meth:`run`."""
+        import os
+        return {f[:-8]: pd.read_parquet(os.path.join(store_path, f)) for f in sorted(os.listdir(store_path))
+                if f.endswith(".parquet")}
+
+    # ---- multi-GPU: partition, run the shard, one gather ---------------------------------------------------------
+    def _run_world(self, optimise, predict, min_obs, table_suffix, config_id, rank, nranks):
+        from . import parallel
+        import torch.distributed as dist
+        parts = self._partition_experts(nranks)
+        shard = LocalExpertOI.__new__(LocalExpertOI)
+        shard.__dict__.update(self.__dict__)
+        shard.expert_locs = self.expert_locs.iloc[parts[rank]].reset_index(drop=True)
+        tables = shard._run_vectorised(optimise, predict, min_obs, table_suffix, config_id)
+        payload = {"tables": tables, "row_expert": {k: parts[rank][v] for k, v in shard._row_expert.items()},
+                   "timings": shard.timings}
+        gathered = [None] * nranks if rank == 0 else None
+        dist.gather_object(payload, gathered, dst=0)
+        if rank != 0:
+            return {}
+        self.timings = {f"rank{r}": g["timings"] for r, g in enumerate(gathered)}
+        return merge_rank_tables(gathered, table_suffix)
+
+    def _partition_experts(self, nranks):
+        """LPT over the experts on n^3 evals + n^2 m with n, m from the counting pass of the selection."""
+        from . import parallel
+        eng, table, locs, conds, ptab, pconds = self._selection_inputs()
+        n = select_counts(eng, table, locs, conds)
+        m = np.ones(len(locs), np.int64) if ptab is None else select_counts(eng, ptab, locs, pconds)
+        return parallel.lpt_partition(parallel.expert_cost(n, m), nranks)
+
+
+def merge_rank_tables(gathered: list, table_suffix: str = "") -> Dict[str, pd.DataFrame]:
+    """Tables of all ranks in the row order of a single-GPU run: every table ordered by expert index, except that
+    ``run_details`` lists the experts with too few observations first (the order ``_run_vectorised`` writes).
+    ``gathered[r]`` = ``{"tables": {...}, "row_expert": {table: global expert index per row}}``."""
+    out = {}
+    names = []
+    for g in gathered:
+        for k in g["tables"]:
+            if k not in names:
+                names.append(k)
+    for k in names:
+        frames = [g["tables"][k] for g in gathered if k in g["tables"]]
+        ids = np.concatenate([np.asarray(g["row_expert"][k]) for g in gathered if k in g["tables"]])
+        df = pd.concat(frames)
+        if k == "run_details" + table_suffix:
+            small = np.isnan(df["run_time"].values)          # the NaN rows of experts below min_obs
+            order = np.lexsort((ids, ~small))
+        else:
+            order = np.argsort(ids, kind="stable")
+        out[k] = df.iloc[order]
+    return out
 
 
 # ---- vectorised driver path: batched selection on the GPU, array-built batch and tables ----------
@@ -407,6 +573,24 @@ def select_all(engine, table: np.ndarray, locs: np.ndarray, conds: list):
     return counts, off, idx[:int(off[-1])]
 
 
+def select_counts(engine, table: np.ndarray, locs: np.ndarray, conds: list) -> np.ndarray:
+    """Counting pass of :func:`select_all` alone (what the multi-GPU partitioner needs)."""
+    import ctypes as C
+    from . import _lib
+    table = np.ascontiguousarray(table, dtype=np.float64)
+    locs = np.ascontiguousarray(locs, dtype=np.float64)
+    arr = (_lib.SelectCond * max(len(conds), 1))()
+    for q, (kind, op, cols, lcols, val) in enumerate(conds):
+        arr[q].kind, arr[q].op, arr[q].ncol, arr[q].val = kind, _OPS[op], len(cols), float(val)
+        for k in range(len(cols)):
+            arr[q].col[k], arr[q].loc_col[k] = int(cols[k]), int(lcols[k])
+    counts = np.zeros(len(locs), dtype=np.int64)
+    _lib.check(engine._lib.gpsat_local_select(engine._h, len(table), table.shape[1], C.c_void_p(table.ctypes.data),
+                                              len(locs), locs.shape[1], C.c_void_p(locs.ctypes.data), len(conds), arr,
+                                              C.c_void_p(counts.ctypes.data), None, None))
+    return counts
+
+
 def select_count_noalloc(engine, table, locs, conds: list, counts):
     """``gpsat_local_select_count_noalloc``: the counting pass of :func:`select_all` without any allocation inside
     the library (no counterpart in the reference; see ``include/gpsat_b200.h``).  ``table`` [N, C], ``locs`` [E, CL]
@@ -433,26 +617,21 @@ def select_count_noalloc(engine, table, locs, conds: list, counts):
     return counts
 
 
-def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
-    from .engine import RaggedBatch
-    t0 = time.time()
-    if self.model_cls is not B200GPRModel or self.replacement_threshold is not None:
-        raise NotImplementedError("device_select=True supports the exact model (B200GPRModel) without a replacement model")
-    coords_col, D = self.coords_col, len(self.coords_col)
+def _template_model(self):
+    """One model instance on dummy data: parameter values, transforms and trainable flags do not depend on the data."""
+    D = len(self.coords_col)
     obs_col = self.obs_col if isinstance(self.obs_col, str) else self.obs_col[0]
-    locs = self.expert_locs[coords_col].values.astype(np.float64)
-    E = len(locs)
-    # template model: parameter values, transforms and trainable flags do not depend on the data
-    def template():
-        return B200GPRModel(coords=np.arange(2.0 * D).reshape(2, D), obs=np.array([[0.0], [1.0]]),
-                            coords_col=coords_col, obs_col=[obs_col], verbose=False, **self.init_params)
+    return B200GPRModel(coords=np.arange(2.0 * D).reshape(2, D), obs=np.array([[0.0], [1.0]]),
+                        coords_col=self.coords_col, obs_col=[obs_col], verbose=False, **self.init_params)
 
-    tmpl = template()
-    eng = tmpl.engine
-    cs = np.broadcast_to(np.atleast_2d(tmpl.coords_scale)[0, :], (D,)).astype(np.float64)
-    obs_scale = float(np.atleast_2d(tmpl.obs_scale).reshape(-1)[0])
-    local_mean = isinstance(self.init_params.get("obs_mean"), str) and self.init_params.get("obs_mean") == "local"
-    # ---- phase A: selection of observations and prediction locations for all experts ----
+
+def _selection_inputs(self):
+    """(engine, point table [N, D + 1], expert locations [E, D], observation conditions, prediction table or None,
+    prediction conditions) in the form ``gpsat_local_select`` takes them."""
+    coords_col = self.coords_col
+    obs_col = self.obs_col if isinstance(self.obs_col, str) else self.obs_col[0]
+    eng = _template_model(self).engine
+    locs = self.expert_locs[coords_col].values.astype(np.float64)
     table = np.ascontiguousarray(self.data[coords_col + [obs_col]].values, dtype=np.float64)
     conds = []
     for ls in self.local_select:
@@ -464,16 +643,38 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
             assert comp in ["<", "<="], "for multi dimensional values only less than comparison handled"
             ids = [coords_col.index(c) for c in col]
             conds.append((1, "<=", ids, ids, ls["val"]))          # KD-tree ball query: d <= r
+    ptab, pconds = None, []
+    if self.pred_df is not None:
+        shared = [c for c in coords_col if c in self.pred_df]
+        ptab = np.ascontiguousarray(self.pred_df[shared].values, dtype=np.float64)
+        sid = [coords_col.index(c) for c in shared]
+        pconds = [] if self.max_dist is None else [(1, "<", list(range(len(shared))), sid, self.max_dist)]
+    return eng, table, locs, conds, ptab, pconds
+
+
+def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
+    from .engine import RaggedBatch
+    from . import _lib
+    t0 = time.time()
+    if not self.vectorisable():
+        raise NotImplementedError("device_select=True supports the exact model (B200GPRModel) without a replacement model")
+    coords_col, D = self.coords_col, len(self.coords_col)
+    template = lambda: _template_model(self)
+    tmpl = template()
+    cs = np.broadcast_to(np.atleast_2d(tmpl.coords_scale)[0, :], (D,)).astype(np.float64)
+    obs_scale = float(np.atleast_2d(tmpl.obs_scale).reshape(-1)[0])
+    local_mean = isinstance(self.init_params.get("obs_mean"), str) and self.init_params.get("obs_mean") == "local"
+    # ---- phase A: selection of observations and prediction locations for all experts ----
+    eng, table, locs, conds, ptab, pconds = _selection_inputs(self)
+    eng = tmpl.engine
+    E = len(locs)
     n_all, off_all, idx_all = select_all(eng, table, locs, conds)
-    if self.pred_df is None:
+    if ptab is None:
         m_all = np.ones(E, dtype=np.int64)
         poff_all = np.arange(E + 1, dtype=np.int64)
         pidx_all, shared = None, []
     else:
         shared = [c for c in coords_col if c in self.pred_df]
-        ptab = np.ascontiguousarray(self.pred_df[shared].values, dtype=np.float64)
-        sid = [coords_col.index(c) for c in shared]
-        pconds = [] if self.max_dist is None else [(1, "<", list(range(len(shared))), sid, self.max_dist)]
         m_all, poff_all, pidx_all = select_all(eng, ptab, locs, pconds)
     has_pred = m_all > 0                                       # local_experts.py:962-965
     small = has_pred & (n_all < min_obs)                       # local_experts.py:988-1012
@@ -544,12 +745,24 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
             pri = (np.tile(tmpl._pkind, (K, 1)), np.tile(tmpl._pa, (K, 1)), np.tile(tmpl._pb, (K, 1)))
         res = eng.fit(batch, theta, tkind, ta, tb, trainable, max_iter=int(opt_kwargs.pop("max_iter", 10_000)),
                       priors=pri, **kw)
-        ok_theta = res.status != 1
+        ok_theta = res.status != _lib.STATUS_NOT_PD
         theta = np.where(ok_theta[:, None], res.theta, theta)
-        success = res.status == 0
+        success = res.status == _lib.STATUS_OK
     if K and predict:
         out = eng.predict(batch, theta)
         objective = -np.asarray(out["lml"])
+        # an expert whose K + s2 I is not positive definite at its final hyper-parameters has no prediction: the
+        # per-model path raises FloatingPointError there (models.py), a batch reports it per expert instead - NaN
+        # predictions and objective, optimise_success False
+        bad = np.asarray(out["status"]) != _lib.STATUS_OK
+        if bad.any():
+            warnings.warn(f"{int(bad.sum())} expert(s): covariance not positive definite at the final hyper-parameters; "
+                          "their predictions are NaN")
+            badrows = np.repeat(bad, m_all[keep])
+            for key in ("f*", "f*_var", "y_var"):
+                out[key] = np.where(badrows, np.nan, np.asarray(out[key]))
+            objective = np.where(bad, np.nan, objective)
+            success = success & ~bad
     elif K:
         objective = -np.asarray(eng.lml_grad(batch, theta, with_grad=False)[0])
     else:
@@ -576,6 +789,7 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
         "config_id": config_id})
     rd.index = midx(np.concatenate([locs[sk], locs[keep]]))
     tables = {"run_details" + table_suffix: rd} if len(rd) else {}
+    row_expert = {"run_details" + table_suffix: np.concatenate([sk, keep])} if len(rd) else {}
     if K and predict:
         f_bar = np.repeat(means, m_all[keep]) if local_mean else np.zeros(len(pc))
         pr = pd.DataFrame({"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"], "f_bar": f_bar})
@@ -583,19 +797,24 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
             pr[f"pred_loc_{c}"] = pc[:, j]
         pr.index = midx(np.repeat(locs[keep], m_all[keep], axis=0))
         tables["preds" + table_suffix] = pr
+        row_expert["preds" + table_suffix] = np.repeat(keep, m_all[keep])
     store = self.params_to_store or tmpl.param_names
     if K:
         if "lengthscales" in store:
             ls = pd.DataFrame({"_dim_0": np.tile(np.arange(D), K), "lengthscales": theta[:, :D].reshape(-1)})
             ls.index = midx(np.repeat(locs[keep], D, axis=0))
             tables["lengthscales" + table_suffix] = ls
+            row_expert["lengthscales" + table_suffix] = np.repeat(keep, D)
         for name, col in (("kernel_variance", D), ("likelihood_variance", D + 1)):
             if name in store:
                 df = pd.DataFrame({name: theta[:, col].copy()})
                 df.index = midx(locs[keep])
                 tables[name + table_suffix] = df
+                row_expert[name + table_suffix] = keep.copy()
     self.timings = {"select_s": t_sel - t0, "engine_s": t_fit - t_sel, "tables_s": time.time() - t_fit}
+    self._row_expert = row_expert          # expert index (row of self.expert_locs) of every table row
     return tables
 
 
 LocalExpertOI._run_vectorised = _run_vectorised
+LocalExpertOI._selection_inputs = _selection_inputs

@@ -51,6 +51,13 @@ def get_engine(device: int = 0) -> Engine:
     return eng
 
 
+def default_device(device=None) -> int:
+    """CUDA device of a model: the one given, else this process's ``LOCAL_RANK`` (one rank per GPU under
+    ``torchrun``), else 0."""
+    import os
+    return int(device) if device is not None else int(os.environ.get("LOCAL_RANK", 0))
+
+
 def _processor_name() -> str:
     """CPU model string, as BaseGPRModel._get_processor_name does on Linux (base_model.py:302-324)."""
     try:
@@ -211,8 +218,8 @@ class B200GPRModel(BaseGPRModel):
     def __init__(self, data=None, coords_col=None, obs_col=None, coords=None, obs=None, coords_scale=None,
                  obs_scale=None, obs_mean=None, verbose=True, *, kernel="Matern32", kernel_kwargs=None,
                  mean_function=None, mean_func_kwargs=None, noise_variance=None, likelihood=None,
-                 device: int = 0, priors: Optional[dict] = None, **kwargs):
-        self.device = int(device)
+                 device: Optional[int] = None, priors: Optional[dict] = None, **kwargs):
+        self.device = default_device(device)
         super().__init__(data=data, coords_col=coords_col, obs_col=obs_col, coords=coords, obs=obs,
                          coords_scale=coords_scale, obs_scale=obs_scale, obs_mean=obs_mean, verbose=verbose)
         assert kernel is not None, "kernel was not provided"
@@ -532,7 +539,7 @@ class B200SGPRModel(B200GPRModel):
     def __init__(self, data=None, coords_col=None, obs_col=None, coords=None, obs=None, coords_scale=None,
                  obs_scale=None, obs_mean=None, verbose=True, *, kernel="Matern32", num_inducing_points=500,
                  kernel_kwargs=None, mean_function=None, mean_func_kwargs=None, noise_variance=None,
-                 likelihood=None, device: int = 0, priors: Optional[dict] = None, **kwargs):
+                 likelihood=None, device: Optional[int] = None, priors: Optional[dict] = None, **kwargs):
         super().__init__(data=data, coords_col=coords_col, obs_col=obs_col, coords=coords, obs=obs,
                          coords_scale=coords_scale, obs_scale=obs_scale, obs_mean=obs_mean, verbose=verbose,
                          kernel=kernel, kernel_kwargs=kernel_kwargs, mean_function=mean_function,
@@ -606,9 +613,9 @@ class B200VFFModel(B200GPRModel):
 
     def __init__(self, data=None, coords_col=None, obs_col=None, coords=None, coords_scale=None, obs=None,
                  obs_scale=None, obs_mean=None, *, kernel="Matern32", num_inducing_features=None, kernel_kwargs=None,
-                 mean_function=None, mean_func_kwargs=None, domain_size=None, expert_loc=None, device: int = 0,
+                 mean_function=None, mean_func_kwargs=None, domain_size=None, expert_loc=None, device: Optional[int] = None,
                  verbose=True, **kwargs):
-        self.device = int(device)
+        self.device = default_device(device)
         BaseGPRModel.__init__(self, data=data, coords_col=coords_col, obs_col=obs_col, coords=coords, obs=obs,
                               coords_scale=coords_scale, obs_scale=obs_scale, obs_mean=obs_mean, verbose=verbose)
         assert kernel is not None, "kernel was not provided"
