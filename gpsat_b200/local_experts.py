@@ -791,7 +791,8 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
     tables = {"run_details" + table_suffix: rd} if len(rd) else {}
     row_expert = {"run_details" + table_suffix: np.concatenate([sk, keep])} if len(rd) else {}
     if K and predict:
-        f_bar = np.repeat(means, m_all[keep]) if local_mean else np.zeros(len(pc))
+        # without obs_mean='local' the reference stores np.array([0]) - an integer - as the mean (base_model.py:199-200)
+        f_bar = np.repeat(means, m_all[keep]) if local_mean else np.zeros(len(pc), dtype=np.int64)
         pr = pd.DataFrame({"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"], "f_bar": f_bar})
         for j, c in enumerate(coords_col):
             pr[f"pred_loc_{c}"] = pc[:, j]
