@@ -118,10 +118,13 @@ def prediction_coords_for(pred_df: Optional[pd.DataFrame], expert_loc: dict, coo
 
 
 def dict_to_tables(x: dict, ref_loc: dict, table: Optional[str] = None) -> Dict[str, pd.DataFrame]:
-    """``dict_of_array_to_table`` of the reference (``local_experts.py:691-747``) for the shapes this
-    path produces: scalars and equal-length 1-d arrays are concatenated column-wise into one frame
-    named ``table``; with ``table=None`` every entry becomes its own frame, 1-d arrays with a
-    ``_dim_0`` column (``GPSat/utils.py:1437-1497``).  Frames are indexed by the expert location."""
+    """``dict_of_array_to_table`` of the reference (``local_experts.py:691-747``) for the shapes this path produces
+    (pinned on the reference function executed from source: ``tests/golden/driver_tables.json``).
+    ``table`` given (the reference's ``concat=True``, used for ``preds`` and ``run_details``, ``:1226-1233``): scalars
+    and 1-d arrays become the columns of one frame, outer-joined on their position, which appears as the leading
+    ``_dim_0`` column.  ``table=None`` (``concat=False``, the hyper-parameters, ``:1234-1236``): one frame per entry
+    with one ``_dim_i`` column per axis (scalars count as length-1 arrays: ``_dim_0`` = 0; ``array_to_dataframe``,
+    ``GPSat/utils.py:1437-1497``).  Frames are indexed by the expert location."""
     names = list(ref_loc.keys())
     vals = tuple(ref_loc.values())
 
@@ -130,24 +133,22 @@ def dict_to_tables(x: dict, ref_loc: dict, table: Optional[str] = None) -> Dict[
             return pd.Index([vals[0]] * nrow, name=names[0])
         return pd.MultiIndex.from_tuples([vals] * nrow, names=names)
 
+    def frame(k, v):
+        v = np.array([v]) if isinstance(v, (int, float, bool, str)) else np.asarray(v)
+        if v.ndim == 0:
+            v = v.reshape(1)
+        midx = pd.MultiIndex.from_product([np.arange(i) for i in v.shape], names=[f"_dim_{i}" for i in range(v.ndim)])
+        return pd.DataFrame(v.flat, index=midx, columns=[k])
+
     if len(x) == 0:
         return {}
     if table is not None:
-        cols = {k: np.atleast_1d(v) for k, v in x.items()}
-        nrow = max(len(v) for v in cols.values())
-        df = pd.DataFrame({k: (v if len(v) == nrow else np.repeat(v, nrow)) for k, v in cols.items()})
+        df = pd.concat([frame(k, v) for k, v in x.items()], join="outer", axis=1).reset_index()
         df.index = index(len(df))
         return {table: df}
     out = {}
     for k, v in x.items():
-        v = np.asarray(v)
-        if v.ndim == 0:
-            df = pd.DataFrame({k: [v.item()]})
-        elif v.ndim == 1:
-            df = pd.DataFrame({"_dim_0": np.arange(len(v)), k: v})
-        else:                                   # n-d (inducing points): one _dim_i column per axis, C order
-            grid = np.indices(v.shape).reshape(v.ndim, -1)
-            df = pd.DataFrame({**{f"_dim_{i}": grid[i] for i in range(v.ndim)}, k: v.reshape(-1)})
+        df = frame(k, v).reset_index()
         df.index = index(len(df))
         out[k] = df
     return out
@@ -779,6 +780,7 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
     sk = np.flatnonzero(small)
     per_expert = (t_fit - t_sel) / max(K, 1)
     rd = pd.DataFrame({
+        "_dim_0": np.zeros(len(sk) + K, dtype=np.int64),
         "num_obs": np.concatenate([n_all[sk], n_all[keep]]),
         "run_time": np.concatenate([np.full(len(sk), np.nan), np.full(K, per_expert)]),
         "objective_value": np.concatenate([np.full(len(sk), np.nan), objective]),
@@ -793,7 +795,8 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
     if K and predict:
         # without obs_mean='local' the reference stores np.array([0]) - an integer - as the mean (base_model.py:199-200)
         f_bar = np.repeat(means, m_all[keep]) if local_mean else np.zeros(len(pc), dtype=np.int64)
-        pr = pd.DataFrame({"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"], "f_bar": f_bar})
+        pos = np.arange(len(pc), dtype=np.int64) - np.repeat(off_m[:-1], m_all[keep])      # row number within the expert
+        pr = pd.DataFrame({"_dim_0": pos, "f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"], "f_bar": f_bar})
         for j, c in enumerate(coords_col):
             pr[f"pred_loc_{c}"] = pc[:, j]
         pr.index = midx(np.repeat(locs[keep], m_all[keep], axis=0))
@@ -808,7 +811,7 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
             row_expert["lengthscales" + table_suffix] = np.repeat(keep, D)
         for name, col in (("kernel_variance", D), ("likelihood_variance", D + 1)):
             if name in store:
-                df = pd.DataFrame({name: theta[:, col].copy()})
+                df = pd.DataFrame({"_dim_0": np.zeros(K, dtype=np.int64), name: theta[:, col].copy()})
                 df.index = midx(locs[keep])
                 tables[name + table_suffix] = df
                 row_expert[name + table_suffix] = keep.copy()

@@ -197,3 +197,114 @@ if __name__ == "__main__":
     sklearn_ard()
     vff_features()
     postprocessing()
+
+
+# ---- 6. driver-side functions of the reference, executed from source ---------------------
+def _extract(path, names, ns, in_class=None):
+    """exec the named top-level functions (or methods of `in_class`, decorators stripped) of a reference file."""
+    tree = ast.parse(open(path).read())
+    body = tree.body
+    if in_class is not None:
+        body = [n for n in tree.body if isinstance(n, ast.ClassDef) and n.name == in_class][0].body
+    fns = [n for n in body if isinstance(n, ast.FunctionDef) and n.name in names]
+    assert len(fns) == len(names), f"{path}: found {[f.name for f in fns]} of {names}"
+    for f in fns:
+        f.decorator_list = []
+    exec(compile(ast.Module(body=fns, type_ignores=[]), path, "exec"), ns)
+    return ns
+
+
+def _frame_to_json(df):
+    """Lossless JSON form of a result table (floats through repr): columns, dtypes, index names and values."""
+    import pandas as pd
+    idx = df.index
+    names = list(idx.names)
+    ivals = [list(map(float, idx.get_level_values(k))) for k in range(idx.nlevels)]
+    return {"columns": list(map(str, df.columns)), "dtypes": [str(df[c].dtype) for c in df.columns],
+            "index_names": names, "index": ivals,
+            "data": [df[c].tolist() for c in df.columns]}
+
+
+def driver_functions():
+    import json
+    import warnings
+    import numba as nb
+    import pandas as pd
+    from scipy.spatial import KDTree
+    util = os.path.join(REF, "GPSat", "utils.py")
+    ns = {"np": np, "pd": pd, "warnings": warnings, "KDTree": KDTree, "nb": nb}
+    _extract(util, {"pandas_to_dict", "array_to_dataframe", "dict_of_array_to_dict_of_dataframe"}, ns)
+    _extract(os.path.join(REF, "GPSat", "local_experts.py"), {"dict_of_array_to_table"}, ns, in_class="LocalExpertOI")
+    _extract(os.path.join(REF, "GPSat", "dataloader.py"), {"local_data_select"}, ns, in_class="DataLoader")
+    # _max_dist_bool keeps its numba decorator: re-apply the reference's guvectorize signature (prediction_locations.py:18-19)
+    _extract(os.path.join(REF, "GPSat", "prediction_locations.py"), {"_max_dist_bool"}, ns)
+    max_dist_bool = nb.guvectorize([(nb.float64[:, :], nb.float64[:], nb.float64[:], nb.bool_[:])],
+                                   '(n, d),(d), () -> (n)')(ns["_max_dist_bool"])
+    out = {}
+
+    # -- DataLoader.local_data_select (dataloader.py:2354-2447) --
+    rng = np.random.default_rng(11)
+    N = 3000
+    df = pd.DataFrame({"x": rng.uniform(-5e5, 5e5, N), "y": rng.uniform(-5e5, 5e5, N),
+                       "t": rng.integers(0, 20, N).astype(float), "obs": rng.standard_normal(N)})
+    # points exactly on the ball boundary of the first expert: (3, 4, .) * 1e5 is at distance 5e5 * ... use r = 5e5
+    df.loc[0, ["x", "y", "t"]] = [3e5, 4e5, 10.0]
+    df.loc[1, ["x", "y", "t"]] = [-3e5, -4e5, 14.0]         # on the ball and on the t <= +4 edge
+    df.loc[2, ["x", "y", "t"]] = [0.0, 0.0, 5.0]            # below the t >= -4 edge by one
+    locs = pd.DataFrame({"x": [0.0, 1e5, -2e5, 4e5, 0.0, 9e5], "y": [0.0, -1e5, 2e5, 4e5, 0.0, 9e5],
+                         "t": [10.0, 3.0, 18.0, 10.0, 0.0, 10.0]})
+    selects = {"example": [{"col": "t", "comp": "<=", "val": 4}, {"col": "t", "comp": ">=", "val": -4},
+                           {"col": ["x", "y"], "comp": "<", "val": 5e5}],
+               "strict_t": [{"col": "t", "comp": "<", "val": 4}, {"col": "t", "comp": ">", "val": -4},
+                            {"col": ["x", "y"], "comp": "<=", "val": 3e5}],
+               "ball3d": [{"col": ["x", "y", "t"], "comp": "<", "val": 2.5e5}, {"col": "t", "comp": "==", "val": 0}],
+               "empty": []}
+    sel = {}
+    for name, ls in selects.items():
+        for e in range(len(locs)):
+            got = ns["local_data_select"](None, df, locs.iloc[e], ls, kdtree=None, verbose=False)
+            sel[f"{name}/{e}"] = got.index.values.astype(np.int64)
+    np.savez_compressed(os.path.join(OUT, "driver_select.npz"), data=df.values, locs=locs.values,
+                        selects=json.dumps(selects), **sel)
+    print("local_data_select:", {k: len(v) for k, v in list(sel.items())[:6]})
+
+    # -- _max_dist_bool (prediction_locations.py:18-43) --
+    g = np.linspace(-3e5, 3e5, 25)
+    grid = np.stack([np.repeat(g, 25), np.tile(g, 25)], axis=1)
+    refs = np.array([[0.0, 0.0], [1e5, -5e4], [2.9e5, 2.9e5], [9e5, 9e5]])
+    md = {}
+    for k, ref in enumerate(refs):
+        for r in (1e5, 2e5):                                   # grid spacing 25 km: points exactly at distance r exist
+            md[f"{k}/{int(r)}"] = max_dist_bool(grid, ref, r)
+    np.savez_compressed(os.path.join(OUT, "driver_max_dist.npz"), grid=grid, refs=refs, **md)
+    print("_max_dist_bool:", {k: int(v.sum()) for k, v in md.items()})
+
+    # -- LocalExpertOI.dict_of_array_to_table (local_experts.py:691-747) as run() calls it (:1226-1237) --
+    rl = pd.Series({"x": 1.5e5, "y": -2.5e4, "t": 18326.0})
+    m = 7
+    pred = {"f*": rng.standard_normal(m), "f*_var": rng.uniform(0.1, 1, m), "y_var": rng.uniform(0.1, 1, m),
+            "f_bar": np.repeat(np.array([0]), m), "pred_loc_x": rng.uniform(-1, 1, m), "pred_loc_y": rng.uniform(-1, 1, m),
+            "pred_loc_t": np.full(m, 18326.0)}
+    run_details = {"num_obs": 412, "run_time": 1.25, "objective_value": -321.5, "parameters_optimised": True,
+                   "optimise_success": False, "model": "GPSat.models.gpflow_models.GPflowGPRModel", "device": "NVIDIA B200",
+                   "config_id": 1}
+    hypes = {"lengthscales": np.array([1.5, 2.5, 3.5]), "kernel_variance": 0.75, "likelihood_variance": 0.02,
+             "inducing_points": rng.standard_normal((4, 3))}
+    tabs = {}
+    tabs["preds"] = ns["dict_of_array_to_table"](dict(pred), ref_loc=rl, concat=True, table="preds")
+    tabs["run_details"] = ns["dict_of_array_to_table"](dict(run_details), ref_loc=rl, concat=True, table="run_details")
+    tabs["hypes"] = ns["dict_of_array_to_table"](dict(hypes), ref_loc=rl, concat=False)
+    tabs["one_d_ref"] = ns["dict_of_array_to_table"]({"kernel_variance": 0.5}, ref_loc=pd.Series({"x": 2.0}), concat=False)
+    gold = {"ref_loc": {k: float(v) for k, v in rl.items()},
+            "inputs": {"pred": {k: v.tolist() for k, v in pred.items()}, "run_details": run_details,
+                       "hypes": {k: (v.tolist() if isinstance(v, np.ndarray) else v) for k, v in hypes.items()}},
+            "tables": {grp: {k: _frame_to_json(v) for k, v in t.items()} for grp, t in tabs.items()}}
+    with open(os.path.join(OUT, "driver_tables.json"), "w") as f:
+        json.dump(gold, f)
+    for grp, t in tabs.items():
+        for k, v in t.items():
+            print("table", grp, k, list(v.columns), v.shape)
+
+
+if __name__ == "__main__" and "--driver" in __import__("sys").argv:
+    driver_functions()

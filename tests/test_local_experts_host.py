@@ -43,10 +43,11 @@ def test_prediction_coords_radius_and_fill():
 def test_tables_shape_and_index():
     ref = {"x": 1.0, "y": 2.0, "t": 3.0}
     t = dict_to_tables({"f*": np.arange(4.0), "f*_var": np.ones(4), "pred_loc_x": np.zeros(4)}, ref, "preds")
-    assert list(t) == ["preds"] and t["preds"].shape == (4, 3)
+    # the reference's layout (tests/test_driver_golden.py): a leading _dim_0 column in every table
+    assert list(t) == ["preds"] and t["preds"].shape == (4, 4) and list(t["preds"]["_dim_0"]) == [0, 1, 2, 3]
     assert t["preds"].index.names == ["x", "y", "t"] and t["preds"].index[0] == (1.0, 2.0, 3.0)
     rd = dict_to_tables({"num_obs": 7, "optimise_success": True, "model": "m"}, ref, "run_details")["run_details"]
-    assert rd.shape == (1, 3) and rd["num_obs"].iloc[0] == 7
+    assert rd.shape == (1, 4) and rd["num_obs"].iloc[0] == 7 and rd["_dim_0"].iloc[0] == 0
     h = dict_to_tables({"lengthscales": np.array([1.0, 2.0, 3.0]), "kernel_variance": 0.5}, ref)
     assert list(h["lengthscales"].columns) == ["_dim_0", "lengthscales"] and len(h["lengthscales"]) == 3
-    assert list(h["kernel_variance"].columns) == ["kernel_variance"] and len(h["kernel_variance"]) == 1
+    assert list(h["kernel_variance"].columns) == ["_dim_0", "kernel_variance"] and len(h["kernel_variance"]) == 1

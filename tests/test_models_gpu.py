@@ -300,3 +300,33 @@ def test_vectorised_driver_other_configs(built):
     assert np.all(b["likelihood_variance"]["likelihood_variance"].values == 1.0)
     with pytest.raises(NotImplementedError):
         LocalExpertOI(locs, data, data_cfg, dict(model_cfg, oi_model="B200SGPRModel")).run(device_select=True)
+
+
+def test_device_selection_equals_the_reference_functions(engine):
+    """gpsat_local_select against vectors produced by the reference's own DataLoader.local_data_select
+    (GPSat/dataloader.py:2354-2447) and _max_dist_bool (GPSat/prediction_locations.py:18-43) executed from source
+    (oracle/make_golden.py --driver): including rows exactly on the ball and on the time-window edges."""
+    import json
+    from gpsat_b200 import local_experts as le
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    g = np.load(os.path.join(gold, "driver_select.npz"))
+    cols = ["x", "y", "t"]
+    table, locs = g["data"], g["locs"]
+    for name, ls_list in json.loads(str(g["selects"])).items():
+        conds = []
+        for ls in ls_list:
+            if isinstance(ls["col"], str):
+                k = cols.index(ls["col"])
+                conds.append((0, ls["comp"], [k], [k], ls["val"]))
+            else:
+                ids = [cols.index(c) for c in ls["col"]]
+                conds.append((1, "<=", ids, ids, ls["val"]))      # the reference's ball query keeps d <= r for "<" too
+        counts, off, idx = le.select_all(engine, table, locs, conds)
+        np.testing.assert_array_equal(le.select_counts(engine, table, locs, conds), counts)
+        for e in range(len(locs)):
+            np.testing.assert_array_equal(idx[off[e]:off[e + 1]], g[f"{name}/{e}"], err_msg=f"{name}/{e}")
+    m = np.load(os.path.join(gold, "driver_max_dist.npz"))
+    for r in (100000, 200000):
+        counts, off, idx = le.select_all(engine, m["grid"], m["refs"], [(1, "<", [0, 1], [0, 1], float(r))])
+        for k in range(len(m["refs"])):
+            np.testing.assert_array_equal(idx[off[k]:off[k + 1]], np.flatnonzero(m[f"{k}/{r}"]), err_msg=f"{k}/{r}")
