@@ -76,7 +76,8 @@ struct FitDev {
   int* n_iters;
   int* status;
   LbfgsState* states;       // [S]
-  int* counters;            // [0] next expert in queue, [1] occupied slots, [2] max T, [3] evals
+  int* counters;            // [0] next expert in queue, [1] occupied slots, [2] max T, [3] evals,
+                            // [4] occupied slots whose next evaluation the precision rule runs on FP64 mma.sync
   LbfgsOptions opt;
 };
 
@@ -239,6 +240,7 @@ __global__ void fit_init_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b
     fit_begin_expert(slots[s], mems[s], f.states[s], b, f, b.order[s], ld);
     atomicAdd(&f.counters[1], 1);
     atomicMax(&f.counters[2], slots[s].T);
+    if (slots[s].Uq8_mem != nullptr && slots[s].Uq8 == nullptr) atomicAdd(&f.counters[4], 1);
   } else {
     slots[s].expert = -1;
   }
@@ -346,6 +348,7 @@ __global__ void lbfgs_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, F
   if (d.expert >= 0) {
     atomicAdd(&f.counters[1], 1);
     atomicMax(&f.counters[2], d.T);
+    if (d.Uq8_mem != nullptr && d.Uq8 == nullptr) atomicAdd(&f.counters[4], 1);
   }
 }
 

@@ -163,14 +163,14 @@ static void begin_call(Engine& g) {
 // Every product call ends here.  A bounded barrier wait of the int8 pipeline that gave up (mbar_wait in i8mma.cuh)
 // left unfinished accumulators in some tile: the call fails instead of returning them.
 static int end_call(Engine& g) {
-  CUDA_TRY(cudaMemcpyFromSymbolAsync(g.h_counters + 4, g_i8_timeout, sizeof(int), 0, cudaMemcpyDeviceToHost, g.stream));
+  CUDA_TRY(cudaMemcpyFromSymbolAsync(g.h_counters + 6, g_i8_timeout, sizeof(int), 0, cudaMemcpyDeviceToHost, g.stream));
   CUDA_TRY(cudaEventRecord(g.ev1, g.stream));
   CUDA_TRY(cudaStreamSynchronize(g.stream));
   float ms = 0.f;
   CUDA_TRY(cudaEventElapsedTime(&ms, g.ev0, g.ev1));
   g.stats.gpu_ms = ms;
   if (g.profile) prof_collect(g);
-  if (g.h_counters[4] != 0) {
+  if (g.h_counters[6] != 0) {
     const int zero = 0;
     cudaMemcpyToSymbol(g_i8_timeout, &zero, sizeof(int));
     g.i8_timeouts_seen++;

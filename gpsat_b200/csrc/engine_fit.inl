@@ -12,7 +12,7 @@ static int fit_stage(Engine& g, int mem, int64_t E, int P, int S, double* theta_
   size_t o_lml = o_pb + EP * 8, o_obj = o_lml + (size_t)E * 8;
   size_t o_tk = o_obj + (size_t)E * 8, o_pk = o_tk + EP * 4, o_nev = o_pk + EP * 4, o_nit = o_nev + (size_t)E * 4;
   size_t o_st = o_nit + (size_t)E * 4, o_tr = o_st + (size_t)E * 4, o_cnt = (o_tr + EP + 15) & ~(size_t)15;
-  if (g.bout.ensure(o_cnt + 16) || g.bstates.ensure(sizeof(LbfgsState) * S)) return 1;
+  if (g.bout.ensure(o_cnt + 32) || g.bstates.ensure(sizeof(LbfgsState) * S)) return 1;
   char* base = g.bout.as<char>();
   const bool dev = mem == GPSAT_MEM_DEVICE;
   const void* p = nullptr;
@@ -95,20 +95,21 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   SlotDesc* slots = g.bslots.as<SlotDesc>();
   const SlotMem* mems = g.bmems.as<SlotMem>();
   // counters: [0] next queue position, [1] occupied, [2] max T, [3] evaluations
-  int init_cnt[4] = {(int)std::min<int64_t>(S, E), 0, 0, 0};
+  int init_cnt[5] = {(int)std::min<int64_t>(S, E), 0, 0, 0, 0};
   CUDA_TRY(cudaMemcpyAsync(fd.counters, init_cnt, sizeof(init_cnt), cudaMemcpyHostToDevice, g.stream));
   fit_init_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(slots, mems, bd, fd, S, ld);
   g.stats.kernel_launches++;
   int evals = 0;
   for (;;) {
-    CUDA_TRY(cudaMemcpyAsync(g.h_counters, fd.counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
-    CUDA_TRY(cudaMemcpyFromSymbolAsync(g.h_counters + 4, g_i8_timeout, sizeof(int), 0, cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyAsync(g.h_counters, fd.counters, 5 * sizeof(int), cudaMemcpyDeviceToHost, g.stream));
+    CUDA_TRY(cudaMemcpyFromSymbolAsync(g.h_counters + 6, g_i8_timeout, sizeof(int), 0, cudaMemcpyDeviceToHost, g.stream));
     CUDA_TRY(cudaStreamSynchronize(g.stream));
-    const int occupied = g.h_counters[1], Tcur = g.h_counters[2];
+    const int occupied = g.h_counters[1], Tcur = g.h_counters[2], dmma_slots = g.h_counters[4];
     evals = g.h_counters[3];
-    if (occupied == 0 || g.h_counters[4] != 0) break;      // done, or an int8 pipeline time-out (end_call reports it)
+    if (occupied == 0 || g.h_counters[6] != 0) break;      // done, or an int8 pipeline time-out (end_call reports it)
     CUDA_TRY(cudaMemsetAsync(fd.counters + 1, 0, 2 * sizeof(int), g.stream));
-    if (launch_sweep(g, S, Tcur, Tcur, true)) return 1;
+    CUDA_TRY(cudaMemsetAsync(fd.counters + 4, 0, sizeof(int), g.stream));
+    if (launch_sweep(g, S, Tcur, Tcur, true, nullptr, true, dmma_slots)) return 1;
     {
       ProfScope ps(g, PROF_OPT);
       lbfgs_kernel<<<(S + 63) / 64, 64, 0, g.stream>>>(slots, mems, bd, fd, S, ld);

@@ -30,7 +30,7 @@ struct Engine {
   int device = 0;
   cudaStream_t stream = nullptr;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  int* h_counters = nullptr;          // pinned [8]: [0..3] fit counters, [4] int8-pipeline time-out flag of the last call
+  int* h_counters = nullptr;          // pinned [8]: [0..4] fit counters, [6] int8-pipeline time-out flag of the last call
   int64_t i8_timeouts_seen = 0;       // calls that failed with a time-out since the engine was created
   DevBuf bX, by, bXs, boffn, boffm, border, btheta, bmisc, bslots, bmems, bA, bside, bstates, bout, bcov, bZ, bsg;
   gpsat_stats stats{};
@@ -266,8 +266,10 @@ static void launch_i8p(Engine& g, const SlotDesc* slots, int S, int ntile) {
 }
 
 // One blocked sweep over all occupied slots.
+// dmma_slots: number of occupied slots the precision rule moved to FP64 mma.sync for this evaluation, when the caller
+// knows it (the fit loop reads it back with its counters); -1 = unknown, launch the FP64 gradient kernel regardless.
 static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, const SlotDesc* slots = nullptr,
-                        bool with_lauum = true) {
+                        bool with_lauum = true, int dmma_slots = -1) {
   if (!slots) slots = g.bslots.as<SlotDesc>();
   {
     ProfScope ps(g, PROF_DIAG);
@@ -291,7 +293,7 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, cons
       if (g.lauum_planes8) {
         lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots, 1);
         g.stats.kernel_launches++;
-        if (g.i8_rho_max > 0.0) {      // slots the precision rule took off the planes for this evaluation
+        if (g.i8_rho_max > 0.0 && dmma_slots != 0) {      // slots the precision rule took off the planes for this evaluation
           lauum_grad_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots, 1);
           g.stats.kernel_launches++;
         }

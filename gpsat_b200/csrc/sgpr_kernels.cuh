@@ -131,7 +131,7 @@ __device__ __forceinline__ void sgpr_set_theta(SgprDesc& d, SlotDesc& k, SlotDes
 }
 
 // ---- Ct[i][k] = k(x_i, z_k); column M = y_i (train) or 0; zero padding elsewhere ----------------
-template <int KIND>
+template <int KIND, int DD>
 __device__ __forceinline__ void kuf_tile(const SgprDesc& d, const double* P, int np, const double* yv, double* out,
                                          int i0, int k0, double* xi, double* zk, int tid) {
   const int D = d.D, M = d.M;
@@ -142,17 +142,25 @@ __device__ __forceinline__ void kuf_tile(const SgprDesc& d, const double* P, int
   }
   __syncthreads();
   const int c = tid & (NB - 1), k = k0 + c;
-  ColCoords<0> cc;
+  ColCoords<DD> cc;
   cc.load(zk, c, D);
-#pragma unroll 4
-  for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
-    const int i = i0 + r;
-    double v = 0.0;
-    if (i < np) {
-      if (k < M) v = d.var * kunit_of_r2<KIND>(cc.r2(xi, r, D));
-      else if (k == M && yv) v = yv[i];
+  const double var = d.var;
+  // batches of 8 rows: 8 independent exp / sqrt chains per thread, values outside the data (coordinates read as
+  // zeros) are formed and then replaced, so the batch is branch-free (same scheme as add_aug_tile_t in tiles.cuh)
+  constexpr int UB = 8, RS = GPSAT_THREADS / NB;
+#pragma unroll 1
+  for (int r0 = tid >> 7; r0 < NB; r0 += RS * UB) {
+    double v[UB];
+#pragma unroll
+    for (int u = 0; u < UB; ++u) v[u] = var * kunit_of_r2<KIND>(cc.r2(xi, r0 + RS * u, D));
+#pragma unroll
+    for (int u = 0; u < UB; ++u) {
+      const int i = i0 + r0 + RS * u;
+      double w = v[u];
+      if (k > M || i >= np) w = 0.0;
+      else if (k == M) w = yv ? yv[i] : 0.0;
+      out[(size_t)i * d.Mp + k] = w;
     }
-    out[(size_t)i * d.Mp + k] = v;
   }
 }
 
@@ -167,12 +175,17 @@ __global__ void __launch_bounds__(GPSAT_THREADS) kuf_build_kernel(const SgprDesc
   const double* P = which ? d.Xs : d.X;
   const double* yv = which ? nullptr : d.y;
   double* out = which ? d.Cts : d.Ct;
+#define KUF_CASE(K) \
+  if (d.D == 3) kuf_tile<K, 3>(d, P, np, yv, out, i0, k0, xi, zk, threadIdx.x); \
+  else kuf_tile<K, 0>(d, P, np, yv, out, i0, k0, xi, zk, threadIdx.x); \
+  break;
   switch (d.kind) {
-    case GPSAT_MATERN12: kuf_tile<GPSAT_MATERN12>(d, P, np, yv, out, i0, k0, xi, zk, threadIdx.x); break;
-    case GPSAT_MATERN32: kuf_tile<GPSAT_MATERN32>(d, P, np, yv, out, i0, k0, xi, zk, threadIdx.x); break;
-    case GPSAT_MATERN52: kuf_tile<GPSAT_MATERN52>(d, P, np, yv, out, i0, k0, xi, zk, threadIdx.x); break;
-    default: kuf_tile<GPSAT_RBF>(d, P, np, yv, out, i0, k0, xi, zk, threadIdx.x); break;
+    case GPSAT_MATERN12: KUF_CASE(GPSAT_MATERN12)
+    case GPSAT_MATERN32: KUF_CASE(GPSAT_MATERN32)
+    case GPSAT_MATERN52: KUF_CASE(GPSAT_MATERN52)
+    default: KUF_CASE(GPSAT_RBF)
   }
+#undef KUF_CASE
 }
 
 // ---- W = L^-1 (dense lower, row-major [Mp][Mp]) and optionally U = W^T from a factored slot ------

@@ -49,3 +49,44 @@ def gpr(kind, X, y, theta, Xs=None, with_grad=True):
     if rc != 0:
         raise MemoryError("ld_gpr: allocation failed")
     return float(lml.value), grad, fm, fv
+
+
+def sgpr(kind, X, y, Z, theta, Xs=None, jitter=1e-6):
+    """(elbo, f* or None, f*_var or None) of the sparse model in extended precision (``ld_sgpr``)."""
+    lib = load()
+    lib.ld_sgpr.restype = C.c_int
+    lib.ld_sgpr.argtypes = [C.c_int] * 5 + [C.c_void_p] * 5 + [C.c_double] + [C.c_void_p] * 3
+    X = np.ascontiguousarray(X, dtype=np.float64)
+    n, D = X.shape
+    y = np.ascontiguousarray(y, dtype=np.float64)
+    Z = np.ascontiguousarray(Z, dtype=np.float64)
+    theta = np.ascontiguousarray(theta, dtype=np.float64)
+    m = 0 if Xs is None else len(Xs)
+    Xs_ = np.ascontiguousarray(Xs, dtype=np.float64) if m else np.zeros((1, D))
+    elbo = C.c_double(0.0)
+    fm, fv = (np.zeros(m), np.zeros(m)) if m else (None, None)
+    p = lambda a: None if a is None else a.ctypes.data
+    rc = lib.ld_sgpr(KIND[kind], n, D, len(Z), m, p(X), p(y), p(Z), p(Xs_), p(theta), float(jitter),
+                     C.addressof(elbo), p(fm), p(fv))
+    if rc == 1:
+        return -np.inf, None, None
+    if rc != 0:
+        raise MemoryError("ld_sgpr: allocation failed")
+    return float(elbo.value), fm, fv
+
+
+def sgpr_grad_fd(kind, X, y, Z, theta, rel_step=1e-6, jitter=1e-6):
+    """d elbo / d theta by central differences of the extended-precision ELBO.  With 64-bit mantissas the
+    round-off term (eps / h) is about 1e-13 and the truncation term (h^2 times the third derivative) about 1e-12
+    relative, so the result is a reference at the 1e-10 level - two orders below what the float64 paths are
+    compared at."""
+    theta = np.asarray(theta, dtype=np.float64)
+    g = np.zeros(len(theta))
+    for p in range(len(theta)):
+        h = rel_step * theta[p]
+        tp, tm = theta.copy(), theta.copy()
+        tp[p] += h
+        tm[p] -= h
+        h2 = tp[p] - tm[p]                      # the step actually taken in float64
+        g[p] = (sgpr(kind, X, y, Z, tp, jitter=jitter)[0] - sgpr(kind, X, y, Z, tm, jitter=jitter)[0]) / h2
+    return g

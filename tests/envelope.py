@@ -82,3 +82,28 @@ def rel_errors(lml, grad, fmean, fvar, ref, theta):
                 grad=float(np.max(np.abs(grad - ref["grad"])) / np.max(np.abs(ref["grad"]))),
                 fmean=float(np.max(np.abs(fmean - ref["fmean"])) / max(np.max(np.abs(ref["fmean"])), 1e-300)),
                 fvar=float(np.max(np.abs(fvar - ref["fvar"])) / theta[D]))
+
+
+# ---- sparse GPR: what a float64 implementation attains with the 1e-6 jitter on Kuu -----------
+SGPR_CASES = (
+    dict(name="c5-shape-Matern32-n20000-M500", kind="Matern32", n=20000, M=500, theta=(4.0, 4.0, 5.0, 0.05, 0.005), c5=True),
+    dict(name="RBF-n5000-M300", kind="RBF", n=5000, M=300, theta=(2.0, 2.5, 3.0, 1.0, 1e-2), c5=False),
+    dict(name="Matern32-n2000-M200-rho1e4", kind="Matern32", n=2000, M=200, theta=(3.0, 3.5, 4.0, 1.0, 1e-4), c5=False),
+    dict(name="Matern52-n300-Z=X", kind="Matern52", n=300, M=300, theta=(2.0, 2.0, 3.0, 0.5, 0.05), c5=False),
+)
+
+
+def make_sgpr_case(c):
+    """(X, y, Z, Xs, theta) of one sparse sweep case; the c5 case is expert 0 of the bench's c5 workload."""
+    theta = np.asarray(c["theta"], dtype=np.float64)
+    if c["c5"]:
+        from gpsat_b200 import synthetic as syn
+        X, y, Xs = syn.make_expert(syn.WORKLOADS["c5"], 0, 0)
+        return X, y, syn.inducing_points(X, 0, 0, c["M"]), Xs[:M_PRED], theta
+    rng = np.random.default_rng([77, c["n"], c["M"]])
+    n = c["n"]
+    X = np.stack([rng.uniform(-6, 6, n), rng.uniform(-6, 6, n), rng.integers(-4, 5, n).astype(float)], axis=1)
+    y = _rff(rng, c["kind"], X, theta[:3], theta[3]) + np.sqrt(theta[4]) * rng.standard_normal(n)
+    Z = X[rng.permutation(n)[:c["M"]]].copy()
+    Xs = np.stack([rng.uniform(-5, 5, M_PRED), rng.uniform(-5, 5, M_PRED), np.zeros(M_PRED)], axis=1)
+    return X, y, Z, Xs, theta

@@ -252,3 +252,36 @@ def test_full_size_c5_expert(engine):
     p = sgpr.predict("Matern32", X, y, Z, theta[0], Xs)
     np.testing.assert_allclose(out["f*"], p["f*"], rtol=1e-6, atol=1e-8)
     np.testing.assert_allclose(out["f*_var"], p["f*_var"], rtol=1e-6, atol=1e-9)
+
+
+def test_sgpr_against_extended_precision(engine, golden_dir):
+    """ELBO / gradient / predictions of the sparse model against extended precision (oracle/longdouble_gpr.c ld_sgpr;
+    gradient = central differences of that ELBO; goldens: oracle/make_sgpr_envelope_golden.py), on the c5 shape
+    (n = 20 000, M = 500) and on three smaller cases with cond(Kuu + 1e-6 I) between 1e5 and 1e9.  The tolerance is a
+    finding, not a convenience: next to the CUDA path's error the goldens hold the error of the float64 LAPACK oracle
+    on the same inputs, and the CUDA path is held to max(floor, 20 x that error) with floors 1e-8 (ELBO), 1e-7
+    (gradient, predictions).  profiles/r02_sgpr_envelope.md has the measured table."""
+    import json
+    import os
+    import envelope as env
+    from gpsat_b200.engine import RaggedBatch
+    gold = np.load(os.path.join(golden_dir, "sgpr_envelope.npz"))
+    rows, bad = [], []
+    for c in env.SGPR_CASES:
+        X, y, Z, Xs, theta = env.make_sgpr_case(c)
+        b = RaggedBatch.from_lists(c["kind"], [X], [y], [Xs])
+        v, g, st = engine.sgpr_elbo(b, [Z], theta[None, :], with_grad=True)
+        p = engine.sgpr_predict(b, [Z], theta[None, :])
+        ref = {k: gold[f"{c['name']}/{k}"] for k in ("elbo", "grad", "fmean", "fvar", "f64_err", "cond_kuu")}
+        err = np.array([abs(v[0] - float(ref["elbo"])) / abs(float(ref["elbo"])),
+                        np.max(np.abs(g[0] - ref["grad"])) / np.max(np.abs(ref["grad"])),
+                        np.max(np.abs(p["f*"] - ref["fmean"])) / np.max(np.abs(ref["fmean"])),
+                        np.max(np.abs(p["f*_var"] - ref["fvar"])) / theta[3]])
+        tol = np.maximum(np.array([1e-8, 1e-7, 1e-7, 1e-7]), 20 * ref["f64_err"])
+        rows.append(dict(case=c["name"], cond_kuu=float(ref["cond_kuu"]), gpu=err.tolist(), f64_oracle=ref["f64_err"].tolist(),
+                         tol=tol.tolist(), status=int(st[0])))
+        if st[0] != 0 or np.any(err > tol):
+            bad.append(rows[-1])
+    os.makedirs("gpurun_out", exist_ok=True)
+    json.dump(rows, open(os.path.join("gpurun_out", "sgpr_envelope.json"), "w"), indent=1)
+    assert not bad, bad
