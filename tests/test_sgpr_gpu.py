@@ -257,10 +257,11 @@ def test_full_size_c5_expert(engine):
 def test_sgpr_against_extended_precision(engine, golden_dir):
     """ELBO / gradient / predictions of the sparse model against extended precision (oracle/longdouble_gpr.c ld_sgpr;
     gradient = central differences of that ELBO; goldens: oracle/make_sgpr_envelope_golden.py), on the c5 shape
-    (n = 20 000, M = 500) and on three smaller cases with cond(Kuu + 1e-6 I) between 1e5 and 1e9.  The tolerance is a
-    finding, not a convenience: next to the CUDA path's error the goldens hold the error of the float64 LAPACK oracle
-    on the same inputs, and the CUDA path is held to max(floor, 20 x that error) with floors 1e-8 (ELBO), 1e-7
-    (gradient, predictions).  profiles/r02_sgpr_envelope.md has the measured table."""
+    (n = 20 000, M = 500) and on three smaller cases with cond(Kuu + 1e-6 I) between 1e3 and 3e7.  Measured on B200
+    (profiles/r02_sgpr_envelope.md): the CUDA path is within 4e-13 (ELBO), 5e-10 (gradient) and 8e-13 (predictions) of
+    extended precision, so it is held to the north star's 1e-8 on all four quantities here.  The looser 1e-7 / 1e-6
+    of the other tests in this file is the float64 NumPy oracle's own error (its gradient is off by 5.7e-6 on the
+    RBF case, recorded in the goldens as f64_err), not the CUDA path's."""
     import json
     import os
     import envelope as env
@@ -277,7 +278,7 @@ def test_sgpr_against_extended_precision(engine, golden_dir):
                         np.max(np.abs(g[0] - ref["grad"])) / np.max(np.abs(ref["grad"])),
                         np.max(np.abs(p["f*"] - ref["fmean"])) / np.max(np.abs(ref["fmean"])),
                         np.max(np.abs(p["f*_var"] - ref["fvar"])) / theta[3]])
-        tol = np.maximum(np.array([1e-8, 1e-7, 1e-7, 1e-7]), 20 * ref["f64_err"])
+        tol = np.full(4, 1e-8)
         rows.append(dict(case=c["name"], cond_kuu=float(ref["cond_kuu"]), gpu=err.tolist(), f64_oracle=ref["f64_err"].tolist(),
                          tol=tol.tolist(), status=int(st[0])))
         if st[0] != 0 or np.any(err > tol):
