@@ -24,6 +24,7 @@
 #include "lauum_kernel.cuh"
 #include "i8mma.cuh"
 #include "step_kernel.cuh"
+#include "lauum_q_kernel.cuh"
 
 namespace gpsat {
 

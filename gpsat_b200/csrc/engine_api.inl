@@ -18,8 +18,9 @@ int gpsat_engine_set_profile(gpsat_engine* h, int on) {
 
 int gpsat_engine_set_lauum_path(gpsat_engine* h, int path) {
   REQUIRE(h != nullptr, "engine is NULL");
-  REQUIRE(path == GPSAT_LAUUM_DMMA || path == GPSAT_LAUUM_I8, "unknown lauum path");
-  h->e.i8_lauum = path == GPSAT_LAUUM_I8;
+  REQUIRE(path == GPSAT_LAUUM_DMMA || path == GPSAT_LAUUM_I8 || path == GPSAT_LAUUM_I8Q, "unknown lauum path");
+  h->e.i8_lauum = path != GPSAT_LAUUM_DMMA;
+  h->e.i8_lauum_q = path == GPSAT_LAUUM_I8Q;
   return 0;
 }
 
@@ -114,6 +115,7 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
   if (const char* lp = getenv("GPSAT_B200_LAUUM")) {
     h->e.i8_lauum = strcmp(lp, "dmma") != 0;
     h->e.i8_persistent = strcmp(lp, "i8p") == 0;
+    h->e.i8_lauum_q = strcmp(lp, "i8") != 0 && strcmp(lp, "i8p") != 0;
   }
   if (const char* sp = getenv("GPSAT_B200_STEP")) h->e.i8_step = strcmp(sp, "dmma") != 0;
   if (const char* dp = getenv("GPSAT_B200_DIAGSUM")) h->e.i8_diag_sum = strcmp(dp, "0") != 0;
@@ -130,7 +132,7 @@ int gpsat_engine_destroy(gpsat_engine* h) {
   cudaStreamSynchronize(g.stream);
   for (cudaEvent_t ev : g.evpool) cudaEventDestroy(ev);
   for (DevBuf* b : {&g.bX, &g.by, &g.bXs, &g.boffn, &g.boffm, &g.border, &g.btheta, &g.bmisc, &g.bslots,
-                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov, &g.bZ, &g.bsg, &g.bUq, &g.bLq, &g.bUq8, &g.bynorm})
+                    &g.bmems, &g.bA, &g.bside, &g.bstates, &g.bout, &g.bcov, &g.bZ, &g.bsg, &g.bUq, &g.bLq, &g.bUq8, &g.bynorm, &g.bQ})
     b->release();
   if (g.h_counters) cudaFreeHost(g.h_counters);
   cudaEventDestroy(g.ev0); cudaEventDestroy(g.ev1);

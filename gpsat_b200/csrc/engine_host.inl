@@ -41,7 +41,10 @@ struct Engine {
   // optional per-kernel timing (gpsat_engine_set_profile)
   // K^-1 tile products of the gradient on the int8 tensor path (i8mma.cuh); GPSAT_B200_LAUUM=dmma turns it off
   bool i8_lauum = true;
-  bool i8_persistent = false;       // GPSAT_B200_LAUUM=i8p: warp-specialised persistent variant (experimental, slower so far)
+  bool i8_persistent = false;       // GPSAT_B200_LAUUM=i8p: first persistent variant (register epilogue; slower, kept for reference)
+  bool i8_lauum_q = true;           // persistent variant with the Q tile parked in an L2-resident scratch (lauum_q_kernel.cuh);
+                                    // GPSAT_B200_LAUUM=i8 selects the one-CTA-per-tile kernel instead
+  DevBuf bQ;                        // its scratch: one FP64 tile per CTA
   int num_sms = 148;
   int cur_kind = GPSAT_MATERN32, cur_D = 3;     // kernel family / input dimension of the loaded batch
   DevBuf bUq;
@@ -98,6 +101,7 @@ static int engine_setup_kernels() {
   CUDA_TRY(cudaFuncSetAttribute(step_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, STEP_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_i8_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_I8_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(lauum_grad_i8q_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_I8Q_SMEM_BYTES));
 #define I8P_ATTR(K) \
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_i8p_kernel<K, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_I8P_SMEM_BYTES)); \
   CUDA_TRY(cudaFuncSetAttribute(lauum_grad_i8p_kernel<K, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, LAUUM_I8P_SMEM_BYTES));
@@ -291,7 +295,13 @@ static int launch_sweep(Engine& g, int S, int Tmax, int TRmax, bool do_inv, cons
     const int ntile = Tmax * (Tmax + 1) / 2;
     if (g.i8_lauum) {
       if (g.lauum_planes8) {
-        lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots, 1);
+        if (g.i8_lauum_q) {
+          const int grid = std::min(g.num_sms, ntile * S);
+          if (g.bQ.ensure((size_t)g.num_sms * I8Q_SCRATCH_D * sizeof(double))) return 1;
+          lauum_grad_i8q_kernel<<<grid, I8Q_THREADS, LAUUM_I8Q_SMEM_BYTES, g.stream>>>(slots, S, ntile, g.bQ.as<double>());
+        } else {
+          lauum_grad_i8_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_I8_SMEM_BYTES, g.stream>>>(slots, 1);
+        }
         g.stats.kernel_launches++;
         if (g.i8_rho_max > 0.0 && dmma_slots != 0) {      // slots the precision rule took off the planes for this evaluation
           lauum_grad_kernel<<<dim3(ntile, S), GPSAT_THREADS, LAUUM_SMEM_BYTES, g.stream>>>(slots, 1);

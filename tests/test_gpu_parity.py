@@ -388,7 +388,7 @@ def test_i8_gradient_path_matches_dmma_path(engine, kind, D):
         engine.set_lauum_path("i8")
         lml1, g1, st1 = engine.lml_grad(b, theta)
     finally:
-        engine.set_lauum_path("i8")
+        engine.set_lauum_path("i8q")
     assert engine.i8_timeouts() == t0
     assert np.all(st0 == 0) and np.all(st1 == 0)
     np.testing.assert_array_equal(lml0, lml1)                  # the factorisation is the same code
@@ -458,6 +458,36 @@ def test_i8_step_path_matches_dmma_path(engine, kind, D, noise):
             np.testing.assert_allclose(p_["f*_var"][sl], pr["f*_var"], rtol=tol, atol=tol * theta[e][D])
         tol = 1e-6 if loose else 1e-8
         np.testing.assert_allclose(p1["f*"][sl], p0["f*"][sl], rtol=tol / 10, atol=tol / 10 * np.abs(pr["f*"]).max())
+
+
+def test_persistent_lauum_is_bitwise_equal(engine):
+    """lauum_grad_i8q_kernel (persistent, warp-specialised, Q tile through an L2-resident scratch: the default) against
+    lauum_grad_i8_kernel (one CTA per tile): the same arithmetic, so LML and gradient must agree bit for bit - ragged
+    sizes from one to eleven tile rows, more tiles than SMs, a slot the precision rule sends to FP64 mma.sync, and a
+    slot with 8 planes (var > 255 noise)."""
+    rng = np.random.default_rng(4242)
+    ns = [1, 100, 128, 129, 257, 383, 640, 1000, 1300] + [520] * 30
+    experts = [_expert(rng, n, 3) for n in ns]
+    b = _batch("Matern32", experts, with_pred=False)
+    theta = np.stack([_theta(rng, 3) for _ in ns])
+    theta[5, 3:] = [1.0, 1e-4]          # rho = 1e4: FP64 path by the precision rule
+    theta[6, 3:] = [1.5, 2e-3]          # rho = 750: 8 planes in the K^-1 products
+    t0 = engine.i8_timeouts()
+    try:
+        engine.set_lauum_path("i8")
+        lml0, g0, st0 = engine.lml_grad(b, theta)
+        engine.set_lauum_path("i8q")
+        lml1, g1, st1 = engine.lml_grad(b, theta)
+        lml2, g2, st2 = engine.lml_grad(b, theta)
+    finally:
+        engine.set_lauum_path("i8q")
+    assert engine.i8_timeouts() == t0
+    assert np.all(st0 == 0) and np.all(st1 == 0)
+    np.testing.assert_array_equal(lml0, lml1)
+    np.testing.assert_array_equal(g0, g1)
+    np.testing.assert_array_equal(g1, g2)              # and repeatable
+    v, g = gpr.lml_and_grad("Matern32", experts[7][0], experts[7][1], theta[7])
+    np.testing.assert_allclose(g1[7], g, rtol=1e-7, atol=1e-8 * np.abs(g).max())
 
 
 def _envelope_run(engine, cases, items, kind):
