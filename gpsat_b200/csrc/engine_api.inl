@@ -115,7 +115,7 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
   if (const char* lp = getenv("GPSAT_B200_LAUUM")) {
     h->e.i8_lauum = strcmp(lp, "dmma") != 0;
     h->e.i8_persistent = strcmp(lp, "i8p") == 0;
-    h->e.i8_lauum_q = strcmp(lp, "i8") != 0 && strcmp(lp, "i8p") != 0;
+    h->e.i8_lauum_q = strcmp(lp, "i8q") == 0;
   }
   if (const char* sp = getenv("GPSAT_B200_STEP")) h->e.i8_step = strcmp(sp, "dmma") != 0;
   if (const char* dp = getenv("GPSAT_B200_DIAGSUM")) h->e.i8_diag_sum = strcmp(dp, "0") != 0;

@@ -42,8 +42,8 @@ struct Engine {
   // K^-1 tile products of the gradient on the int8 tensor path (i8mma.cuh); GPSAT_B200_LAUUM=dmma turns it off
   bool i8_lauum = true;
   bool i8_persistent = false;       // GPSAT_B200_LAUUM=i8p: first persistent variant (register epilogue; slower, kept for reference)
-  bool i8_lauum_q = true;           // persistent variant with the Q tile parked in an L2-resident scratch (lauum_q_kernel.cuh);
-                                    // GPSAT_B200_LAUUM=i8 selects the one-CTA-per-tile kernel instead
+  bool i8_lauum_q = false;          // GPSAT_B200_LAUUM=i8q: persistent variant with the Q tile parked in an L2-resident scratch
+                                    // (lauum_q_kernel.cuh): bitwise the same results, measured 11 % slower at c2
   DevBuf bQ;                        // its scratch: one FP64 tile per CTA
   int num_sms = 148;
   int cur_kind = GPSAT_MATERN32, cur_D = 3;     // kernel family / input dimension of the loaded batch

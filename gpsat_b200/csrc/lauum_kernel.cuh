@@ -31,14 +31,25 @@ __device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c,
     // interior off-diagonal tile: every element counts twice, no bounds, no diagonal.  Batches of 4 rows keep 4
     // independent exp / sqrt chains in flight per thread.
     constexpr int UB = 4, RS = GPSAT_THREADS / NB;
+    // the Q values of the next batch are fetched before the current batch is evaluated: with the tile in shared memory
+    // that costs four registers, with the tile in the L2-resident scratch of lauum_grad_i8q_kernel it hides the latency
+    double qn[UB];
+#pragma unroll
+    for (int u = 0; u < UB; ++u) qn[u] = Cs[((tid >> 7) + RS * u) * LDC + c];
 #pragma unroll 1
     for (int r0 = tid >> 7; r0 < NB; r0 += RS * UB) {
-      double wq[UB], sd[UB][ND], ku[UB], gu[UB];
+      double wq[UB], sd[UB][ND], ku[UB], gu[UB], qv[UB];
+#pragma unroll
+      for (int u = 0; u < UB; ++u) qv[u] = qn[u];
+      if (r0 + RS * UB < NB) {
+#pragma unroll
+        for (int u = 0; u < UB; ++u) qn[u] = Cs[(r0 + RS * UB + RS * u) * LDC + c];
+      }
 #pragma unroll
       for (int u = 0; u < UB; ++u) {
         const int r = r0 + RS * u;
         const double aa = ar[r] * acv;
-        wq[u] = 2.0 * (aa - (Cs[r * LDC + c] - aac * aa));
+        wq[u] = 2.0 * (aa - (qv[u] - aac * aa));
         double r2 = 0.0;
 #pragma unroll
         for (int dd = 0; dd < ND; ++dd) {
@@ -65,14 +76,16 @@ __device__ __forceinline__ void grad_tile_t(const SlotDesc& d, int g0r, int g0c,
     for (int r0 = tid >> 7; r0 < NB; r0 += RS * UB) {
       if (g0r + r0 >= n) break;
       if (g0r + r0 + RS * (UB - 1) < wc0) continue;
-      double wq[UB], qd[UB], sd[UB][ND], ku[UB], gu[UB];
+      double wq[UB], qd[UB], sd[UB][ND], ku[UB], gu[UB], qv[UB];
+#pragma unroll
+      for (int u = 0; u < UB; ++u) qv[u] = Cs[(r0 + RS * u) * LDC + c];       // four loads in flight before the first use
 #pragma unroll
       for (int u = 0; u < UB; ++u) {
         const int r = r0 + RS * u, gi = g0r + r;
         const bool live = gi < n && gj <= gi;
         const double aa = ar[r] * acv;
         // aac = 1: the tile holds Ks^-1 + alpha alpha^T (column n of U is -alpha); aac = 0: Ks^-1 alone
-        const double q = aa - (Cs[r * LDC + c] - aac * aa);
+        const double q = aa - (qv[u] - aac * aa);
         wq[u] = live ? ((gi == gj) ? q : 2.0 * q) : 0.0;
         qd[u] = (live && gi == gj) ? q : 0.0;
         double r2 = 0.0;

@@ -10,6 +10,10 @@
 // straight from registers; its fully unrolled 64-column epilogue was instruction-fetch bound.)  The arithmetic is that
 // of lauum_grad_i8_kernel operation for operation, so the gradient partial sums are bitwise identical
 // (tests/test_gpu_parity.py::test_persistent_lauum_is_bitwise_equal).
+// Measured at c2 (profiles/README.md r02h): 149.6 ms of LAUUM per bench step against 134.4 ms for the one-CTA-per-tile kernel -
+// the round trip of the Q tile through L2 (uncoalesced 16-byte row stores, reads at L2 latency) keeps the eight drain /
+// reduce warps busy for ~22 us per tile, longer than the 7.5 us of pass-0 MMAs they are meant to hide behind, so the MMA
+// warp waits for them.  Not the default; selectable with GPSAT_B200_LAUUM=i8q / GPSAT_LAUUM_I8Q.
 #pragma once
 #include "i8slice.cuh"
 

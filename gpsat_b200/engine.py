@@ -163,7 +163,7 @@ class Engine:
         _lib.check(self._lib.gpsat_engine_set_profile(self._h, int(bool(on))))
 
     def set_lauum_path(self, path: str):
-        """``"i8q"`` (default, persistent kernel) / ``"i8"`` (one CTA per tile; bitwise the same results): K^-1 tile
+        """``"i8"`` (default, one CTA per tile) / ``"i8q"`` (persistent kernel; bitwise the same results): K^-1 tile
         products of the gradient by error-free int8 slicing on the tcgen05 tensor path; ``"dmma"``: FP64 ``mma.sync``.  The int8 slices are taken against a-priori
         bounds, so they match FP64 only while (var + noise) / noise stays moderate: see
         :meth:`set_precision_rule` (on by default) and ``profiles/r02_precision_envelope.md``."""

@@ -132,12 +132,12 @@ void* gpsat_engine_stream(const gpsat_engine* eng);
 int gpsat_engine_set_profile(gpsat_engine* eng, int on);
 /* How the K^-1 tile products of the gradient (the LAUUM piece of the sweep, the inverse GPflow's
  * autodiff forms implicitly at gpflow_models.py:317-321) are evaluated:
- *   GPSAT_LAUUM_I8 / GPSAT_LAUUM_I8Q (default)  error-free int8 slicing on the tcgen05 tensor path
+ *   GPSAT_LAUUM_I8 (default) / GPSAT_LAUUM_I8Q  error-free int8 slicing on the tcgen05 tensor path
  *   GPSAT_LAUUM_DMMA FP64 mma.sync
  * The environment variable GPSAT_B200_LAUUM=dmma selects the second at engine creation. */
 #define GPSAT_LAUUM_DMMA 0
-#define GPSAT_LAUUM_I8 1             /* one CTA per tile */
-#define GPSAT_LAUUM_I8Q 2            /* default: persistent, warp-specialised; same arithmetic, bitwise the same results */
+#define GPSAT_LAUUM_I8 1             /* default: one CTA per tile */
+#define GPSAT_LAUUM_I8Q 2            /* persistent, warp-specialised; same arithmetic, bitwise the same results (slower so far) */
 int gpsat_engine_set_lauum_path(gpsat_engine* eng, int path);
 /* How the potrf tiles of the sweep (the Cholesky GPflow runs inside GPR.log_marginal_likelihood / predict_f,
  * gpflow_models.py:229-230, 337) accumulate sum_k L_rk L_ik^T:

@@ -388,7 +388,7 @@ def test_i8_gradient_path_matches_dmma_path(engine, kind, D):
         engine.set_lauum_path("i8")
         lml1, g1, st1 = engine.lml_grad(b, theta)
     finally:
-        engine.set_lauum_path("i8q")
+        engine.set_lauum_path("i8")
     assert engine.i8_timeouts() == t0
     assert np.all(st0 == 0) and np.all(st1 == 0)
     np.testing.assert_array_equal(lml0, lml1)                  # the factorisation is the same code
@@ -461,8 +461,8 @@ def test_i8_step_path_matches_dmma_path(engine, kind, D, noise):
 
 
 def test_persistent_lauum_is_bitwise_equal(engine):
-    """lauum_grad_i8q_kernel (persistent, warp-specialised, Q tile through an L2-resident scratch: the default) against
-    lauum_grad_i8_kernel (one CTA per tile): the same arithmetic, so LML and gradient must agree bit for bit - ragged
+    """lauum_grad_i8q_kernel (persistent, warp-specialised, Q tile through an L2-resident scratch; GPSAT_LAUUM_I8Q)
+    against lauum_grad_i8_kernel (one CTA per tile, the default): the same arithmetic, so LML and gradient must agree bit for bit - ragged
     sizes from one to eleven tile rows, more tiles than SMs, a slot the precision rule sends to FP64 mma.sync, and a
     slot with 8 planes (var > 255 noise)."""
     rng = np.random.default_rng(4242)
@@ -480,7 +480,7 @@ def test_persistent_lauum_is_bitwise_equal(engine):
         lml1, g1, st1 = engine.lml_grad(b, theta)
         lml2, g2, st2 = engine.lml_grad(b, theta)
     finally:
-        engine.set_lauum_path("i8q")
+        engine.set_lauum_path("i8")
     assert engine.i8_timeouts() == t0
     assert np.all(st0 == 0) and np.all(st1 == 0)
     np.testing.assert_array_equal(lml0, lml1)
