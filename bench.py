@@ -14,7 +14,8 @@ generates and uploads only its shard, runs independently, and rank 0 gathers the
 step: weak scaling (per-GPU work fixed), no collective on the hot path.
 Every default line also carries `extra.ns2048_strong`: the north-star pass - 2048 experts x 2000 observations,
 fit + predict - strong-scaled over the same N ranks through the same partitioner; at N = 1 `extra` adds short
-runs of the other BASELINE.json configs (c1, c3, c4 predict-only, c5 sparse GPR).
+runs of the other BASELINE.json configs (c1, c3, c4 predict-only, c5 sparse GPR), at N >= 4 the full-size c3 set
+(3 000 experts x 2 000-4 000 observations) strong-scaled.
 
 Workloads: c1 c2 c3 ns = exact GPR fit + predict; c4 = predict only at fixed hyper-parameters
 (GPSat/postprocessing.py:365-395); c5 = GPflowSGPRModel shape, n = 20 000, M = 500 (gpflow_models.py:704).
@@ -545,6 +546,8 @@ def run_ours(args):
     if default_run and not args.no_extra:
         job.close()
         extra = {"ns2048_strong": run_extra("ns", syn.WORKLOADS["ns"], world, rank, local, dist, flush)}
+        if world >= 4:      # BASELINE.json configs[2] at full size: ~3k experts x 2-4k observations (a few seconds per pass)
+            extra["c3_3000_strong"] = run_extra("c3", syn.WORKLOADS["c3"], world, rank, local, dist, flush)
         if world == 1:
             extra["c3_96"] = run_extra("c3", replace(syn.WORKLOADS["c3"], E=96), world, rank, local, dist, flush)
             extra["c4_96_predict_only"] = run_extra("c4", replace(syn.WORKLOADS["c4"], E=96), world, rank, local, dist, flush, passes=3)
