@@ -97,7 +97,7 @@ static int sgpr_setup(Engine& g, const gpsat_batch* batch, const int64_t* off_z,
 // One evaluation of every occupied slot: ELBO by-products, optionally the gradient partial sums
 // and / or the prediction reductions.
 static int sgpr_launch_eval(Engine& g, const SgprCall& c, bool with_grad, bool with_pred, double* dfm, double* dfv,
-                            double* dyv) {
+                            double* dyv, const int64_t* doffc = nullptr, double* dcov = nullptr, int64_t mmax = 0) {
   const int S = c.S, MT = c.Mp / NB, ntl = MT * (MT + 1) / 2, NT = c.npad / NB, PT = c.mpad / NB;
   const unsigned T32 = c.Mp / 32;
   cudaStream_t st = g.stream;
@@ -140,6 +140,11 @@ static int sgpr_launch_eval(Engine& g, const SgprCall& c, bool with_grad, bool w
     sgpr_predict_reduce_kernel<<<dim3((unsigned)((c.mpad * 32 + 255) / 256), S), 256, 0, st>>>(dd, c.sb, c.bd.off_m, dfm,
                                                                                              dfv, dyv);
     g.stats.kernel_launches += 2;
+    if (dcov && mmax > 0) {
+      const unsigned nt = (unsigned)((mmax + 63) / 64);
+      sgpr_predict_cov_kernel<<<dim3(nt, nt, S), 256, 0, st>>>(dd, doffc, dcov);
+      g.stats.kernel_launches++;
+    }
   }
   g.stats.ticks++;
   return 0;
@@ -155,7 +160,7 @@ static double sgpr_flops(const Engine& g, const int64_t* off_z, int64_t e, bool 
 
 static int sgpr_eval_impl(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,
                           const double* theta, bool with_pred, double* fmean, double* fvar, double* yvar,
-                          double* elbo, double* grad, int32_t* status) {
+                          double* elbo, double* grad, int32_t* status, double* fcov = nullptr) {
   REQUIRE(h != nullptr, "engine is NULL");
   if (check_batch(batch, with_pred)) return 2;
   REQUIRE(theta != nullptr && off_z != nullptr, "theta / off_z is NULL");
@@ -185,10 +190,28 @@ static int sgpr_eval_impl(gpsat_engine* h, const gpsat_batch* batch, const int64
   double* dfv = dev ? fvar : dfm + Mtot;
   double* dyv = dev ? yvar : dfv + Mtot;
   const int S = c.S;
+  // full covariance blocks: expert e owns m_e x m_e doubles at off_c[e] (as gpsat_gpr_predict_cov)
+  double* dcov = nullptr;
+  int64_t* doffc = nullptr;
+  int64_t ctotal = 0, mmax = 0;
+  if (fcov && with_pred) {
+    std::vector<int64_t> offc(E + 1, 0);
+    for (int64_t e = 0; e < E; ++e) { offc[e + 1] = offc[e] + g.hm[e] * g.hm[e]; mmax = std::max(mmax, g.hm[e]); }
+    ctotal = offc[E];
+    if (g.bmisc.ensure((E + 1) * 8)) return 1;
+    doffc = g.bmisc.as<int64_t>();
+    CUDA_TRY(cudaMemcpyAsync(doffc, offc.data(), (E + 1) * 8, cudaMemcpyHostToDevice, g.stream));
+    CUDA_TRY(cudaStreamSynchronize(g.stream));    // offc is a stack-lifetime source
+    if (dev) dcov = fcov;
+    else {
+      if (g.bcov.ensure(std::max<int64_t>(ctotal, 1) * 8)) return 1;
+      dcov = g.bcov.as<double>();
+    }
+  }
   for (int64_t b0 = 0; b0 < E; b0 += S) {
     sgpr_eval_init_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(c.descs, c.sk, c.sb, c.ws, c.L, c.bd, c.in,
                                                                  (const double*)dtheta, (int)b0, S, with_pred ? 1 : 0);
-    if (sgpr_launch_eval(g, c, with_grad, with_pred, dfm, dfv, dyv)) return 1;
+    if (sgpr_launch_eval(g, c, with_grad, with_pred, dfm, dfv, dyv, doffc, dcov, mmax)) return 1;
     sgpr_eval_finish_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(c.descs, c.sk, c.sb, c.bd, delbo, dgrad, dstatus, S);
     g.stats.kernel_launches += 2;
   }
@@ -203,7 +226,8 @@ static int sgpr_eval_impl(gpsat_engine* h, const gpsat_batch* batch, const int64
     if (elbo) CUDA_TRY(cudaMemcpyAsync(elbo, delbo, (size_t)E * 8, cudaMemcpyDeviceToHost, g.stream));
     if (grad) CUDA_TRY(cudaMemcpyAsync(grad, dgrad, EP * 8, cudaMemcpyDeviceToHost, g.stream));
     if (status) CUDA_TRY(cudaMemcpyAsync(status, dstatus, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
-    g.stats.d2h_bytes += (double)Mtot * 24 + (double)E * 12 + (grad ? (double)EP * 8 : 0.0);
+    if (dcov && ctotal > 0) CUDA_TRY(cudaMemcpyAsync(fcov, dcov, (size_t)ctotal * 8, cudaMemcpyDeviceToHost, g.stream));
+    g.stats.d2h_bytes += (double)Mtot * 24 + (double)E * 12 + (grad ? (double)EP * 8 : 0.0) + (dcov ? (double)ctotal * 8 : 0.0);
   }
   CUDA_TRY(cudaGetLastError());
   return end_call(g);
@@ -219,6 +243,13 @@ int gpsat_sgpr_elbo(gpsat_engine* h, const gpsat_batch* batch, const int64_t* of
 int gpsat_sgpr_predict(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,
                        const double* theta, double* fmean, double* fvar, double* yvar, double* elbo, int32_t* status) {
   return sgpr_eval_impl(h, batch, off_z, Z, mem, theta, true, fmean, fvar, yvar, elbo, nullptr, status);
+}
+
+int gpsat_sgpr_predict_cov(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,
+                           const double* theta, double* fmean, double* fvar, double* yvar, double* fcov, double* elbo,
+                           int32_t* status) {
+  REQUIRE(fcov != nullptr, "fcov is NULL");
+  return sgpr_eval_impl(h, batch, off_z, Z, mem, theta, true, fmean, fvar, yvar, elbo, nullptr, status, fcov);
 }
 
 int gpsat_sgpr_fit(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,

@@ -671,4 +671,66 @@ __global__ void sgpr_predict_reduce_kernel(const SgprDesc* __restrict__ descs, c
   }
 }
 
+// sgpr_predict_cov_kernel: full posterior covariance of the prediction points of one slot (SGPR.predict_f with
+// full_cov = True, reached through GPflowSGPRModel.predict(full_cov=True), gpflow_models.py:229-230, 245-263):
+//   cov[s][t] = k(xs_s, xs_t) - <T1_s, T1_t> + <T2_s, T2_t>,  T1 = Kus^T L^-T, T2 = T1 LB^-T  (rows of d.T1 / d.T2, columns < M)
+// written as a dense m x m block at fcov + off_c[expert].  64 x 64 output tile per CTA, 4 x 4 per thread, plain DFMA:
+// an occasional diagnostic output like predict_cov_kernel, not part of the timed hot path.
+__global__ void __launch_bounds__(256) sgpr_predict_cov_kernel(const SgprDesc* __restrict__ descs,
+                                                               const int64_t* __restrict__ off_c, double* __restrict__ fcov) {
+  const SgprDesc& d = descs[blockIdx.z];
+  if (d.expert < 0) return;
+  const int m = d.m, M = d.M, D = d.D, Mp = d.Mp;
+  const int s0 = blockIdx.y * 64, t0 = blockIdx.x * 64;
+  if (s0 >= m || t0 >= m || t0 > s0) return;          // lower tiles; mirrored on store
+  __shared__ double A1[64][17], B1[64][17], A2[64][17], B2[64][17];
+  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+  double acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+  for (int k0 = 0; k0 < M; k0 += 16) {
+    for (int idx = tid; idx < 64 * 16; idx += 256) {
+      const int r = idx >> 4, k = idx & 15;
+      const bool ka = k0 + k < M;
+      const bool ra = s0 + r < m && ka, rb = t0 + r < m && ka;
+      A1[r][k] = ra ? d.T1[(size_t)(s0 + r) * Mp + k0 + k] : 0.0;
+      A2[r][k] = ra ? d.T2[(size_t)(s0 + r) * Mp + k0 + k] : 0.0;
+      B1[r][k] = rb ? d.T1[(size_t)(t0 + r) * Mp + k0 + k] : 0.0;
+      B2[r][k] = rb ? d.T2[(size_t)(t0 + r) * Mp + k0 + k] : 0.0;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+      double a1[4], a2[4], b1[4], b2[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) { a1[a] = A1[ty * 4 + a][k]; a2[a] = A2[ty * 4 + a][k]; }
+#pragma unroll
+      for (int b = 0; b < 4; ++b) { b1[b] = B1[tx * 4 + b][k]; b2[b] = B2[tx * 4 + b][k]; }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = fma(a2[a], b2[b], fma(-a1[a], b1[b], acc[a][b]));
+    }
+    __syncthreads();
+  }
+  double* out = fcov + off_c[d.expert];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) {
+      const int s = s0 + ty * 4 + a, t = t0 + tx * 4 + b;
+      if (s >= m || t >= m || t > s) continue;
+      double r2 = 0.0;
+      for (int dd = 0; dd < D; ++dd) {
+        const double df = (d.Xs[(size_t)s * D + dd] - d.Xs[(size_t)t * D + dd]) * d.inv_ls[dd];
+        r2 += df * df;
+      }
+      const double v = d.var * kunit_dyn(d.kind, r2) + acc[a][b];
+      out[(size_t)s * m + t] = v;
+      out[(size_t)t * m + s] = v;
+    }
+}
+
 }  // namespace gpsat

@@ -353,8 +353,9 @@ class Engine:
                                              _ptr(grad), _ptr(status)))
         return elbo, grad, status
 
-    def sgpr_predict(self, batch: RaggedBatch, Z, theta):
-        """``SGPR.predict_f`` / ``predict_y`` (full_cov=False) per expert at fixed theta."""
+    def sgpr_predict(self, batch: RaggedBatch, Z, theta, full_cov: bool = False):
+        """``SGPR.predict_f`` / ``predict_y`` per expert at fixed theta; ``full_cov`` adds ``"f*_cov"``: one dense
+        [m_e, m_e] block per expert (``gpsat_sgpr_predict_cov``)."""
         E, P = batch.E, batch.D + 2
         mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
         M = int(batch.off_m[-1])
@@ -365,6 +366,14 @@ class Engine:
         status = self._empty(batch, (E,), np.int32)
         cb = batch._c(True)
         self._pre(batch)
+        if full_cov:
+            msz = batch.m.astype(np.int64)
+            off_c = np.concatenate([[0], np.cumsum(msz * msz)])
+            cov = self._empty(batch, (int(off_c[-1]),), np.float64)
+            _lib.check(self._lib.gpsat_sgpr_predict_cov(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, _ptr(th), _ptr(fm),
+                                                        _ptr(fv), _ptr(yv), _ptr(cov), _ptr(elbo), _ptr(status)))
+            blocks = [cov[int(off_c[e]):int(off_c[e + 1])].reshape(int(msz[e]), int(msz[e])) for e in range(E)]
+            return {"f*": fm, "f*_var": fv, "y_var": yv, "f*_cov": blocks, "elbo": elbo, "status": status}
         _lib.check(self._lib.gpsat_sgpr_predict(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, _ptr(th), _ptr(fm),
                                                 _ptr(fv), _ptr(yv), _ptr(elbo), _ptr(status)))
         return {"f*": fm, "f*_var": fv, "y_var": yv, "elbo": elbo, "status": status}

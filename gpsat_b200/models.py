@@ -533,7 +533,7 @@ class B200SGPRModel(B200GPRModel):
     (``:860-862``), ``predict`` is the parent's (``predict_f`` / ``predict_y`` of the sparse model)
     and ``param_names`` gains "inducing_points".  ``optimise_parameters(train_inducing_points=True)``
     is not implemented: the device optimiser keeps Z fixed, which is the reference's default
-    (``:896-897``).  ``full_cov=True`` is not available for the sparse model.
+    (``:896-897``).
     """
 
     def __init__(self, data=None, coords_col=None, obs_col=None, coords=None, obs=None, coords_scale=None,
@@ -572,13 +572,20 @@ class B200SGPRModel(B200GPRModel):
         self.inducing_points = Z.copy()
 
     def predict(self, coords, full_cov=False, apply_scale=True) -> Dict[str, np.ndarray]:
-        if full_cov:
-            raise NotImplementedError("full_cov=True is not implemented for the sparse model")
         Xs = self._prep_pred_coords(coords, apply_scale)
-        out = self.engine.sgpr_predict(self._batch(Xs), self._inducing_list(), self._theta[None, :])
+        out = self.engine.sgpr_predict(self._batch(Xs), self._inducing_list(), self._theta[None, :], full_cov=full_cov)
         if int(out["status"][0]) != _lib.STATUS_OK:
             raise FloatingPointError("Kuu + jitter * I or B is not positive definite at the current parameters")
-        return {"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"], "f_bar": self._f_bar(len(out["f*"]))}
+        res = {"f*": out["f*"], "f*_var": out["f*_var"], "y_var": out["y_var"]}
+        if full_cov:                                  # same keys as the exact model (gpflow_models.py:245-263)
+            f_cov = out["f*_cov"][0]
+            y_cov = f_cov.copy()
+            y_cov[np.diag_indices(len(y_cov))] += res["y_var"] - res["f*_var"]
+            res["f*_var"] = np.diag(f_cov).copy()
+            res["f*_cov"] = f_cov
+            res["y_cov"] = y_cov
+        res["f_bar"] = self._f_bar(len(res["f*"]))
+        return res
 
     def optimise_parameters(self, train_inducing_points=False, max_iter=10_000, fixed_params=None, **opt_kwargs):
         if train_inducing_points:

@@ -221,6 +221,13 @@ int gpsat_sgpr_predict(gpsat_engine* eng, const gpsat_batch* batch, const int64_
                        int mem, const double* theta, double* fmean, double* fvar, double* yvar,
                        double* elbo, int32_t* status);
 
+/* Same, plus the full posterior covariance of every expert's prediction points (SGPR.predict_f(full_cov=True), reached
+ * through GPflowSGPRModel.predict(full_cov=True), gpflow_models.py:230, 245-263): expert e owns a dense row-major
+ * m_e x m_e block at fcov + sum_{e' < e} m_e'^2.  y_cov = f_cov + likelihood_variance * I. */
+int gpsat_sgpr_predict_cov(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,
+                           int mem, const double* theta, double* fmean, double* fvar, double* yvar, double* fcov,
+                           double* elbo, int32_t* status);
+
 /* Replaces GPflowSGPRModel.optimise_parameters (gpflow_models.py:290-329 inherited: L-BFGS-B on
  * training_loss = -elbo, inducing points fixed, :896-897) for all experts.  Arguments as
  * gpsat_gpr_fit; objective[e] = -(elbo + log prior) at the optimum, elbo[e] (may be NULL) = elbo. */

@@ -111,8 +111,9 @@ def elbo_and_grad(kind, X, y, Z, theta):
     return val, grad
 
 
-def predict(kind, X, y, Z, theta, Xs):
-    """SGPR.predict_f (full_cov=False) and predict_y: ``f*``, ``f*_var``, ``y_var``."""
+def predict(kind, X, y, Z, theta, Xs, full_cov=False):
+    """SGPR.predict_f and predict_y: ``f*``, ``f*_var``, ``y_var``; with ``full_cov`` also ``f*_cov`` =
+    Kss + tmp2^T tmp2 - tmp1^T tmp1 and ``y_cov`` (gpflow/models/sgpr.py ``predict_f``)."""
     kind = gpr.canonical_kernel(kind)
     f = _factor(kind, X, y, Z, theta)
     Kus = gpr.kernel_matrix(kind, Z, Xs, f["ls"], f["var"])
@@ -120,7 +121,12 @@ def predict(kind, X, y, Z, theta, Xs):
     tmp2 = sla.solve_triangular(f["LB"], tmp1, lower=True)
     mean = tmp2.T @ f["c"]
     fvar = f["var"] + np.sum(tmp2 * tmp2, axis=0) - np.sum(tmp1 * tmp1, axis=0)
-    return {"f*": mean, "f*_var": fvar, "y_var": fvar + f["noise"]}
+    out = {"f*": mean, "f*_var": fvar, "y_var": fvar + f["noise"]}
+    if full_cov:
+        cov = gpr.kernel_matrix(kind, Xs, None, f["ls"], f["var"]) + tmp2.T @ tmp2 - tmp1.T @ tmp1
+        out["f*_cov"] = cov
+        out["y_cov"] = cov + f["noise"] * np.eye(len(Xs))
+    return out
 
 
 def fit(kind, X, y, Z, theta0, transform=None, trainable=None, max_iter=10_000):

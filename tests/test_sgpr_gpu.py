@@ -286,3 +286,37 @@ def test_sgpr_against_extended_precision(engine, golden_dir):
     os.makedirs("gpurun_out", exist_ok=True)
     json.dump(rows, open(os.path.join("gpurun_out", "sgpr_envelope.json"), "w"), indent=1)
     assert not bad, bad
+
+
+@pytest.mark.parametrize("kind", ["Matern32", "RBF"])
+def test_sgpr_full_cov(engine, kind):
+    """gpsat_sgpr_predict_cov (SGPR.predict_f(full_cov=True), gpflow_models.py:230, 245-263): the m x m blocks against
+    the oracle, symmetric, diagonal = f*_var, ragged m including 0 and sizes around the 64-wide output tile; and through
+    B200SGPRModel.predict(full_cov=True) with the exact model's keys."""
+    from gpsat_b200.models import B200SGPRModel
+    rng = np.random.default_rng(31 + len(kind))
+    shapes = [(300, 40, 17), (500, 128, 64), (257, 129, 65), (200, 30, 0), (700, 200, 130)]
+    experts = [_expert(rng, n, 3, M, m) for n, M, m in shapes]
+    theta = np.stack([_theta(rng, 3) for _ in experts])
+    b = _batch(kind, experts)
+    out = engine.sgpr_predict(b, [e[3] for e in experts], theta, full_cov=True)
+    ref_plain = engine.sgpr_predict(b, [e[3] for e in experts], theta)
+    np.testing.assert_array_equal(out["f*"], ref_plain["f*"])
+    off = b.off_m
+    for e, (X, y, Xs, Z) in enumerate(experts):
+        cov = out["f*_cov"][e]
+        assert cov.shape == (len(Xs), len(Xs))
+        if len(Xs) == 0:
+            continue
+        p = sgpr.predict(kind, X, y, Z, theta[e], Xs, full_cov=True)
+        np.testing.assert_allclose(cov, p["f*_cov"], rtol=RTOL, atol=RTOL * theta[e][3])
+        np.testing.assert_array_equal(cov, cov.T)
+        np.testing.assert_allclose(np.diag(cov), out["f*_var"][off[e]:off[e + 1]], rtol=1e-10, atol=1e-12 * theta[e][3])
+    X, y, Xs, Z = experts[0]
+    m = B200SGPRModel(coords=X, obs=y[:, None], kernel=kind, num_inducing_points=len(Z), verbose=False)
+    m.set_inducing_points(Z)
+    m.set_parameters(lengthscales=theta[0][:3], kernel_variance=theta[0][3], likelihood_variance=theta[0][4])
+    res = m.predict(Xs, full_cov=True)
+    assert set(res) >= {"f*", "f*_var", "y_var", "f*_cov", "y_cov", "f_bar"}
+    np.testing.assert_allclose(res["f*_cov"], out["f*_cov"][0], rtol=1e-12, atol=1e-14)
+    np.testing.assert_allclose(res["y_cov"], res["f*_cov"] + theta[0][4] * np.eye(len(Xs)), rtol=1e-12, atol=1e-14)
