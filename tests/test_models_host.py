@@ -174,8 +174,6 @@ def test_sgpr_model_inducing_points():
         B200SGPRModel(data=_df(8), obs_col="obs", coords_col=["x", "y"], num_inducing_points=None)
     with pytest.raises(NotImplementedError):
         small.optimise_parameters(train_inducing_points=True)
-    with pytest.raises(NotImplementedError):
-        small.predict(np.zeros((1, 2)), full_cov=True)
 
 
 def test_vff_model_domain_and_parameters():
