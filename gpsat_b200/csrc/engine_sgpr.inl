@@ -198,15 +198,13 @@ static int sgpr_eval_impl(gpsat_engine* h, const gpsat_batch* batch, const int64
     std::vector<int64_t> offc(E + 1, 0);
     for (int64_t e = 0; e < E; ++e) { offc[e + 1] = offc[e] + g.hm[e] * g.hm[e]; mmax = std::max(mmax, g.hm[e]); }
     ctotal = offc[E];
-    if (g.bmisc.ensure((E + 1) * 8)) return 1;
-    doffc = g.bmisc.as<int64_t>();
+    // [off_c | blocks (host callers)] in g.bcov: g.bmisc already holds off_z and the zero observations (sgpr_setup)
+    const size_t o_blocks = ((size_t)(E + 1) * 8 + 255) & ~(size_t)255;
+    if (g.bcov.ensure(o_blocks + (dev ? 0 : (size_t)std::max<int64_t>(ctotal, 1) * 8))) return 1;
+    doffc = g.bcov.as<int64_t>();
     CUDA_TRY(cudaMemcpyAsync(doffc, offc.data(), (E + 1) * 8, cudaMemcpyHostToDevice, g.stream));
     CUDA_TRY(cudaStreamSynchronize(g.stream));    // offc is a stack-lifetime source
-    if (dev) dcov = fcov;
-    else {
-      if (g.bcov.ensure(std::max<int64_t>(ctotal, 1) * 8)) return 1;
-      dcov = g.bcov.as<double>();
-    }
+    dcov = dev ? fcov : reinterpret_cast<double*>(g.bcov.as<char>() + o_blocks);
   }
   for (int64_t b0 = 0; b0 < E; b0 += S) {
     sgpr_eval_init_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(c.descs, c.sk, c.sb, c.ws, c.L, c.bd, c.in,

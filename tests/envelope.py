@@ -107,3 +107,34 @@ def make_sgpr_case(c):
     Z = X[rng.permutation(n)[:c["M"]]].copy()
     Xs = np.stack([rng.uniform(-5, 5, M_PRED), rng.uniform(-5, 5, M_PRED), np.zeros(M_PRED)], axis=1)
     return X, y, Z, Xs, theta
+
+
+# ---- variational Fourier features: the ELBO / predictions of GPR_kron in extended precision --
+VFF_CASES = (
+    dict(name="Matern32-1D-n2000-f40", kind="Matern32", n=2000, nfreq=(40,), ell=(0.8,), var=(1.2,), noise=0.05),
+    dict(name="Matern12-1D-n500-f64", kind="Matern12", n=500, nfreq=(64,), ell=(1.5,), var=(0.7,), noise=0.1),
+    dict(name="Matern52-2D-n1500-f12x9", kind="Matern52", n=1500, nfreq=(12, 9), ell=(0.9, 1.3), var=(1.1, 0.8), noise=0.02),
+    dict(name="Matern32-2D-n3000-f20x20", kind="Matern32", n=3000, nfreq=(20, 20), ell=(0.7, 0.6), var=(1.0, 1.0), noise=0.01),
+    dict(name="Matern32-2D-n1000-f10x10-s1e-4", kind="Matern32", n=1000, nfreq=(10, 10), ell=(1.0, 1.2), var=(1.0, 2.0),
+         noise=1e-4),
+    dict(name="Matern32-3D-n1000-f5x4x3", kind="Matern32", n=1000, nfreq=(5, 4, 3), ell=(1.0, 1.4, 2.0), var=(1.0, 0.9, 1.1),
+         noise=0.05),
+)
+
+
+def make_vff_case(c):
+    """(X, y, Xs, a, b, ms, theta) of one Fourier-feature sweep case; two of the M_PRED prediction points lie outside
+    the domain box for the kinds whose edge features the reference implements (vff.py:472-497)."""
+    D = len(c["nfreq"])
+    rng = np.random.default_rng([911, c["n"], D, len(c["kind"])])
+    X = rng.uniform(-2.0, 2.0, (c["n"], D))
+    y = np.sin(2 * X[:, 0]) + (0.5 * np.cos(X[:, 1]) if D > 1 else 0.0) + np.sqrt(c["noise"]) * rng.standard_normal(c["n"])
+    a = X.min(axis=0) - 0.4 * rng.uniform(0.5, 1.5, D)
+    b = X.max(axis=0) + 0.4 * rng.uniform(0.5, 1.5, D)
+    Xs = rng.uniform(-1.9, 1.9, (M_PRED, D))
+    if c["kind"] != "Matern52":
+        Xs[0, 0] = a[0] - 0.3
+        Xs[1, D - 1] = b[D - 1] + 0.25
+    ms = [np.arange(k) for k in c["nfreq"]]
+    theta = np.array([*c["ell"], *c["var"], c["noise"]])
+    return X, y, Xs, a, b, ms, theta

@@ -221,6 +221,28 @@ def test_vff_gradient_fd(kind, D):
         assert abs(fd - g[i]) <= 1e-6 * max(1.0, abs(g[i]))
 
 
+def test_vff_oracle_against_extended_precision(golden_dir):
+    """oracle/vff.py (float64) against the extended-precision restatement of the same formulas (oracle/vff_ld.py,
+    goldens by oracle/make_vff_envelope_golden.py): ELBO, analytic gradient (vs central differences of the long-double
+    ELBO) and predictions of the small sweep cases, at the error levels recorded in the goldens."""
+    import envelope as env
+    from oracle import vff
+    gold = np.load(os.path.join(golden_dir, "vff_envelope.npz"))
+    for c in env.VFF_CASES:
+        if c["n"] > 1500:
+            continue
+        X, y, Xs, a, b, ms, theta = env.make_vff_case(c)
+        D = X.shape[1]
+        pre = vff.Precomputed(X, y, a, b, ms)
+        v, g = vff.elbo_and_grad(c["kind"], pre, theta)
+        p = vff.predict(c["kind"], pre, theta, Xs)
+        ref = {k: gold[f"{c['name']}/{k}"] for k in ("elbo", "grad", "fmean", "fvar")}
+        assert abs(v - float(ref["elbo"])) <= 1e-10 * abs(float(ref["elbo"])), c["name"]
+        assert np.max(np.abs(g - ref["grad"])) <= 1e-8 * np.max(np.abs(ref["grad"])), c["name"]
+        assert np.max(np.abs(p["f*"] - ref["fmean"])) <= 1e-10 * np.max(np.abs(ref["fmean"])), c["name"]
+        assert np.max(np.abs(p["f*_var"] - ref["fvar"])) <= 1e-10 * np.prod(theta[D:2 * D]), c["name"]
+
+
 def test_vff_edge_features_and_fit():
     """Prediction features outside [a, b] take the kernel's edge form (vff.py:472-497); Matern52
     refuses them (:498-511).  The optimiser increases the ELBO."""

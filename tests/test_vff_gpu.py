@@ -199,3 +199,39 @@ def test_vff_model_driver_sequence_and_batched(engine):
         np.testing.assert_allclose(batch[e]._theta, loop[e]._theta, rtol=1e-12)
         assert abs(obj_b[e] - loop_obj[e]) <= 1e-12 * abs(loop_obj[e])
         np.testing.assert_allclose(pred_b[e]["f*"], loop_pred[e]["f*"], rtol=1e-12, atol=1e-14)
+
+
+def test_vff_against_extended_precision(engine, golden_dir):
+    """ELBO / gradient / predictions of the Fourier-feature model against extended precision (oracle/vff_ld.py, the
+    formulas of GPR_kron.elbo / predict_f, vff.py:612-675, in numpy.longdouble; gradient = central differences of that
+    ELBO; goldens: oracle/make_vff_envelope_golden.py).  The reference's own GPR_kron needs TensorFlow and its test is
+    commented out (tests/test_localexperts.py:150-190), so this is the pin of the row: 1-D with 40 and 64 frequencies,
+    2-D up to 20 x 20 (M = 1 521), 3-D, likelihood variance down to 1e-4, prediction points outside the domain box.
+    Held to the north star's 1e-8 on all four quantities; the float64 NumPy oracle's own error is recorded in the
+    goldens (f64_err) and written beside the CUDA path's to gpurun_out/vff_envelope.json."""
+    import json
+    import os
+    import envelope as env
+    from gpsat_b200.engine import RaggedBatch
+    gold = np.load(os.path.join(golden_dir, "vff_envelope.npz"))
+    rows, bad = [], []
+    for c in env.VFF_CASES:
+        X, y, Xs, a, b_, ms, theta = env.make_vff_case(c)
+        D = X.shape[1]
+        batch = RaggedBatch.from_lists(c["kind"], [X], [y], [Xs])
+        dom = (a[None, :], b_[None, :], np.asarray([c["nfreq"]], dtype=np.int32))
+        v, g, st = engine.vff_elbo(batch, dom, theta[None, :], with_grad=True)
+        p = engine.vff_predict(batch, dom, theta[None, :])
+        ref = {k: gold[f"{c['name']}/{k}"] for k in ("elbo", "grad", "fmean", "fvar", "f64_err", "cond_p")}
+        err = np.array([abs(v[0] - float(ref["elbo"])) / abs(float(ref["elbo"])),
+                        np.max(np.abs(g[0] - ref["grad"])) / np.max(np.abs(ref["grad"])),
+                        np.max(np.abs(p["f*"] - ref["fmean"])) / np.max(np.abs(ref["fmean"])),
+                        np.max(np.abs(p["f*_var"] - ref["fvar"])) / np.prod(theta[D:2 * D])])
+        tol = np.full(4, 1e-8)
+        rows.append(dict(case=c["name"], cond_p=float(ref["cond_p"]), gpu=err.tolist(), f64_oracle=ref["f64_err"].tolist(),
+                         tol=tol.tolist(), status=int(st[0])))
+        if st[0] != 0 or p["status"][0] != 0 or np.any(err > tol):
+            bad.append(rows[-1])
+    os.makedirs("gpurun_out", exist_ok=True)
+    json.dump(rows, open(os.path.join("gpurun_out", "vff_envelope.json"), "w"), indent=1)
+    assert not bad, bad
