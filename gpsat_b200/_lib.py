@@ -28,7 +28,7 @@ EXPORTED_SYMBOLS = (
     "gpsat_engine_i8_timeouts", "gpsat_engine_debug_set_i8_spin_limit", "gpsat_engine_set_precision_rule",
     "gpsat_engine_precision_rule_default", "gpsat_engine_i8_phases", "gpsat_engine_step_phases", "gpsat_fit_options_default",
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
-    "gpsat_sgpr_elbo", "gpsat_sgpr_predict", "gpsat_sgpr_predict_cov", "gpsat_sgpr_fit",
+    "gpsat_sgpr_elbo", "gpsat_sgpr_elbo_gradz", "gpsat_sgpr_predict", "gpsat_sgpr_predict_cov", "gpsat_sgpr_fit",
     "gpsat_vff_elbo", "gpsat_vff_predict", "gpsat_vff_fit",
     "gpsat_gaussian_smooth", "gpsat_glue_predictions", "gpsat_local_select", "gpsat_local_select_count_noalloc",
 )
@@ -110,6 +110,7 @@ def load():
     lib.gpsat_gpr_predict_cov.argtypes = [vp, C.POINTER(Batch), C.c_int, vp, vp, vp, vp, vp, vp, vp]
     lib.gpsat_gpr_factor_debug.argtypes = [vp, C.POINTER(Batch), vp, vp, vp]
     lib.gpsat_sgpr_elbo.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp]
+    lib.gpsat_sgpr_elbo_gradz.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp, vp]
     lib.gpsat_sgpr_fit.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp, vp,
                                    C.POINTER(FitOptions), C.POINTER(Priors), vp, vp, vp, vp, vp]
     lib.gpsat_sgpr_predict.argtypes = [vp, C.POINTER(Batch), vp, vp, C.c_int, vp, vp, vp, vp, vp, vp]

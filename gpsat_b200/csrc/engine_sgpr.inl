@@ -3,7 +3,7 @@
 // optimise_parameters (GPSat/models/gpflow_models.py:860-862, :229-230 and :290-329 inherited) for
 // a batch of experts.  Included at the end of engine_fit.inl (global namespace, using namespace gpsat).
 
-static SgprLay sgpr_layout(int npad, int mpad, int Mp, int nsplit, bool with_grad, bool with_pred) {
+static SgprLay sgpr_layout(int npad, int mpad, int Mp, int nsplit, bool with_grad, bool with_pred, bool with_z = false) {
   SgprLay L{};
   const size_t mm = (size_t)Mp * Mp, nm = (size_t)npad * Mp, pm = (size_t)mpad * Mp;
   const int MT = Mp / NB;
@@ -22,6 +22,9 @@ static SgprLay sgpr_layout(int npad, int mpad, int Mp, int nsplit, bool with_gra
   take(L.rrp, with_grad ? npad / SGPR_RES_ROWS : 0);
   take(L.gpc, with_grad ? (size_t)(npad / NB) * MT * PG : 0); take(L.gpk, with_grad ? (size_t)MT * MT * PG : 0);
   take(L.sums, SGPR_NSUMS);
+  L.with_z = with_z ? 1 : 0;
+  take(L.zpc, with_z ? (size_t)(npad / NB) * MT * 2 * NB * GPSAT_DMAX : 0);
+  take(L.zpk, with_z ? (size_t)MT * MT * 2 * NB * GPSAT_DMAX : 0);
   take(L.cts, with_pred ? pm : 0); take(L.t1, with_pred ? pm : 0); take(L.t2, with_pred ? pm : 0);
   take(L.ak, mm); take(L.ab, mm);
   take(L.side_k, side); take(L.side_b, side);
@@ -41,7 +44,7 @@ struct SgprCall {
 };
 
 static int sgpr_setup(Engine& g, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,
-                      bool with_grad, bool with_pred, int max_slots, SgprCall& c) {
+                      bool with_grad, bool with_pred, int max_slots, SgprCall& c, bool with_z = false) {
   const int64_t E = batch->E;
   const int D = batch->D;
   int Mmax = 0;
@@ -79,7 +82,7 @@ static int sgpr_setup(Engine& g, const gpsat_batch* batch, const int64_t* off_z,
   int S = (int)std::min<int64_t>(E, max_slots > 0 ? max_slots : 148);
   for (;;) {
     c.nsplit = (c.npad + SGPR_KCHUNK - 1) / SGPR_KCHUNK;
-    c.L = sgpr_layout(c.npad, c.mpad, c.Mp, c.nsplit, with_grad, with_pred);
+    c.L = sgpr_layout(c.npad, c.mpad, c.Mp, c.nsplit, with_grad, with_pred, with_z);
     if (c.L.total * 8 * S <= (size_t)((free_b + g.bsg.cap) * 0.8) || S == 1) break;
     S = std::max(1, S / 2);
   }
@@ -97,7 +100,8 @@ static int sgpr_setup(Engine& g, const gpsat_batch* batch, const int64_t* off_z,
 // One evaluation of every occupied slot: ELBO by-products, optionally the gradient partial sums
 // and / or the prediction reductions.
 static int sgpr_launch_eval(Engine& g, const SgprCall& c, bool with_grad, bool with_pred, double* dfm, double* dfv,
-                            double* dyv, const int64_t* doffc = nullptr, double* dcov = nullptr, int64_t mmax = 0) {
+                            double* dyv, const int64_t* doffc = nullptr, double* dcov = nullptr, int64_t mmax = 0,
+                            double* dgradz = nullptr) {
   const int S = c.S, MT = c.Mp / NB, ntl = MT * (MT + 1) / 2, NT = c.npad / NB, PT = c.mpad / NB;
   const unsigned T32 = c.Mp / 32;
   cudaStream_t st = g.stream;
@@ -130,6 +134,10 @@ static int sgpr_launch_eval(Engine& g, const SgprCall& c, bool with_grad, bool w
     gemm(SGPR_GEMM_TT, MT * MT, 1);
     gemm(SGPR_GEMM_GK, MT * MT, 1);
     g.stats.kernel_launches += 3;
+    if (dgradz) {
+      sgpr_gradz_kernel<<<dim3((unsigned)((c.Mp * GPSAT_DMAX + 255) / 256), S), 256, 0, st>>>(dd, c.in.off_z, dgradz);
+      g.stats.kernel_launches++;
+    }
   }
   sgpr_sums_kernel<<<S, 256, 0, st>>>(dd, with_grad ? 1 : 0);
   g.stats.kernel_launches++;
@@ -160,7 +168,7 @@ static double sgpr_flops(const Engine& g, const int64_t* off_z, int64_t e, bool 
 
 static int sgpr_eval_impl(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,
                           const double* theta, bool with_pred, double* fmean, double* fvar, double* yvar,
-                          double* elbo, double* grad, int32_t* status, double* fcov = nullptr) {
+                          double* elbo, double* grad, int32_t* status, double* fcov = nullptr, double* gradz = nullptr) {
   REQUIRE(h != nullptr, "engine is NULL");
   if (check_batch(batch, with_pred)) return 2;
   REQUIRE(theta != nullptr && off_z != nullptr, "theta / off_z is NULL");
@@ -174,7 +182,8 @@ static int sgpr_eval_impl(gpsat_engine* h, const gpsat_batch* batch, const int64
   const int P = batch->D + 2;
   const bool dev = mem == GPSAT_MEM_DEVICE, with_grad = grad != nullptr;
   SgprCall c;
-  if (int rc = sgpr_setup(g, batch, off_z, Z, mem, with_grad, with_pred, 0, c)) return rc;
+  REQUIRE(!gradz || (with_grad && !with_pred), "gradz needs grad and no prediction");
+  if (int rc = sgpr_setup(g, batch, off_z, Z, mem, with_grad, with_pred, 0, c, gradz != nullptr)) return rc;
   const int64_t Mtot = with_pred ? batch->off_m[E] : 0;
   const size_t EP = (size_t)E * P;
   size_t o_theta = 0, o_elbo = EP * 8, o_grad = o_elbo + (size_t)E * 8, o_status = o_grad + EP * 8;
@@ -206,10 +215,20 @@ static int sgpr_eval_impl(gpsat_engine* h, const gpsat_batch* batch, const int64
     CUDA_TRY(cudaStreamSynchronize(g.stream));    // offc is a stack-lifetime source
     dcov = dev ? fcov : reinterpret_cast<double*>(g.bcov.as<char>() + o_blocks);
   }
+  // d elbo / d Z: [off_z[E]][D] in the layout of Z; staged in g.bcov for host callers (no covariance blocks in this mode)
+  double* dgradz = nullptr;
+  const size_t zbytes = (size_t)off_z[E] * batch->D * 8;
+  if (gradz) {
+    if (dev) dgradz = gradz;
+    else {
+      if (g.bcov.ensure(std::max<size_t>(zbytes, 8))) return 1;
+      dgradz = g.bcov.as<double>();
+    }
+  }
   for (int64_t b0 = 0; b0 < E; b0 += S) {
     sgpr_eval_init_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(c.descs, c.sk, c.sb, c.ws, c.L, c.bd, c.in,
                                                                  (const double*)dtheta, (int)b0, S, with_pred ? 1 : 0);
-    if (sgpr_launch_eval(g, c, with_grad, with_pred, dfm, dfv, dyv, doffc, dcov, mmax)) return 1;
+    if (sgpr_launch_eval(g, c, with_grad, with_pred, dfm, dfv, dyv, doffc, dcov, mmax, dgradz)) return 1;
     sgpr_eval_finish_kernel<<<(S + 127) / 128, 128, 0, g.stream>>>(c.descs, c.sk, c.sb, c.bd, delbo, dgrad, dstatus, S);
     g.stats.kernel_launches += 2;
   }
@@ -225,6 +244,10 @@ static int sgpr_eval_impl(gpsat_engine* h, const gpsat_batch* batch, const int64
     if (grad) CUDA_TRY(cudaMemcpyAsync(grad, dgrad, EP * 8, cudaMemcpyDeviceToHost, g.stream));
     if (status) CUDA_TRY(cudaMemcpyAsync(status, dstatus, (size_t)E * 4, cudaMemcpyDeviceToHost, g.stream));
     if (dcov && ctotal > 0) CUDA_TRY(cudaMemcpyAsync(fcov, dcov, (size_t)ctotal * 8, cudaMemcpyDeviceToHost, g.stream));
+    if (gradz && zbytes > 0) {
+      CUDA_TRY(cudaMemcpyAsync(gradz, dgradz, zbytes, cudaMemcpyDeviceToHost, g.stream));
+      g.stats.d2h_bytes += (double)zbytes;
+    }
     g.stats.d2h_bytes += (double)Mtot * 24 + (double)E * 12 + (grad ? (double)EP * 8 : 0.0) + (dcov ? (double)ctotal * 8 : 0.0);
   }
   CUDA_TRY(cudaGetLastError());
@@ -236,6 +259,12 @@ extern "C" {
 int gpsat_sgpr_elbo(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,
                     const double* theta, double* elbo, double* grad, int32_t* status) {
   return sgpr_eval_impl(h, batch, off_z, Z, mem, theta, false, nullptr, nullptr, nullptr, elbo, grad, status);
+}
+
+int gpsat_sgpr_elbo_gradz(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,
+                          const double* theta, double* elbo, double* grad, double* gradz, int32_t* status) {
+  REQUIRE(grad != nullptr && gradz != nullptr, "grad / gradz is NULL");
+  return sgpr_eval_impl(h, batch, off_z, Z, mem, theta, false, nullptr, nullptr, nullptr, elbo, grad, status, nullptr, gradz);
 }
 
 int gpsat_sgpr_predict(gpsat_engine* h, const gpsat_batch* batch, const int64_t* off_z, const double* Z, int mem,

@@ -59,6 +59,8 @@ struct SgprDesc {
   double* gpc;           // [npad/128 * Mp/128][8] partial gradient sums of the Kuf term
   double* gpk;           // [(Mp/128)^2][8]        partial gradient sums of the Kuu term
   double* sums;          // [12] block-reduced scalars of one evaluation (sgpr_sums_kernel)
+  double* zpc;           // [Mp/128 * npad/128][2][128][DMAX] per-row partial sums of d elbo / d Z, Kuf term (or nullptr)
+  double* zpk;           // [(Mp/128)^2][2][128][DMAX]        the Kuu term (trainable inducing points only)
   double* Cts;           // [mpad][Mp]
   double* T1;            // [mpad][Mp]
   double* T2;            // [mpad][Mp]
@@ -67,7 +69,8 @@ struct SgprDesc {
 // Offsets (in doubles) of one slot's workspace; the same for every slot of a call.
 struct SgprLay {
   size_t ct, aq, at, w, u, wb, ub, bm, binv, q, tt, part, gam, bid, res, rrp, gpc, gpk, sums, cts, t1, t2, ak, ab,
-      side_k, side_b, total, tile_d;
+      side_k, side_b, total, tile_d, zpc, zpk;
+  int with_z;
   int Tmax, lgd;         // tiles per side of the M x M slots; aligned length of logdet[]
 };
 
@@ -112,6 +115,7 @@ __device__ __forceinline__ void sgpr_set_expert(SgprDesc& d, SlotDesc& k, SlotDe
   d.WB = base + L.wb; d.UB = base + L.ub; d.Bm = base + L.bm; d.Binv = base + L.binv; d.Q = base + L.q;
   d.TT = base + L.tt; d.part = base + L.part; d.gam = base + L.gam; d.bid = base + L.bid; d.res = base + L.res;
   d.rrp = base + L.rrp; d.gpc = base + L.gpc; d.gpk = base + L.gpk; d.sums = base + L.sums;
+  d.zpc = L.with_z ? base + L.zpc : nullptr; d.zpk = L.with_z ? base + L.zpk : nullptr;
   d.Cts = base + L.cts; d.T1 = base + L.t1;
   d.T2 = base + L.t2;
   sgpr_fill_slot(k, e, d.M, d.kind, d.D, base + L.ak, base + L.side_k, L);
@@ -285,6 +289,47 @@ __device__ __noinline__ void cross_grad_tile(int kind, int D, const double* xr, 
   }
 }
 
+// ---- the same tile contracted with d k / d z of its ROW points (trainable inducing points) -----------------------
+//   zp[half][r][d] = sum_{c in half} G_rc gunit(r2_rc) (xc_d[c] - xr_d[r]),   d k(z_r, p_c) / d z_rd = var gunit (xc_d - xr_d) / l_d
+// thread = (row r, column parity): 64 columns each, the two parities are summed by sgpr_gradz_kernel in a fixed order.
+template <int KIND>
+__device__ __forceinline__ void cross_gradz_tile_t(int D, const double* xr, const double* xc, int nr, int nc,
+                                                   const double* Cs, int tid, double* zp) {
+  const int r = tid & (NB - 1), half = tid >> 7;
+  double x0[GPSAT_DMAX], pz[GPSAT_DMAX];
+#pragma unroll
+  for (int dd = 0; dd < GPSAT_DMAX; ++dd) { x0[dd] = dd < D ? xr[dd * NB + r] : 0.0; pz[dd] = 0.0; }
+  if (r < nr) {
+#pragma unroll 2
+    for (int c = half; c < nc; c += GPSAT_THREADS / NB) {
+      const double gv = Cs[r * LDC + c];
+      double df[GPSAT_DMAX], r2 = 0.0;
+#pragma unroll
+      for (int dd = 0; dd < GPSAT_DMAX; ++dd) {
+        df[dd] = dd < D ? xc[dd * NB + c] - x0[dd] : 0.0;
+        r2 = fma(df[dd], df[dd], r2);
+      }
+      double ku, gu;
+      kunit_gunit_of_r2<KIND>(r2, ku, gu);
+      const double wg = gv * gu;
+#pragma unroll
+      for (int dd = 0; dd < GPSAT_DMAX; ++dd) pz[dd] = fma(wg, df[dd], pz[dd]);
+    }
+  }
+#pragma unroll
+  for (int dd = 0; dd < GPSAT_DMAX; ++dd) zp[((size_t)half * NB + r) * GPSAT_DMAX + dd] = pz[dd];
+}
+
+__device__ __noinline__ void cross_gradz_tile(int kind, int D, const double* xr, const double* xc, int nr, int nc,
+                                              const double* Cs, int tid, double* zp) {
+  switch (kind) {
+    case GPSAT_MATERN12: cross_gradz_tile_t<GPSAT_MATERN12>(D, xr, xc, nr, nc, Cs, tid, zp); break;
+    case GPSAT_MATERN32: cross_gradz_tile_t<GPSAT_MATERN32>(D, xr, xc, nr, nc, Cs, tid, zp); break;
+    case GPSAT_MATERN52: cross_gradz_tile_t<GPSAT_MATERN52>(D, xr, xc, nr, nc, Cs, tid, zp); break;
+    default: cross_gradz_tile_t<GPSAT_RBF>(D, xr, xc, nr, nc, Cs, tid, zp); break;
+  }
+}
+
 // scaled coordinates of rows [g0, g0 + 128) of a point set with np valid rows -> xs[dim][row]
 __device__ __forceinline__ void load_scaled_coords(const double* P, int np, int D, const double* inv_ls, int g0,
                                                    double* xs, int tid) {
@@ -411,6 +456,11 @@ sgpr_gemm_kernel(const SgprDesc* __restrict__ descs, int mode, int nsplit, int w
     const int nc = min(NB, max(0, (mode == SGPR_GEMM_GC ? d.n : d.M) - ct * NB));
     double part[GPSAT_DMAX + 2];
     cross_grad_tile(d.kind, d.D, xr, xc, nr, nc, Cs, tid, part);
+    if (d.zpc != nullptr) {
+      const int nct = (mode == SGPR_GEMM_GC) ? d.npad / NB : MT;
+      double* zp = (mode == SGPR_GEMM_GC ? d.zpc : d.zpk) + (size_t)(rt * nct + ct) * (2 * NB * GPSAT_DMAX);
+      cross_gradz_tile(d.kind, d.D, xr, xc, nr, nc, Cs, tid, zp);
+    }
 #pragma unroll
     for (int p = 0; p < GPSAT_DMAX + 2; ++p) {
       double v = part[p];
@@ -637,6 +687,30 @@ __device__ __forceinline__ double sgpr_finish_eval(const SgprDesc& d, const Slot
     gtheta[d.D + 1] = -0.5 * n / s2 + 0.5 * (rr + n * d.var - s2 * (trB - 2.0 * d.M + trBinv)) / (s2 * s2);
   }
   return bad ? -INFINITY : v;
+}
+
+// d elbo / d Z of one slot from the per-tile row sums (fixed order: Kuf tiles left to right, then the Kuu tiles):
+//   gradz[z_k][d] = var / l_d * ( sum_tiles zpc + 2 sum_tiles zpk )     (G_K is symmetric: row and column of Kuu move with z_k)
+// written at gradz + (off_z[expert] + k) * D + d.  One thread per (k, d).
+__global__ void __launch_bounds__(256) sgpr_gradz_kernel(const SgprDesc* __restrict__ descs,
+                                                         const int64_t* __restrict__ off_z, double* __restrict__ gradz) {
+  const SgprDesc& d = descs[blockIdx.y];
+  if (d.expert < 0 || d.zpc == nullptr) return;
+  const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+  const int k = idx / GPSAT_DMAX, dd = idx - k * GPSAT_DMAX;
+  if (k >= d.M || dd >= d.D) return;
+  const int rt = k / NB, r = k - rt * NB, NT = d.npad / NB, MT = d.Mp / NB;
+  constexpr size_t TS = 2 * NB * GPSAT_DMAX;
+  double sc = 0.0, sk = 0.0;
+  for (int ct = 0; ct < NT; ++ct) {
+    const double* zp = d.zpc + (size_t)(rt * NT + ct) * TS + (size_t)r * GPSAT_DMAX + dd;
+    sc += zp[0] + zp[NB * GPSAT_DMAX];
+  }
+  for (int ct = 0; ct < MT; ++ct) {
+    const double* zp = d.zpk + (size_t)(rt * MT + ct) * TS + (size_t)r * GPSAT_DMAX + dd;
+    sk += zp[0] + zp[NB * GPSAT_DMAX];
+  }
+  gradz[(size_t)(off_z[d.expert] + k) * d.D + dd] = d.var * d.inv_ls[dd] * (sc + 2.0 * sk);
 }
 
 // One warp per prediction point s: mean = <T2_s, c>, var = var_f + |T2_s|^2 - |T1_s|^2

@@ -337,18 +337,24 @@ class Engine:
         Zp = np.ascontiguousarray(np.concatenate(Zl, axis=0)) if Zl else np.zeros((1, batch.D))
         return off_z, self._in(batch, Zp, np.float64, Zp.shape)
 
-    def sgpr_elbo(self, batch: RaggedBatch, Z, theta, with_grad: bool = False):
+    def sgpr_elbo(self, batch: RaggedBatch, Z, theta, with_grad: bool = False, with_z: bool = False):
         """ELBO of ``gpflow.models.SGPR`` per expert at fixed theta (and, ``with_grad``, its gradient
-        w.r.t. theta with Z fixed).  Returns (elbo, grad or None, status)."""
+        w.r.t. theta with Z fixed).  Returns (elbo, grad or None, status); ``with_z`` (implies ``with_grad``) appends
+        the gradient w.r.t. the inducing points, packed [sum M_e, D] like Z (``gpsat_sgpr_elbo_gradz``)."""
         E, P = batch.E, batch.D + 2
         mem = _lib.MEM_DEVICE if batch.on_device else _lib.MEM_HOST
         off_z, Zp = self._inducing(batch, Z)
         th = self._in(batch, theta, np.float64, (E, P))
         elbo = self._empty(batch, (E,), np.float64)
-        grad = self._empty(batch, (E, P), np.float64) if with_grad else None
+        grad = self._empty(batch, (E, P), np.float64) if (with_grad or with_z) else None
         status = self._empty(batch, (E,), np.int32)
         cb = batch._c(False)
         self._pre(batch)
+        if with_z:
+            gz = self._empty(batch, (max(int(off_z[-1]), 1), batch.D), np.float64)
+            _lib.check(self._lib.gpsat_sgpr_elbo_gradz(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, _ptr(th),
+                                                       _ptr(elbo), _ptr(grad), _ptr(gz), _ptr(status)))
+            return elbo, grad, gz[:int(off_z[-1])], status
         _lib.check(self._lib.gpsat_sgpr_elbo(self._h, C.byref(cb), _ptr(off_z), _ptr(Zp), mem, _ptr(th), _ptr(elbo),
                                              _ptr(grad), _ptr(status)))
         return elbo, grad, status

@@ -532,8 +532,7 @@ class B200SGPRModel(B200GPRModel):
     when there are fewer data points, ``:810-814``), the objective value is **+ELBO**
     (``:860-862``), ``predict`` is the parent's (``predict_f`` / ``predict_y`` of the sparse model)
     and ``param_names`` gains "inducing_points".  ``optimise_parameters(train_inducing_points=True)``
-    is not implemented: the device optimiser keeps Z fixed, which is the reference's default
-    (``:896-897``).
+    (``:864-899``) optimises Z together with the hyper-parameters (host L-BFGS-B around CUDA evaluations).
     """
 
     def __init__(self, data=None, coords_col=None, obs_col=None, coords=None, obs=None, coords_scale=None,
@@ -588,10 +587,66 @@ class B200SGPRModel(B200GPRModel):
         return res
 
     def optimise_parameters(self, train_inducing_points=False, max_iter=10_000, fixed_params=None, **opt_kwargs):
-        if train_inducing_points:
-            raise NotImplementedError("train_inducing_points=True is not implemented: the device optimiser keeps "
-                                      "the inducing points fixed (the reference's default)")
-        return super().optimise_parameters(max_iter=max_iter, fixed_params=fixed_params, **opt_kwargs)
+        """``gpflow_models.py:864-899``.  With the inducing points fixed (the reference's default, ``:896-897``) this is
+        the parent's device-side batched L-BFGS.  ``train_inducing_points=True`` makes Z [M, D] (unconstrained, as in
+        GPflow) part of the search: D + 2 + M D variables are beyond the device optimiser's state, so the loop is the
+        host routine GPflow's ``Scipy`` optimiser calls itself - ``scipy.optimize.minimize(method="L-BFGS-B", jac=True)``
+        - around one CUDA evaluation per step (``gpsat_sgpr_elbo_gradz``: ELBO, d/d theta and d/d Z in one pass)."""
+        if not train_inducing_points:
+            return super().optimise_parameters(max_iter=max_iter, fixed_params=fixed_params, **opt_kwargs)
+        import scipy.optimize as sopt
+        if np.any(self._pkind):
+            raise NotImplementedError("priors are not supported together with train_inducing_points=True")
+        self._fix_hyperparameters([] if fixed_params is None else fixed_params)
+        method = opt_kwargs.pop("method", "L-BFGS-B")
+        if method != "L-BFGS-B":
+            raise NotImplementedError(f"optimiser method '{method}' is not implemented (L-BFGS-B only)")
+        tol = opt_kwargs.pop("tol", None)
+        for k in ("compile", "allow_unused_variables", "tf_fun_args", "track_loss_history"):
+            opt_kwargs.pop(k, None)
+        if opt_kwargs:
+            raise TypeError(f"unexpected optimiser arguments: {sorted(opt_kwargs)}")
+        free = self._trainable.astype(bool)
+        nfree = int(free.sum())
+        sig = self._tkind == _lib.TRANSFORM_SIGMOID
+        a, b = self._ta, self._tb
+        theta0 = self._theta.copy()
+        Z0 = self.get_inducing_points()
+        y0 = theta0 - a
+        with np.errstate(divide="ignore", invalid="ignore"):
+            xi0 = np.where(sig, np.log(theta0 - a) - np.log(b - theta0), y0 + np.log(-np.expm1(-y0)))
+        batch = self._batch().to_device(f"cuda:{self.device}")      # X, y stay resident across the evaluations
+        eng = self.engine
+
+        def unpack(v):
+            xi = xi0.copy()
+            xi[free] = v[:nfree]
+            s = np.where(xi >= 0, 1.0 / (1.0 + np.exp(-np.abs(xi))), np.exp(-np.abs(xi)) / (1.0 + np.exp(-np.abs(xi))))
+            sp = np.log1p(np.exp(-np.abs(xi))) + np.maximum(xi, 0.0)
+            theta = np.where(free, np.where(sig, b * s + a * (1.0 - s), a + sp), theta0)
+            dth = np.where(sig, (b - a) * s * (1.0 - s), s)
+            return theta, dth, v[nfree:].reshape(Z0.shape)
+
+        def fun(v):
+            theta, dth, Z = unpack(v)
+            elbo, g, gz, st = eng.sgpr_elbo(batch, [Z], theta[None, :], with_z=True)
+            elbo, g, gz, st = (np.asarray(t.cpu() if hasattr(t, "cpu") else t) for t in (elbo, g, gz, st))
+            if int(st[0]) != _lib.STATUS_OK or not np.isfinite(elbo[0]):
+                return np.inf, np.zeros(len(v))
+            return -float(elbo[0]), np.concatenate([(-g[0] * dth)[free], -gz.ravel()])
+
+        options = {"maxiter": int(max_iter)}
+        res = sopt.minimize(fun, np.concatenate([xi0[free], Z0.ravel()]), jac=True, method="L-BFGS-B", tol=tol, options=options)
+        theta, _, Z = unpack(res.x)
+        if np.isfinite(res.fun):
+            self._theta = np.array(theta, dtype=np.float64)
+            self.inducing_points = np.array(Z, dtype=np.float64)
+        self.opt_info = {"status": 0 if res.success else 2, "n_evals": int(res.nfev), "n_iters": int(res.nit),
+                         "objective": float(res.fun)}
+        if not res.success:
+            print("*" * 10)
+            print("optimization failed!")
+        return bool(res.success)
 
     def get_objective_function_value(self):
         """ELBO at the current parameters (``gpflow_models.py:860-862``; note the sign: not negated)."""

@@ -215,6 +215,14 @@ int gpsat_gpr_predict_cov(gpsat_engine* eng, const gpsat_batch* batch, int mem, 
 int gpsat_sgpr_elbo(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,
                     int mem, const double* theta, double* elbo, double* grad, int32_t* status);
 
+/* gpsat_sgpr_elbo plus the gradient with respect to the inducing points: gradz [sum M_e][D] in the layout of Z
+ * (follows `mem`), d elbo / d Z in the scaled coordinates Z is given in.  This is what TensorFlow differentiates once
+ * GPflowSGPRModel.optimise_parameters(train_inducing_points=True) has made inducing_variable.Z trainable
+ * (gpflow_models.py:864-899, set_trainable at :896-897); grad and gradz must both be non-NULL. */
+int gpsat_sgpr_elbo_gradz(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,
+                          int mem, const double* theta, double* elbo, double* grad, double* gradz,
+                          int32_t* status);
+
 /* SGPR.predict_f / predict_y (full_cov = False) at batch->Xs, as GPflowSGPRModel.predict uses them
  * (gpflow_models.py:229-230 inherited); elbo (may be NULL) comes out of the same factorisation. */
 int gpsat_sgpr_predict(gpsat_engine* eng, const gpsat_batch* batch, const int64_t* off_z, const double* Z,

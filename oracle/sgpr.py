@@ -64,9 +64,12 @@ def elbo(kind, X, y, Z, theta):
     return float(bound)
 
 
-def elbo_and_grad(kind, X, y, Z, theta):
+def elbo_and_grad(kind, X, y, Z, theta, with_z=False):
     """(elbo, d elbo / d theta), theta in constrained space, Z fixed (the reference freezes the
-    inducing points unless ``train_inducing_points``, gpflow_models.py:896-897).
+    inducing points unless ``train_inducing_points``, gpflow_models.py:896-897); ``with_z`` adds
+    d elbo / d Z [M, D] (what ``set_trainable(inducing_variable.Z, True)`` makes TensorFlow differentiate):
+        d elbo / d z_kd = sum_i G_C[k,i] dk(z_k, x_i)/dz_kd + 2 sum_j G_K[k,j] dk(z_k, z_j)/dz_kd
+    (the jitter on the diagonal of Kuu does not depend on Z; dk/dz vanishes at z_j = z_k).
 
     With K = Kuu + jitter I, C = Kuf, Sigma = K + C C^T / s2, beta = Sigma^-1 C y / s2:
         G_K = 1/2 [K^-1 - Sigma^-1 - beta beta^T - K^-1 C C^T K^-1 / s2]
@@ -108,6 +111,13 @@ def elbo_and_grad(kind, X, y, Z, theta):
     Kuu_nojit = f["Kuu"] - JITTER * np.eye(M)
     grad[D] = (np.sum(G_K * Kuu_nojit) + np.sum(G_C * C)) / var - 0.5 * n / s2
     grad[D + 1] = -0.5 * n / s2 + 0.5 * (resid @ resid + n * var - np.sum(Dm * (C @ C.T))) / s2 ** 2
+    if with_z:
+        gz = np.empty((M, D))
+        for d in range(D):
+            dxz = X[:, d][None, :] - Z[:, d][:, None]          # x_i - z_k
+            dzz = Z[:, d][None, :] - Z[:, d][:, None]          # z_j - z_k
+            gz[:, d] = (np.sum(GCg * dxz, axis=1) + 2.0 * np.sum(GKg * dzz, axis=1)) / ls[d] ** 2
+        return val, grad, gz
     return val, grad
 
 
@@ -127,6 +137,37 @@ def predict(kind, X, y, Z, theta, Xs, full_cov=False):
         out["f*_cov"] = cov
         out["y_cov"] = cov + f["noise"] * np.eye(len(Xs))
     return out
+
+
+def fit_z(kind, X, y, Z0, theta0, transform=None, trainable=None, max_iter=10_000):
+    """gpflow.optimizers.Scipy().minimize(-elbo) over the free hyper-parameters AND the inducing points
+    (``optimise_parameters(train_inducing_points=True)``, gpflow_models.py:864-899; Z is unconstrained).
+    Returns (theta, Z, elbo, success, nfev)."""
+    n, D = X.shape
+    P = D + 2
+    theta0 = np.asarray(theta0, dtype=np.float64).copy()
+    Z0 = np.asarray(Z0, dtype=np.float64)
+    transform = gpr.Transform.gpflow_default(D) if transform is None else transform
+    trainable = np.ones(P, bool) if trainable is None else np.asarray(trainable, bool)
+    xi0 = transform.inverse(theta0)
+    nfree = int(trainable.sum())
+
+    def unpack(v):
+        xi = xi0.copy()
+        xi[trainable] = v[:nfree]
+        return xi, np.where(trainable, transform.forward(xi), theta0), v[nfree:].reshape(Z0.shape)
+
+    def fun(v):
+        xi, theta, Z = unpack(v)
+        val, g, gz = elbo_and_grad(kind, X, y, Z, theta, with_z=True)
+        if not np.isfinite(val):
+            return np.inf, np.zeros(len(v))
+        return -val, np.concatenate([(-g * transform.dtheta_dxi(xi))[trainable], -gz.ravel()])
+
+    res = sopt.minimize(fun, np.concatenate([xi0[trainable], Z0.ravel()]), jac=True, method="L-BFGS-B",
+                        options=dict(maxiter=max_iter))
+    _, theta, Z = unpack(res.x)
+    return theta, Z, elbo(kind, X, y, Z, theta), bool(res.success), int(res.nfev)
 
 
 def fit(kind, X, y, Z, theta0, transform=None, trainable=None, max_iter=10_000):

@@ -172,8 +172,6 @@ def test_sgpr_model_inducing_points():
     np.testing.assert_array_equal(small.get_inducing_points(), small.coords)
     with pytest.raises(AssertionError):
         B200SGPRModel(data=_df(8), obs_col="obs", coords_col=["x", "y"], num_inducing_points=None)
-    with pytest.raises(NotImplementedError):
-        small.optimise_parameters(train_inducing_points=True)
 
 
 def test_vff_model_domain_and_parameters():

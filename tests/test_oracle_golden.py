@@ -164,6 +164,29 @@ def test_sgpr_gradient_fd_and_tight_bound(kind):
     assert abs(sgpr.elbo(kind, X, y, X.copy(), th) - exact) < 1e-2
 
 
+@pytest.mark.parametrize("kind", gpr.KERNELS)
+def test_sgpr_inducing_point_gradient_fd(kind):
+    """d elbo / d Z of oracle/sgpr.py (the gradient train_inducing_points=True exposes, gpflow_models.py:896-897)
+    against central differences of the ELBO."""
+    from oracle import sgpr
+    rng = np.random.default_rng(len(kind))
+    n, M, D = 120, 15, 3
+    X = rng.uniform(-2, 2, (n, D))
+    y = np.sin(X[:, 0]) + 0.1 * rng.standard_normal(n)
+    Z = X[:M] + 0.05 * rng.standard_normal((M, D))
+    th = np.array([1.0, 1.3, 0.8, 0.9, 0.05])
+    v, g, gz = sgpr.elbo_and_grad(kind, X, y, Z, th, with_z=True)
+    v2, g2 = sgpr.elbo_and_grad(kind, X, y, Z, th)
+    assert v == v2 and np.array_equal(g, g2)
+    for k in range(0, M, 4):
+        for d in range(D):
+            Zp, Zm = Z.copy(), Z.copy()
+            Zp[k, d] += 1e-6
+            Zm[k, d] -= 1e-6
+            fd = (sgpr.elbo(kind, X, y, Zp, th) - sgpr.elbo(kind, X, y, Zm, th)) / 2e-6
+            assert abs(fd - gz[k, d]) <= 1e-6 * max(1.0, np.abs(gz).max()), (k, d, fd, gz[k, d])
+
+
 # ---- VFF (oracle/vff.py) ---------------------------------------------------------------------
 def test_vff_features_match_reference_numpy(golden_dir):
     """make_Kuf_np / make_kvs_np and the static quantities of GPR_kron.__init__
