@@ -197,8 +197,6 @@ def test_sgpr_model_driver_sequence(engine, golden_dir):
     assert set(p) == {"f*", "f*_var", "y_var", "f_bar"}
     assert abs(p["f*"][0] - g["pred_mean"][0]) < 1e-4
     assert abs(p["f*_var"][0] - g["pred_std"][0] ** 2) < 1e-4
-    with pytest.raises(NotImplementedError):
-        m.optimise_parameters(train_inducing_points=True)
 
 
 def test_batched_helper_equals_loop(engine):
