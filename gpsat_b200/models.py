@@ -742,6 +742,18 @@ class B200VFFModel(B200GPRModel):
     def _vff(self):
         return (self.vff_a[None, :], self.vff_b[None, :], self.vff_nfreq[None, :])
 
+    def update_obs_data(self, data=None, coords_col=None, obs_col=None, coords=None, obs=None, coords_scale=None,
+                        obs_scale=None):
+        """Swap the training data (``gpflow_models.py:159-176`` inherited by the reference's VFF model, where the
+        static ``Kuf`` products of ``GPR_kron.__init__`` are NOT rebuilt; here they are rebuilt on the next call).  The
+        Fourier domain keeps its box and is widened, by the constructor's rule (``vff_model.py:186-199``), wherever the
+        new data would fall outside it."""
+        super().update_obs_data(data=data, coords_col=coords_col, obs_col=obs_col, coords=coords, obs=obs,
+                                coords_scale=coords_scale, obs_scale=obs_scale)
+        cmin, cmax = self.coords.min(axis=0), self.coords.max(axis=0)
+        self.vff_a = np.where(self.vff_a < cmin, self.vff_a, cmin - 1e-8)
+        self.vff_b = np.where(self.vff_b > cmax, self.vff_b, cmax + 1e-8)
+
     def _fit_kwargs(self) -> dict:
         return {"vff": self._vff()}
 

@@ -203,6 +203,14 @@ def test_vff_model_domain_and_parameters():
     np.testing.assert_array_equal(m._trainable, [True, False, True, False, True])
     one = B200VFFModel(data=df, obs_col="obs", coords_col=["x"], num_inducing_features=5)
     assert one.num_features == 9 and one.vff_a[0] == one.coords.min() - 1e-8        # domain_size=None
+    # update_obs_data: the box is kept where the new data fits and widened where it does not
+    a0, b0 = m.vff_a.copy(), m.vff_b.copy()
+    df2 = df.copy()
+    df2["y"] = df2["y"] * 3.0
+    m.update_obs_data(data=df2, obs_col="obs", coords_col=["x", "y"], coords_scale=[5e4, 5e4])
+    assert m.vff_a[0] == a0[0] and m.vff_b[0] == b0[0]
+    assert np.all(m.coords > m.vff_a) and np.all(m.coords < m.vff_b)
+    assert m.vff_a[1] <= a0[1] and m.vff_b[1] >= b0[1]
     with pytest.raises(NotImplementedError):
         B200VFFModel(data=df, obs_col="obs", coords_col=["x"], num_inducing_features=5, kernel="RBF")
     with pytest.raises(AssertionError):
