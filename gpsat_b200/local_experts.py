@@ -333,15 +333,15 @@ class LocalExpertOI:
 
     def run(self, store_path: Optional[str] = None, optimise: bool = True, predict: bool = True,
             min_obs: int = 3, table_suffix: str = "", config_id: int = 1,
-            device_select: Optional[bool] = False, store_every: int = 10, check_config_compatible: bool = True,
+            device_select: Optional[bool] = None, store_every: int = 10, check_config_compatible: bool = True,
             skip_valid_checks_on: Optional[list] = None, world: Optional[bool] = None) -> Dict[str, pd.DataFrame]:
         """All experts: select, fit, predict, tabulate.  Returns ``{table name: DataFrame}`` with the
         reference's tables (``preds``, ``run_details``, one per stored hyper-parameter), each name
         extended by ``table_suffix``.  ``device_select=True`` evaluates the selection rules of all
         experts in one GPU launch (``gpsat_local_select``) and builds the packed batch and the
         tables with array operations instead of one model instance and one DataFrame per expert
-        (exact-GPR model only; ``None`` = whenever the configuration allows it); the tables are identical to the
-        default path.
+        (exact-GPR model only; ``None``, the default, = whenever the configuration allows it; ``False`` forces the
+        per-model path); the tables of the two paths are identical.
 
         ``store_every`` / ``check_config_compatible`` / ``skip_valid_checks_on`` are the reference's remaining
         ``run`` arguments (``local_experts.py:761-790``): all experts are processed in one batch and stored once, so

@@ -270,7 +270,7 @@ def test_vectorised_driver_equals_per_model_driver(built, optimise, predict):
     from gpsat_b200.local_experts import LocalExpertOI
     locs, data, data_cfg, model_cfg, grid = _driver_case()
     a = LocalExpertOI(locs, data, data_cfg, model_cfg, {"df": grid, "max_dist": 1e5}).run(
-        min_obs=100, optimise=optimise, predict=predict, table_suffix="_A", config_id=3)
+        min_obs=100, optimise=optimise, predict=predict, table_suffix="_A", config_id=3, device_select=False)
     b = LocalExpertOI(locs, data, data_cfg, model_cfg, {"df": grid, "max_dist": 1e5}).run(
         min_obs=100, optimise=optimise, predict=predict, table_suffix="_A", config_id=3, device_select=True)
     assert set(a) == set(b)
@@ -289,8 +289,9 @@ def test_vectorised_driver_other_configs(built):
     model_cfg = dict(model_cfg, init_params={"coords_scale": [5e4, 5e4, 1]},
                      optim_kwargs={"max_iter": 25, "fixed_params": ["likelihood_variance"]},
                      params_to_store=["lengthscales", "likelihood_variance"])
-    a = LocalExpertOI(locs, data, data_cfg, model_cfg).run(min_obs=30)
+    a = LocalExpertOI(locs, data, data_cfg, model_cfg).run(min_obs=30, device_select=False)
     b = LocalExpertOI(locs, data, data_cfg, model_cfg).run(min_obs=30, device_select=True)
+    c = LocalExpertOI(locs, data, data_cfg, model_cfg).run(min_obs=30)                 # default: automatic = array-built
     assert set(a) == set(b) == {"run_details", "preds", "lengthscales", "likelihood_variance"}
     for k in a:
         ta, tb = a[k], b[k]
@@ -298,6 +299,7 @@ def test_vectorised_driver_other_configs(built):
             ta, tb = ta.drop(columns="run_time"), tb.drop(columns="run_time")
         pd.testing.assert_frame_equal(ta, tb, check_exact=True, check_dtype=False)
     assert np.all(b["likelihood_variance"]["likelihood_variance"].values == 1.0)
+    pd.testing.assert_frame_equal(c["preds"], b["preds"], check_exact=True)
     with pytest.raises(NotImplementedError):
         LocalExpertOI(locs, data, data_cfg, dict(model_cfg, oi_model="B200SGPRModel")).run(device_select=True)
 

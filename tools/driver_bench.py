@@ -46,7 +46,7 @@ def main():
                        {"oi_model": "B200GPRModel", "init_params": {"coords_scale": [5e4, 5e4, 1], "obs_mean": "local"},
                         "constraints": {"lengthscales": {"low": [1e-8, 1e-8, 1e-8], "high": [6e5, 6e5, 9]}}},
                        {"df": pred, "max_dist": 200e3})
-    kw = {"device_select": True} if args.device_select else {}
+    kw = {"device_select": bool(args.device_select)}
     oi.run(**kw)                      # warm-up (allocations, first CUDA call)
     t0 = time.time()
     tabs = oi.run(**kw)
