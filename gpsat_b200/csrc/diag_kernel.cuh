@@ -3,8 +3,10 @@
 // step of the blocked factorisation for larger ones).
 //
 // Blocked right-looking factorisation with 32-wide panels, all in shared memory:
-//   for p in 0..3:  warp 0 factors the 32 x 32 diagonal block in registers (one row per lane) and
-//                   inverts it (one column per lane);  all warps: rows below *= W_pp^T (DMMA),
+//   for p in 0..3:  warp 0 factors the 32 x 32 diagonal block in registers (one row per lane);
+//                   full panels: warps 0..2 solve the rows below against L_pp (one row per thread) while warp 7
+//                   inverts the block off the critical path; partial panels (the tile with the y row): warp 0
+//                   inverts it (one column per lane) and all warps multiply the rows below by W_pp^T (DMMA);
 //                   trailing block -= panel panel^T (DMMA, lower fragments only)
 //   then U = L^-T block by block (the 32-granular twin of the trtri tiles of step_kernel).
 // The tile is "augmented": local row ncol (global row n) is the observation row y^T and rides
@@ -14,6 +16,13 @@
 #include "i8slice.cuh"
 
 namespace gpsat {
+
+__device__ unsigned long long g_step_phase[32];   // see step_kernel.cuh
+#ifdef GPSAT_STEP_PHASES
+#define DIAG_PHASE(k) do { if (tid == 0) { long long now_ = clock64(); atomicAdd(&g_step_phase[k], (unsigned long long)(now_ - tdiag)); tdiag = now_; } } while (0)
+#else
+#define DIAG_PHASE(k) do { } while (0)
+#endif
 
 constexpr int LDD = NB + 4;                 // tile stride: DMMA fragment loads are conflict-free
 constexpr int PB = 32;                      // panel width
@@ -36,6 +45,91 @@ __device__ __forceinline__ void frag_nt(double& c0, double& c1, const double* A,
   for (int k4 = 0; k4 < nk4; ++k4) dmma884(c0, c1, sa * ap[4 * k4], bp[4 * k4]);
 }
 
+// ---- full 32-wide panels (every column an observation column): the three pieces of the fast path ----------------
+// (1) Cholesky of the 32 x 32 diagonal block by one warp, lane = row.  The dependent chain per pivot is
+//     shuffle -> rsqrt -> one multiply -> one FMA: every lane tracks its own diagonal entry in `dcur` (a_ll -= v^2 needs
+//     no other lane's value, so the next pivot does not wait for the column's round trip through shared memory), and
+//     L_jj = sqrt(pivot) and 1 / L_jj are refined once per lane after the loop, all 32 pivots in parallel, instead
+//     of five dependent FP64 operations inside every step.  Returns log(L_ll) of the lane's pivot.
+__device__ __forceinline__ double chol32_fast(double* Cs, int c0, double* colb, double* wdiag, int lane, bool& bad) {
+  double a[PB];
+#pragma unroll
+  for (int k = 0; k < PB; ++k) a[k] = Cs[(c0 + lane) * LDD + c0 + k];
+  double dcur = 0.0, mypiv = 1.0;
+#pragma unroll
+  for (int k = 0; k < PB; ++k) if (k == lane) dcur = a[k];
+#pragma unroll
+  for (int j = 0; j < PB; ++j) {
+    double piv = __shfl_sync(0xffffffffu, dcur, j);
+    const bool nok = !(piv > 0.0) || !isfinite(piv);
+    bad = bad || nok;
+    piv = nok ? 1.0 : piv;
+    if (lane == j) mypiv = piv;
+    const double inv0 = rsqrt(piv);
+    const double v = (lane > j) ? a[j] * inv0 : 0.0;
+    dcur = fma(-v, v, dcur);
+    a[j] = v;
+    double* cb = colb + (j & 1) * PB;
+    cb[lane] = v;
+    __syncwarp();
+    // a[k] -= L[lane][j] * L[k][j]; entries with k > lane are never read, so no predicate
+#pragma unroll
+    for (int k = j + 1; k < PB; ++k) a[k] = fma(-v, cb[k], a[k]);
+  }
+  const double inv0 = rsqrt(mypiv);
+  double dg = mypiv * inv0;
+  dg = fma(fma(-dg, dg, mypiv), 0.5 * inv0, dg);
+  const double inv = fma(fma(-dg, inv0, 1.0), inv0, inv0);
+  wdiag[c0 + lane] = inv;
+#pragma unroll
+  for (int k = 0; k < PB; ++k) if (k == lane) a[k] = dg;
+#pragma unroll
+  for (int k = 0; k < PB; ++k) if (k <= lane) Cs[(c0 + lane) * LDD + c0 + k] = a[k];
+  return log(dg);
+}
+
+// (2) inverse of the factored block by one warp, lane = column c of W_pp: x[r] = W[r][c]; W_pp goes to W (row-major,
+//     stride LDP) and its transpose U_pp into the strict upper part of the block in Cs.
+__device__ __forceinline__ void inv32(double* Cs, int c0, const double* wdiag, double* W, int lane) {
+  double x[PB], acc[PB];
+#pragma unroll
+  for (int r = 0; r < PB; ++r) { x[r] = 0.0; acc[r] = 0.0; }
+  const double myinv = wdiag[c0 + lane];
+#pragma unroll
+  for (int r = 0; r < PB; ++r) if (r == lane) x[r] = myinv;
+#pragma unroll
+  for (int k = 0; k < PB - 1; ++k) {
+    const double xk = x[k];
+#pragma unroll
+    for (int r = k + 1; r < PB; ++r) acc[r] = fma(Cs[(c0 + r) * LDD + c0 + k], xk, acc[r]);
+    if (k + 1 > lane) x[k + 1] = -acc[k + 1] * wdiag[c0 + k + 1];
+  }
+#pragma unroll
+  for (int r = 0; r < PB; ++r) {
+    W[r * LDP + lane] = x[r];                                  // W_pp[r][c], zero above the diagonal
+    if (r > lane) Cs[(c0 + lane) * LDD + c0 + r] = x[r];      // U_pp = W_pp^T, strict upper
+  }
+}
+
+// (3) one row below the block: x L_pp^T = a by forward substitution (two dependent operations per column), in place.
+//     Replaces the product with the explicit inverse, which therefore leaves the critical path.
+__device__ __forceinline__ void rowsolve32(double* Cs, int c0, const double* wdiag, int R) {
+  double x[PB];
+  double* row = Cs + R * LDD + c0;
+#pragma unroll
+  for (int k = 0; k < PB; ++k) x[k] = row[k];
+#pragma unroll
+  for (int j = 0; j < PB; ++j) {
+    x[j] *= wdiag[c0 + j];
+#pragma unroll
+    for (int k = j + 1; k < PB; ++k) x[k] = fma(-x[j], Cs[(c0 + k) * LDD + c0 + j], x[k]);
+  }
+#pragma unroll
+  for (int k = 0; k < PB; ++k) row[k] = x[k];
+}
+
+__device__ __forceinline__ void diag_bar_w06() { asm volatile("bar.sync 3, 224;\n" ::: "memory"); }
+
 // Factor the diagonal tile i of slot d held in shared memory: on entry the lower triangle of
 // Cs[128][LDD] is the Schur complement S_ii (the strict upper part may hold anything finite); on
 // exit L_ii / W_ii are in the slot's side buffers, U_ii in the slot matrix, logdet[i] (and quad,
@@ -54,6 +148,9 @@ __device__ __noinline__ void diag_factor_tile(const SlotDesc& d, int i, double* 
   if (ncol < 0) ncol = 0;
   if (tid == 0) misc[0] = 0.0;
   __syncthreads();
+#ifdef GPSAT_STEP_PHASES
+  long long tdiag = clock64();
+#endif
 
   bool bad = false;
   for (int p = 0; p < NB / PB; ++p) {
@@ -61,6 +158,38 @@ __device__ __noinline__ void diag_factor_tile(const SlotDesc& d, int i, double* 
     int jmax = ncol - c0;
     if (jmax > PB) jmax = PB;
     if (jmax < 0) jmax = 0;
+    if (jmax == PB) {
+      // ---- full panel: warp 0 factors the block; then warp 7 inverts it off the critical path (nothing before the
+      // U sweep below reads W_pp) while warps 0..6 solve the rows below against L_pp and update the trailing block ----
+      if (warp == 0) {
+        double lg = chol32_fast(Cs, c0, colb, wdiag, lane, bad);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) lg += __shfl_xor_sync(0xffffffffu, lg, o);
+        if (lane == 0) misc[0] += lg;
+      }
+      __syncthreads();                 // L_pp and 1 / L_jj visible; warp 7 is done with the previous block's inverse
+      const int nbelow = NB - c0 - PB;
+      if (warp == 7) {
+        inv32(Cs, c0, wdiag, Wp + p * PB * LDP, lane);
+      } else if (nbelow > 0) {
+        if (tid < nbelow) rowsolve32(Cs, c0, wdiag, c0 + PB + tid);
+        diag_bar_w06();
+        const int nf = nbelow / 8;
+        const double* P0 = Cs + (c0 + PB) * LDD + c0;
+        for (int f = warp; f < nf * (nf + 1) / 2; f += 7) {
+          int fr = (int)((sqrtf(8.0f * f + 1.0f) - 1.0f) * 0.5f);
+          while (fr * (fr + 1) / 2 > f) --fr;
+          while ((fr + 1) * (fr + 2) / 2 <= f) ++fr;
+          const int fc = f - fr * (fr + 1) / 2;
+          double* Cg = Cs + (c0 + PB + 8 * fr + lr) * LDD + c0 + PB + 8 * fc + 2 * lk;
+          double2 cv = *reinterpret_cast<double2*>(Cg);
+          frag_nt(cv.x, cv.y, P0 + 8 * fr * LDD, LDD, P0 + 8 * fc * LDD, LDD, PB / 4, lane, -1.0);
+          *reinterpret_cast<double2*>(Cg) = cv;
+        }
+        diag_bar_w06();                // trailing block complete before warp 0 factors the next diagonal block
+      }
+      continue;
+    }
     // ---- (a) warp 0: Cholesky of the 32 x 32 diagonal block, lane = row; then its inverse ----
     if (warp == 0) {
       double a[PB];
@@ -171,6 +300,8 @@ __device__ __noinline__ void diag_factor_tile(const SlotDesc& d, int i, double* 
       __syncthreads();
     }
   }
+  __syncthreads();                       // the last block's inverse (warp 7 on the fast path) is complete
+  DIAG_PHASE(11);
   if (bad && tid == 0) *d.notpd = 1;     // `bad` is only ever set in warp 0 (all lanes agree)
   if (tid == 0) d.logdet[i] = misc[0];
 
@@ -207,6 +338,7 @@ __device__ __noinline__ void diag_factor_tile(const SlotDesc& d, int i, double* 
     __syncthreads();
   }
 
+  DIAG_PHASE(12);
   // ---- write L_ii, W_ii (side buffers) and U_ii = W_ii^T (into the slot matrix) ----
   double* Ld = d.Ld + (size_t)i * NB * NB;
   double* Wd = d.Wd + (size_t)i * NB * NB;
@@ -226,6 +358,7 @@ __device__ __noinline__ void diag_factor_tile(const SlotDesc& d, int i, double* 
   // later trtri tiles and the gradient's K^-1 products read U_ii on the int8 path
   if (d.Uq8 != nullptr)
     slice_tile_udiag(d, ncol, Cs, wdiag, d.Uq8 + (size_t)utile_index(d.T, i, i) * I8L_TILE_B, tid);
+  DIAG_PHASE(13);
 }
 
 // Stand-alone launch: tile (0,0) of every slot (evaluates the covariance itself); the later

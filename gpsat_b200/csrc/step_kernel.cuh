@@ -27,8 +27,8 @@ namespace gpsat {
 
 // cycles per phase of step_kernel summed over CTAs (thread 0's clock), potrf tiles in [0, 16), trtri tiles in
 // [16, 32): 0 prologue, 1 main loop (int8: pass 0), 2 drain 0, 3 pass 1, 4 drain 1, 5 C tile store, 6 covariance,
-// 7 C W^T, 8 stores + slicing, 9 SYRK + Schur update, 10 diagonal factorisation, 15 tiles.  -DGPSAT_STEP_PHASES only.
-__device__ unsigned long long g_step_phase[32];
+// 7 C W^T, 8 stores + slicing, 9 SYRK + Schur update, 10 diagonal factorisation (11 its panel loop, 12 U sweep, 13 stores +
+// slicing), 15 tiles.  -DGPSAT_STEP_PHASES only.  g_step_phase itself is defined in diag_kernel.cuh.
 #ifdef GPSAT_STEP_PHASES
 #define STEP_PHASE(k) do { if (tid == 0) { long long now_ = clock64(); atomicAdd(&g_step_phase[phbase + (k)], (unsigned long long)(now_ - tphase)); tphase = now_; } } while (0)
 #else

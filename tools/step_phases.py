@@ -29,6 +29,8 @@ out = {"gpu_ms": s["gpu_ms"]}
 for kind, base in (("potrf", 0), ("trtri", 16)):
     tiles = max(ph[base + 15], 1)
     o = {k: round(v / tiles / 1.9e3, 2) for k, v in zip(names, ph[base:base + 11])}
+    if base == 0:
+        o.update({k: round(ph[j] / tiles / 1.9e3, 2) for k, j in (("diag_panels", 11), ("diag_u_sweep", 12), ("diag_store_slice", 13))})
     o["tiles"] = ph[base + 15]
     o["sum_us_per_tile"] = round(sum(ph[base:base + 11]) / tiles / 1.9e3, 2)
     out[kind] = o
