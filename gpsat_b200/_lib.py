@@ -26,7 +26,7 @@ EXPORTED_SYMBOLS = (
     "gpsat_version", "gpsat_last_error", "gpsat_device_name", "gpsat_engine_create", "gpsat_engine_destroy",
     "gpsat_engine_stats", "gpsat_engine_stream", "gpsat_engine_set_profile", "gpsat_engine_set_lauum_path", "gpsat_engine_set_step_path",
     "gpsat_engine_i8_timeouts", "gpsat_engine_debug_set_i8_spin_limit", "gpsat_engine_set_precision_rule",
-    "gpsat_engine_precision_rule_default", "gpsat_engine_i8_phases", "gpsat_engine_step_phases", "gpsat_fit_options_default",
+    "gpsat_engine_precision_rule_default", "gpsat_engine_set_precision_low_tier", "gpsat_engine_precision_low_tier_default", "gpsat_engine_i8_phases", "gpsat_engine_step_phases", "gpsat_fit_options_default",
     "gpsat_gpr_lml_grad", "gpsat_gpr_fit", "gpsat_gpr_predict", "gpsat_gpr_predict_cov", "gpsat_gpr_factor_debug",
     "gpsat_sgpr_elbo", "gpsat_sgpr_elbo_gradz", "gpsat_sgpr_predict", "gpsat_sgpr_predict_cov", "gpsat_sgpr_fit",
     "gpsat_vff_elbo", "gpsat_vff_predict", "gpsat_vff_fit",
@@ -99,6 +99,9 @@ def load():
     lib.gpsat_engine_set_precision_rule.argtypes = [vp, C.c_double]
     lib.gpsat_engine_precision_rule_default.argtypes = []
     lib.gpsat_engine_precision_rule_default.restype = C.c_double
+    lib.gpsat_engine_set_precision_low_tier.argtypes = [vp, C.c_double]
+    lib.gpsat_engine_precision_low_tier_default.argtypes = []
+    lib.gpsat_engine_precision_low_tier_default.restype = C.c_double
     lib.gpsat_engine_i8_phases.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
     lib.gpsat_engine_step_phases.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
     lib.gpsat_fit_options_default.argtypes = [C.POINTER(FitOptions)]

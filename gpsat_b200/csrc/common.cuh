@@ -50,6 +50,8 @@ struct SlotDesc {
   int8_t* Lq_mem;        // the slot's plane storage; Lq / Uq8 point at it for evaluations the precision rule admits
   int8_t* Uq8_mem;       //   (slot_set_theta in engine.cu) and are nullptr otherwise: FP64 mma.sync for that evaluation
   double ynorm2;         // |y|^2 (a-priori scale of the observation row of the factor)
+  int i8_low;            // 1: low-rho tier of the precision rule - the int8 k-sums of step_kernel drop their last
+                         //    slice-pair group (slot_set_theta in engine.cu)
   double inv_ls[GPSAT_DMAX];
   double var;            // kernel variance
   double noise;          // likelihood variance

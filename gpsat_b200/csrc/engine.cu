@@ -60,6 +60,7 @@ struct BatchDev {
   const int* order;         // experts sorted by n, descending
   const double* ynorm2;     // [E] |y|^2 per expert
   double i8_rho_max;        // precision rule: int8-sliced k-sums only while (var + noise) / noise <= this (0 = always)
+  double i8_rho_low;        // ... and with one slice-pair group fewer while (var + noise) / noise <= this (0 = never)
 };
 
 struct FitDev {
@@ -190,13 +191,22 @@ __device__ __forceinline__ void slot_set_expert(SlotDesc& d, const SlotMem& mem,
 // themselves the accuracy falls with rho = (var + noise) / noise.  Evaluations with rho above rho_max take the FP64
 // mma.sync loops instead (the FP64 tiles are always stored, so the choice is free per slot and per evaluation).
 // The threshold comes from the measured envelope, profiles/r02_precision_envelope.md.
-__device__ __forceinline__ void slot_set_theta(SlotDesc& d, const double* theta, double rho_max) {
+// Low-rho tier: the same bound argument read the other way - while rho <= rho_low the a-priori scales sit within a few
+// bits of the entries, so the last group of slice pairs (s + t = 7: 2^-49 of the scale product) is below what the
+// north star asks by the margin measured in profiles/r02_low_tier_envelope.md, and the sweep's k-sums run with 28 instead
+// of 36 slice pairs per slab (the gradient's K^-1 products keep their 7 planes: with 6 the gradient error reached 8e-8).
+// c2 / north-star / c3 experts end at rho = 3 .. 35, median 11 (tools/rho_hist.py).
+__device__ __forceinline__ void slot_set_theta(SlotDesc& d, const double* theta, double rho_max, double rho_low) {
   for (int k = 0; k < d.D; ++k) d.inv_ls[k] = 1.0 / theta[k];
   d.var = theta[d.D];
   d.noise = theta[d.D + 1];
   const bool ok = !(rho_max > 0.0) || (d.var + d.noise <= rho_max * d.noise);
   d.Lq = ok ? d.Lq_mem : nullptr;
   d.Uq8 = ok ? d.Uq8_mem : nullptr;
+  // the squared-exponential kernel's matrices are worse conditioned at the same rho (gradient of the n = 2000, rho = 31
+  // sweep case: 4e-8 with the tier, 8e-10 without; 7e-11 at rho = 11), so its tier ends at 3/8 of the threshold (12)
+  const double lim = d.kind == GPSAT_RBF ? 0.375 * rho_low : rho_low;
+  d.i8_low = (lim > 0.0 && d.var + d.noise <= lim * d.noise) ? 1 : 0;
 }
 
 // lml and d lml / d theta from the sweep's by-products (fixed summation order => reproducible)
@@ -231,7 +241,7 @@ __device__ void fit_begin_expert(SlotDesc& d, const SlotMem& mem, LbfgsState& st
     if (f.trainable[q]) x0[np++] = transform_inv(f.tkind[q], f.ta[q], f.tb[q], f.theta[q]);
   }
   lbfgs_init(&st, np, x0);
-  slot_set_theta(d, f.theta + (size_t)e * P, b.i8_rho_max);
+  slot_set_theta(d, f.theta + (size_t)e * P, b.i8_rho_max, b.i8_rho_low);
 }
 
 __global__ void fit_init_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, FitDev f, int S, int ld) {
@@ -342,7 +352,7 @@ __global__ void lbfgs_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev b, F
     else d.expert = -1;
   } else {
     fit_theta_trial(f, st, e, P, theta);
-    slot_set_theta(d, theta, b.i8_rho_max);
+    slot_set_theta(d, theta, b.i8_rho_max, b.i8_rho_low);
     *d.notpd = 0;
     *d.quad = 0.0;
   }
@@ -361,7 +371,7 @@ __global__ void eval_init_kernel(SlotDesc* slots, const SlotMem* mems, BatchDev 
   if (base + s < b.E) {
     int e = b.order[base + s];
     slot_set_expert(slots[s], mems[s], b, e, with_pred, ld);
-    slot_set_theta(slots[s], theta + (size_t)e * b.P, b.i8_rho_max);
+    slot_set_theta(slots[s], theta + (size_t)e * b.P, b.i8_rho_max, b.i8_rho_low);
   } else {
     slots[s].expert = -1;
   }

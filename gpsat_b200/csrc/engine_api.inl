@@ -76,6 +76,15 @@ int gpsat_engine_set_precision_rule(gpsat_engine* h, double rho_max) {
 
 double gpsat_engine_precision_rule_default(void) { return I8_RHO_MAX_DEFAULT; }
 
+int gpsat_engine_set_precision_low_tier(gpsat_engine* h, double rho_low) {
+  REQUIRE(h != nullptr, "engine is NULL");
+  REQUIRE(rho_low >= 0.0, "rho_low must be >= 0 (0 = every int8-sliced k-sum keeps all its slice pairs)");
+  h->e.i8_rho_low = rho_low;
+  return 0;
+}
+
+double gpsat_engine_precision_low_tier_default(void) { return I8_RHO_LOW_DEFAULT; }
+
 void gpsat_fit_options_default(gpsat_fit_options* o) {
   o->pgtol = 1e-5;
   o->ftol = 2.220446049250313e-09;
@@ -120,6 +129,7 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
   if (const char* sp = getenv("GPSAT_B200_STEP")) h->e.i8_step = strcmp(sp, "dmma") != 0;
   if (const char* dp = getenv("GPSAT_B200_DIAGSUM")) h->e.i8_diag_sum = strcmp(dp, "0") != 0;
   if (const char* rp = getenv("GPSAT_B200_RHO_MAX")) h->e.i8_rho_max = std::max(0.0, atof(rp));
+  if (const char* rp = getenv("GPSAT_B200_RHO_LOW")) h->e.i8_rho_low = std::max(0.0, atof(rp));
   h->e.num_sms = prop.multiProcessorCount;
   *out = h;
   return 0;

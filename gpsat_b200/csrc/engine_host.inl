@@ -4,6 +4,7 @@ namespace gpsat {
 // Default of the precision rule (slot_set_theta in engine.cu): the measured envelope behind it is
 // profiles/r02_precision_envelope.md.
 constexpr double I8_RHO_MAX_DEFAULT = 4096.0;
+constexpr double I8_RHO_LOW_DEFAULT = 32.0;
 
 struct DevBuf {
   void* p = nullptr;
@@ -54,6 +55,7 @@ struct Engine {
   bool lauum_planes8 = false;       // set by engine_alloc_slots: lauum_grad_i8_kernel reads d.Uq8
   // precision rule (slot_set_theta in engine.cu): evaluations with (var + noise) / noise above this run on FP64 mma.sync
   double i8_rho_max = I8_RHO_MAX_DEFAULT;
+  double i8_rho_low = I8_RHO_LOW_DEFAULT;
   DevBuf bLq, bUq8, bynorm;
   bool profile = false;
   std::vector<cudaEvent_t> evpool;
@@ -176,6 +178,7 @@ static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with
   }
   out.ynorm2 = nullptr;
   out.i8_rho_max = g.i8_rho_max;
+  out.i8_rho_low = g.i8_rho_low;
   if (g.i8_step && E > 0) {
     if (g.bynorm.ensure(E * 8)) return 1;
     ynorm_kernel<<<(unsigned)E, 128, 0, g.stream>>>(out.off_n, out.y, g.bynorm.as<double>());

@@ -249,7 +249,7 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   const size_t slab_b = planes8 ? (size_t)8 * I8_SLAB_B : (size_t)I8_S * I8_SLAB_B;
   // planes read per value: 7 (2^-49 of the scale) unless the a-priori scale may sit far above the entries of U
   // (|U_rr| = 1 / L_rr >= 1 / sqrt(var + noise) against the bound 1 / sqrt(noise)), then all 8
-  const int S = (planes8 && d.var > 255.0 * d.noise) ? 8 : I8_S;
+  const int S = (planes8 && d.var > 255.0 * d.noise) ? 8 : I8_S;   // (6 planes in the low-rho tier: gradient error 8e-8, not adopted)
   int eu = 0;
   if (planes8) {      // a-priori scale of the sweep's planes: |U| <= 1 / sqrt(noise) (urow_exp in i8slice.cuh)
     double b2 = 1.0 / d.noise;

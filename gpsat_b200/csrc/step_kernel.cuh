@@ -35,6 +35,32 @@ namespace gpsat {
 #define STEP_PHASE(k) do { } while (0)
 #endif
 
+// MMA issue of one pass over k by the calling thread: for every slab all slice pairs (s, t) of the groups s + t = G0 .. G1-1
+// (accumulator g - G0), straight-line code per slab - the group range is a template parameter because a run-time test in
+// front of each tcgen05.mma costs about 20 cycles of the single issuing thread (measured: 0.1 us per slab).
+template <int G0, int G1>
+__device__ __forceinline__ bool i8_issue_pass(int nslabs, int it0, uint32_t full0, uint32_t empty0, uint32_t accb, int pass,
+                                              uint64_t desc0, bool same, uint32_t tb, bool ok) {
+  for (int sl = 0; sl < nslabs; ++sl) {
+    const int itm = it0 + sl, st = itm % I8L_NST;
+    ok = ok && mbar_wait(full0 + 8 * st, (itm / I8L_NST) & 1);
+    if (!ok) break;
+    tc_fence_after();
+    const uint64_t adesc = desc0 + (uint64_t)((st * I8L_STAGE_B) >> 4);
+    const uint64_t bdesc = same ? adesc : adesc + (uint64_t)(I8L_OPER_B >> 4);
+    const uint32_t acc0 = sl == 0 ? 0u : 1u;
+#pragma unroll
+    for (int gg = G0; gg < G1; ++gg)
+#pragma unroll
+      for (int s = 0; s <= gg; ++s)
+        umma_i8(tb + (uint32_t)((gg - G0) * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
+                bdesc + (uint64_t)((gg - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
+    umma_commit(empty0 + 8 * st);
+  }
+  umma_commit(accb);
+  return mbar_wait(accb, pass) && ok;         // only this thread polls; the others sleep in the barrier that follows
+}
+
 // Cs = -sum_{k < i NB} L[rowblk][k] L[i][k]^T on the int8 tensor path (see the header comment).  `pipe` is the
 // 192 KB area that holds Cs and the W stages afterwards.  All 256 threads call it; ends with a CTA barrier.
 // mode I8M_TRTRI: the trtri sum  Cs = +sum_{j NB <= k < i NB} U[rowblk][k] L[i][k]^T  (A planes from d.Uq8).
@@ -80,9 +106,11 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
   for (int q = 0; q < 64; ++q) acc[q] = 0.0;
   bool ok = true;
   STEP_PHASE(0);
+  const int SG = d.i8_low ? I8L_S - 1 : I8L_S;                // slice-pair groups s + t < SG (low-rho tier: 7, planes 0..6)
 #pragma unroll 1
   for (int pass = 0; pass < 2; ++pass) {
-    const int np = pass == 0 ? 4 : I8L_S;                     // planes per operand this pass
+    const int np = pass == 0 ? 4 : SG;                        // planes per operand this pass
+    const int ng = pass == 0 ? 4 : SG - 4;                    // groups accumulated (and drained) this pass
     if (tid == 0) {
       // ---- producer: one bulk copy per operand and slab (tiles (r, 0..i-1) are consecutive in the packing) ----
       for (int sl = 0; sl < nslabs; ++sl) {
@@ -96,27 +124,9 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
       }
     } else if (tid == 32) {
       // ---- MMA issue: all slice pairs of the pass for every slab ----
-      for (int sl = 0; sl < nslabs; ++sl) {
-        const int itm = pass * nslabs + sl, st = itm % I8L_NST;
-        ok = ok && mbar_wait(full0 + 8 * st, (itm / I8L_NST) & 1);
-        if (!ok) break;
-        tc_fence_after();
-        const uint64_t adesc = desc0 + (uint64_t)((st * I8L_STAGE_B) >> 4);
-        const uint64_t bdesc = same ? adesc : adesc + (uint64_t)(I8L_OPER_B >> 4);
-        const uint32_t acc0 = sl == 0 ? 0u : 1u;
-#pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          const int gg = pass * 4 + g;
-#pragma unroll
-          for (int s = 0; s < I8L_S; ++s)
-            if (s <= gg)
-              umma_i8(tb + (uint32_t)(g * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
-                      bdesc + (uint64_t)((gg - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
-        }
-        umma_commit(empty0 + 8 * st);
-      }
-      umma_commit(accb);
-      ok = mbar_wait(accb, pass) && ok;       // only this thread polls; the others sleep in the barrier below
+      if (pass == 0) ok = i8_issue_pass<0, 4>(nslabs, 0, full0, empty0, accb, 0, desc0, same, tb, ok);
+      else if (SG == I8L_S) ok = i8_issue_pass<4, I8L_S>(nslabs, nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
+      else ok = i8_issue_pass<4, I8L_S - 1>(nslabs, nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
     } else if (pass == 0 && xr != nullptr && tid >= 64) {
       // warps 2..7 have nothing to do during the loop: they fetch the coordinates the covariance epilogue needs
       load_block_coords(d, rowblk * NB, xr, yr, tid - 64, GPSAT_THREADS - 64);
@@ -130,20 +140,23 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
     STEP_PHASE(1 + 2 * pass);
     if (ok) {
       // drain: Horner over the four groups of the pass in FP64 (partial sums are integers below 2^53: exact)
-      const double rs = pow2i(exrow - 12 - 7 * (pass * 4 + 3));
+      const double rs = pow2i(exrow - 12 - 7 * (pass * 4 + ng - 1));
 #pragma unroll
       for (int c = 0; c < 64; c += 16) {
         uint32_t v[4][16];
 #pragma unroll
         for (int g = 0; g < 4; ++g)
-          tmem_ld16_nowait(tb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(g * NB + chalf * 64 + c), v[g]);
+          if (g < ng)
+            tmem_ld16_nowait(tb + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)(g * NB + chalf * 64 + c), v[g]);
         tmem_ld_wait();
         double sum[16];
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
-          tmem_ld_fence(v[g]);
+          if (g < ng) {
+            tmem_ld_fence(v[g]);
 #pragma unroll
-          for (int q = 0; q < 16; ++q) sum[q] = g == 0 ? i32_to_f64(v[g][q]) : fma(sum[q], 128.0, i32_to_f64(v[g][q]));
+            for (int q = 0; q < 16; ++q) sum[q] = g == 0 ? i32_to_f64(v[g][q]) : fma(sum[q], 128.0, i32_to_f64(v[g][q]));
+          }
         }
 #pragma unroll
         for (int q = 0; q < 16; ++q) acc[c + q] = fma(sum[q] * rs, csd[chalf * 64 + c + q], acc[c + q]);

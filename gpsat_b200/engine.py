@@ -203,6 +203,13 @@ class Engine:
             rho_max = float(self._lib.gpsat_engine_precision_rule_default())
         _lib.check(self._lib.gpsat_engine_set_precision_rule(self._h, float(rho_max or 0.0)))
 
+    def set_precision_low_tier(self, rho_low=True):
+        """Low-rho tier of the precision rule: while ``(var + noise) / noise <= rho_low`` the int8-sliced k-sums drop
+        their last slice-pair group.  ``True`` = the library default, ``False`` / 0 = tier off."""
+        if rho_low is True:
+            rho_low = float(self._lib.gpsat_engine_precision_low_tier_default())
+        _lib.check(self._lib.gpsat_engine_set_precision_low_tier(self._h, float(rho_low or 0.0)))
+
     @property
     def stream_ptr(self) -> int:
         """cudaStream_t of the engine (wrap with torch.cuda.ExternalStream to record events on it)."""

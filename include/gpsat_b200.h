@@ -159,6 +159,13 @@ int gpsat_engine_set_step_path(gpsat_engine* eng, int path);
  * (gpflow_models.py:404-411), i.e. rho up to 1e7 is reachable through the reference's API. */
 int gpsat_engine_set_precision_rule(gpsat_engine* eng, double rho_max);
 double gpsat_engine_precision_rule_default(void);
+/* Low-rho tier of the same rule (no counterpart in the reference): while rho <= rho_low the a-priori scales sit within
+ * a few bits of the entries, and the k-sums of the Cholesky / inverse sweep drop their last group of slice pairs
+ * (2^-49 of the scale product; 28 instead of 36 int8 MMAs per 32-wide slab).  The squared-exponential kernel uses
+ * 3/8 of rho_low (its matrices are worse conditioned at equal rho).  rho_low = 0 turns the tier off.  Default gpsat_engine_precision_low_tier_default() from the same envelope
+ * measurement; the environment variable GPSAT_B200_RHO_LOW overrides it at engine creation. */
+int gpsat_engine_set_precision_low_tier(gpsat_engine* eng, double rho_low);
+double gpsat_engine_precision_low_tier_default(void);
 /* A bounded barrier wait of the int8 tensor pipeline that gives up makes the call that ran it FAIL (non-zero
  * return, gpsat_last_error() says so; per-expert outputs of that call must not be used).  out = number of calls
  * that failed that way since the engine was created. */

@@ -31,7 +31,24 @@ def one(kind, X, y, Xs, theta):
     return ref, np.array([e["lml"], e["grad"], e["fmean"], e["fvar"]])
 
 
+def low_tier():
+    """tests/golden/low_tier_envelope.npz: the cases at and below the threshold of the precision rule's low-rho tier."""
+    out = {}
+    t0 = time.time()
+    for c in env.low_tier_cases():
+        X, y, Xs, theta = env.make_case(c)
+        ref, f64 = one(c["kind"], X, y, Xs, theta)
+        for k, v in ref.items():
+            out[f"{c['name']}/{k}"] = np.asarray(v)
+        out[f"{c['name']}/f64_err"] = f64
+        print(f"{c['name']:32s} lml {ref['lml']:.12e}  float64 oracle err: lml {f64[0]:.1e} grad {f64[1]:.1e} "
+              f"f* {f64[2]:.1e} f*_var {f64[3]:.1e}   [{time.time() - t0:.0f} s]", flush=True)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", "low_tier_envelope.npz"), **out)
+
+
 def main():
+    if "--low-tier" in sys.argv:
+        return low_tier()
     out = {}
     t0 = time.time()
     for c in env.cases():

@@ -138,3 +138,20 @@ def make_vff_case(c):
     ms = [np.arange(k) for k in c["nfreq"]]
     theta = np.array([*c["ell"], *c["var"], c["noise"]])
     return X, y, Xs, a, b, ms, theta
+
+
+# ---- low-rho tier of the precision rule: rho up to the tier's threshold 32, and one case outside -------
+LOW_TIER = ((0.1, 1.0), (0.5, 5.0), (0.033, 1.0), (0.0033, 0.1), (0.02, 1.0))      # (noise, var): rho 11, 11, 31.3, 31.3, 51
+
+
+LOW_TIER_KINDS = ("Matern32", "RBF", "Matern12", "Matern52")
+
+
+def low_tier_cases():
+    out = []
+    for kind in LOW_TIER_KINDS:
+        for n in (1000, 2000) if kind in KINDS else (2000,):
+            for noise, var in LOW_TIER:
+                out.append(dict(name=f"low-{kind}-n{n}-s{noise:g}-v{var:g}", kind=kind, n=n, noise=noise, var=var, dup=0.10, D=3,
+                                seed=1000 + len(out)))
+    return out

@@ -38,10 +38,20 @@ def test_factor_matches_numpy(engine, n):
     rng = np.random.default_rng(n)
     X, y, _ = _expert(rng, n, 3)
     th = _theta(rng, 3)
-    L, U = engine.factor_debug("Matern32", X, y, th)
     Ks = gpr.kernel_matrix("Matern32", X, None, th[:3], th[3]) + th[4] * np.eye(n)
     Lr = np.linalg.cholesky(Ks)
     a = np.linalg.solve(Lr, y)
+    # default configuration: the low-rho tier of the precision rule (one slice-pair group fewer) is active at
+    # these hyper-parameters for n > 128; the observation row of the factor, whose a-priori scale |y| / sigma_n is the
+    # loosest, shows it first
+    L, U = engine.factor_debug("Matern32", X, y, th)
+    np.testing.assert_allclose(L[:n, :n], Lr, rtol=0, atol=1e-11 * np.abs(Lr).max())
+    np.testing.assert_allclose(L[n, :n], a, rtol=0, atol=1e-9 * max(1.0, np.abs(a).max()))
+    try:                                   # all slice pairs: the factor to 1e-12 of its largest entry
+        engine.set_precision_low_tier(False)
+        L, U = engine.factor_debug("Matern32", X, y, th)
+    finally:
+        engine.set_precision_low_tier(True)
     np.testing.assert_allclose(L[:n, :n], Lr, rtol=0, atol=1e-12 * np.abs(Lr).max())
     np.testing.assert_allclose(L[n, :n], a, rtol=0, atol=1e-11 * max(1.0, np.abs(a).max()))
     assert L[n, n] == 1.0
@@ -421,6 +431,7 @@ def test_i8_step_path_matches_dmma_path(engine, kind, D, noise):
         for name, path, rule in (("dmma", "dmma", False), ("i8", "i8", False), ("default", "i8", True)):
             engine.set_step_path(path)
             engine.set_precision_rule(rule)
+            engine.set_precision_low_tier(rule)            # "i8": all 36 slice pairs on every slot
             lml, g, st = engine.lml_grad(b, theta)
             p = engine.predict(b, theta)
             L, U = engine.factor_debug(kind, experts[3][0], experts[3][1], theta[3])
@@ -428,6 +439,7 @@ def test_i8_step_path_matches_dmma_path(engine, kind, D, noise):
     finally:
         engine.set_step_path("i8")
         engine.set_precision_rule(True)
+        engine.set_precision_low_tier(True)
     assert engine.i8_timeouts() == t0
     (lml0, g0, st0, p0, L0, U0), (lml1, g1, st1, p1, L1, U1) = out["dmma"], out["i8"]
     lml2, g2, st2, p2, _, _ = out["default"]
@@ -436,8 +448,12 @@ def test_i8_step_path_matches_dmma_path(engine, kind, D, noise):
     rho = (theta[:, D] + theta[:, D + 1]) / theta[:, D + 1]
     from gpsat_b200 import _lib
     rho_max = _lib.load().gpsat_engine_precision_rule_default()
+    rho_low = _lib.load().gpsat_engine_precision_low_tier_default()
     for e in range(len(ns)):                               # the rule picks the path per expert
-        assert lml2[e] == (lml1[e] if rho[e] <= rho_max else lml0[e])
+        if rho[e] <= rho_low:                              # low tier: 28 of the 36 slice pairs
+            assert abs(lml2[e] - lml1[e]) <= 1e-9 * abs(lml1[e])
+        else:
+            assert lml2[e] == (lml1[e] if rho[e] <= rho_max else lml0[e])
     # factor of the 257-observation expert: elementwise against the row scales the slicing uses
     np.testing.assert_allclose(L1, L0, rtol=0, atol=1e-12 * np.abs(L0).max())
     np.testing.assert_allclose(U1, U0, rtol=0, atol=1e-10 * np.abs(U0).max())
@@ -523,6 +539,49 @@ def test_i8_precision_envelope(engine, golden_dir, kind):
         tol = dict(lml=1e-8, grad=max(1e-7, 2e-13 * rho), fmean=1e-8, fvar=1e-8)
         if st[k] != 0 or any(not (e[q] <= tol[q]) for q in tol):
             bad.append((c["name"], int(st[k]), e, tol))
+    assert not bad, bad
+
+
+@pytest.mark.parametrize("kind", ["Matern32", "RBF", "Matern12", "Matern52"])
+def test_i8_low_tier_envelope(engine, golden_dir, kind):
+    """Low-rho tier of the precision rule (slot_set_theta in engine.cu: while rho = (var + noise) / noise <= 32 - 12 for
+    the squared-exponential kernel - the int8-sliced k-sums of the sweep drop their last slice-pair group: 28 instead of
+    36 MMAs per 32-wide slab) against extended precision at rho = 11 and 31.3 (just below the threshold) and 51
+    (outside: tier on == tier off), n = 1000 and 2000, 10 % duplicate rows, all four kernels: held to a TENTH of the
+    north star's tolerances (1e-9 on LML and predictions, 1e-8 on the gradient), so that the tier keeps a margin of 10
+    at its own edge.  The same cases with the tier switched off are written beside them to
+    gpurun_out/low_tier_envelope.json (profiles/r02_low_tier_envelope.md)."""
+    import json
+    import os
+    import envelope as env
+    gold = np.load(os.path.join(golden_dir, "low_tier_envelope.npz"))
+    cs = [c for c in env.low_tier_cases() if c["kind"] == kind]
+    items = [env.make_case(c) for c in cs]
+    runs = {}
+    try:
+        for name, tier in (("tier_on", True), ("tier_off", False)):
+            engine.set_precision_low_tier(tier)
+            runs[name] = _envelope_run(engine, cs, items, kind)
+    finally:
+        engine.set_precision_low_tier(True)
+    rows, bad = [], []
+    for k, c in enumerate(cs):
+        ref = {q: gold[f"{c['name']}/{q}"] for q in ("lml", "grad", "fmean", "fvar")}
+        ref["lml"] = float(ref["lml"])
+        row = dict(case=c["name"], rho=(c["var"] + c["noise"]) / c["noise"])
+        for name, (lml, grad, st, p, off) in runs.items():
+            sl = slice(off[k], off[k + 1])
+            row[name] = env.rel_errors(lml[k], grad[k], p["f*"][sl], p["f*_var"][sl], ref, items[k][3])
+            row[name]["status"] = int(st[k])
+        rows.append(row)
+        e = row["tier_on"]
+        tol = dict(lml=1e-9, grad=1e-8, fmean=1e-9, fvar=1e-9)
+        if e["status"] != 0 or any(not (e[q] <= tol[q]) for q in tol):
+            bad.append(row)
+    os.makedirs("gpurun_out", exist_ok=True)
+    path = os.path.join("gpurun_out", "low_tier_envelope.json")
+    prev = json.load(open(path)) if os.path.exists(path) else []
+    json.dump([r for r in prev if not r["case"].startswith(f"low-{kind}-")] + rows, open(path, "w"), indent=1)
     assert not bad, bad
 
 
