@@ -125,6 +125,18 @@ __device__ __forceinline__ double i32_to_f64(uint32_t v) {
 }
 __device__ __forceinline__ double pow2i(int p) { return __longlong_as_double((long long)(p + 1023) << 52); }
 
+// all slice pairs (s, t) of the groups s + t = G0 .. G1-1 of one 32-wide slab into the accumulators g - G0
+template <int G0, int G1>
+__device__ __forceinline__ void i8_issue_groups(uint32_t tb, uint64_t adesc, uint64_t bdesc, uint32_t acc0) {
+#pragma unroll
+  for (int g = G0; g < G1; ++g)
+#pragma unroll
+    for (int s = 0; s <= g; ++s)
+      if (s < G1 && g - s < G1)
+        umma_i8(tb + (uint32_t)((g - G0) * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
+                bdesc + (uint64_t)((g - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
+}
+
 // index of tile (j, k), k >= j, in the packed upper block triangle
 __device__ __forceinline__ int utile_index(int T, int j, int k) { return j * T - j * (j - 1) / 2 + (k - j); }
 __device__ __forceinline__ int lauum_kend(int n) { return ((n + 1 + KC - 1) / KC) * KC; }
@@ -313,22 +325,11 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
           const uint64_t adesc = desc0 + (uint64_t)((st * I8_STAGE_B) >> 4);
           const uint64_t bdesc = same ? adesc : adesc + (uint64_t)((I8_SP * I8_SLAB_B) >> 4);
           const uint32_t acc0 = first ? 0u : 1u;
-          if (pass == 0) {
-#pragma unroll
-            for (int g = 0; g < 4; ++g)
-#pragma unroll
-              for (int s = 0; s <= g; ++s)
-                umma_i8(tb + (uint32_t)(g * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
-                        bdesc + (uint64_t)((g - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
-          } else {
-#pragma unroll
-            for (int g = 4; g < I8_SP; ++g)
-#pragma unroll
-              for (int s = 0; s <= g; ++s)
-                if (g < S && s < S && g - s < S)
-                  umma_i8(tb + (uint32_t)((g - 4) * NB), adesc + (uint64_t)(s * (I8_SLAB_B >> 4)),
-                          bdesc + (uint64_t)((g - s) * (I8_SLAB_B >> 4)), s == 0 ? acc0 : 1u);
-          }
+          // straight-line issue per slab: the plane count is resolved outside (a run-time test in front of each
+          // tcgen05.mma costs the issuing thread about 20 cycles, see i8_issue_pass in step_kernel.cuh)
+          if (pass == 0) i8_issue_groups<0, 4>(tb, adesc, bdesc, acc0);
+          else if (S == 8) i8_issue_groups<4, 8>(tb, adesc, bdesc, acc0);
+          else i8_issue_groups<4, I8_S>(tb, adesc, bdesc, acc0);
           umma_commit(empty0 + 8 * st);
           first = false;
         }
