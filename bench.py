@@ -553,6 +553,14 @@ def run_ours(args):
             extra["c4_96_predict_only"] = run_extra("c4", replace(syn.WORKLOADS["c4"], E=96), world, rank, local, dist, flush, passes=3)
             extra["c5_8_sgpr"] = run_extra("c5", replace(syn.WORKLOADS["c5"], E=8), world, rank, local, dist, flush)
             extra["c1"] = run_extra("c1", syn.WORKLOADS["c1"], world, rank, local, dist, flush, passes=3)
+            # Matern-3/2 is the headline; the other kernels of the plugin as a sweep at c2
+            sweep = {}
+            for kind in ("Matern12", "Matern52", "RBF"):
+                r = run_extra("c2", replace(syn.WORKLOADS["c2"], kernel=kind), world, rank, local, dist, flush)
+                sweep[kind] = {k: r[k] for k in ("value", "unit", "seconds_per_pass", "e2e_value", "whole_job_frac", "evals_all_ranks")}
+                sweep[kind]["status_counts"] = r["rank0"]["status_counts"]
+                sweep[kind]["step_kernel_frac"] = r["rank0"]["step_kernel_frac"]
+            extra["c2_kernel_sweep"] = sweep
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,

@@ -154,4 +154,7 @@ def low_tier_cases():
             for noise, var in LOW_TIER:
                 out.append(dict(name=f"low-{kind}-n{n}-s{noise:g}-v{var:g}", kind=kind, n=n, noise=noise, var=var, dup=0.10, D=3,
                                 seed=1000 + len(out)))
+    for noise, var in ((0.1, 1.0), (0.033, 1.0)):          # the largest c3 experts: 32 tile columns
+        out.append(dict(name=f"low-Matern32-n4000-s{noise:g}-v{var:g}", kind="Matern32", n=4000, noise=noise, var=var, dup=0.10,
+                        D=3, seed=1000 + len(out)))
     return out
