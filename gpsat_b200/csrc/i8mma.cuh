@@ -97,6 +97,14 @@ __device__ __forceinline__ void bulk_g2s(uint32_t dst, const void* src, uint32_t
   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n"
                :: "r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
+// one lane of a converged warp (elect.sync): inside `if (warp == w)` the compiler then knows that a single lane runs the
+// branch and keeps descriptors / addresses in uniform registers, instead of wrapping every tcgen05.mma in an
+// elect / broadcast / branch loop as it does under `if (tid == t)`
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}\n" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" :: "r"(dst_smem), "r"(ncols) : "memory");
   asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
@@ -293,9 +301,10 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
   for (int pass = 0; pass < 2; ++pass) {
     const int np = pass == 0 ? 4 : S;                         // planes per operand this pass
     const int g0 = pass * 4, g1 = min(g0 + 4, S);             // groups s + t = g of this pass
-    if (tid == 0) {
+    if (warp == 0) {
       // ---- producer: bulk copies of the slab planes ----
       int itp = it;
+      if (elect_one())
       for (int kb = i; kb < T && ok; ++kb) {
         const int8_t* ga = Ubase + (size_t)utile_index(T, i, kb) * tile_b;
         const int8_t* gb = Ubase + (size_t)utile_index(T, j, kb) * tile_b;
@@ -310,8 +319,8 @@ __global__ void __launch_bounds__(GPSAT_THREADS, 1) lauum_grad_i8_kernel(const S
           if (!same) bulk_g2s(sbase + I8_SP * I8_SLAB_B, gb + (size_t)sl * slab_b, np * I8_SLAB_B, fb);
         }
       }
-    } else if (tid == 32) {
-      // ---- MMA issue: all slice pairs of the pass for every slab ----
+    } else if (warp == 1 && elect_one()) {
+      // ---- MMA issue: all slice pairs of the pass for every slab (one elected lane of a converged warp, see elect_one) ----
       int itm = it;
       bool first = true;
       for (int kb = i; kb < T && ok; ++kb) {

@@ -111,8 +111,9 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
   for (int pass = 0; pass < 2; ++pass) {
     const int np = pass == 0 ? 4 : SG;                        // planes per operand this pass
     const int ng = pass == 0 ? 4 : SG - 4;                    // groups accumulated (and drained) this pass
-    if (tid == 0) {
+    if (warp == 0) {
       // ---- producer: one bulk copy per operand and slab (tiles (r, 0..i-1) are consecutive in the packing) ----
+      if (elect_one())
       for (int sl = 0; sl < nslabs; ++sl) {
         const int itp = pass * nslabs + sl, st = itp % I8L_NST;
         if (itp >= I8L_NST) ok = ok && mbar_wait(empty0 + 8 * st, ((itp / I8L_NST) - 1) & 1);
@@ -122,11 +123,13 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
         bulk_g2s(sbase, ga0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
         if (!same) bulk_g2s(sbase + I8L_OPER_B, gb0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
       }
-    } else if (tid == 32) {
+    } else if (warp == 1) {
       // ---- MMA issue: all slice pairs of the pass for every slab ----
-      if (pass == 0) ok = i8_issue_pass<0, 4>(nslabs, 0, full0, empty0, accb, 0, desc0, same, tb, ok);
-      else if (SG == I8L_S) ok = i8_issue_pass<4, I8L_S>(nslabs, nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
-      else ok = i8_issue_pass<4, I8L_S - 1>(nslabs, nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
+      if (elect_one()) {
+        if (pass == 0) ok = i8_issue_pass<0, 4>(nslabs, 0, full0, empty0, accb, 0, desc0, same, tb, ok);
+        else if (SG == I8L_S) ok = i8_issue_pass<4, I8L_S>(nslabs, nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
+        else ok = i8_issue_pass<4, I8L_S - 1>(nslabs, nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
+      }
     } else if (pass == 0 && xr != nullptr && tid >= 64) {
       // warps 2..7 have nothing to do during the loop: they fetch the coordinates the covariance epilogue needs
       load_block_coords(d, rowblk * NB, xr, yr, tid - 64, GPSAT_THREADS - 64);
