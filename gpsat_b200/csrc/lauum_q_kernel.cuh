@@ -66,7 +66,7 @@ lauum_grad_i8q_kernel(const SlotDesc* __restrict__ slots, int S, int ntile_max, 
 
   if (warp == 8) {
     // ---- producer ----
-    if (lane == 0) {
+    if (elect_one()) {
       int it = 0;
       for (int w = blockIdx.x; w < W && ok; w += gridDim.x) {
         int slot, t, i, j;
@@ -98,7 +98,7 @@ lauum_grad_i8q_kernel(const SlotDesc* __restrict__ slots, int S, int ntile_max, 
     __syncwarp();
   } else if (warp == 9) {
     // ---- MMA issue ----
-    if (lane == 0) {
+    if (elect_one()) {
       const uint64_t desc0 = umma_desc_kmajor(pipe_s, NB * 16, 128);
       int it = 0, npass = 0;
       for (int w = blockIdx.x; w < W && ok; w += gridDim.x) {
