@@ -106,37 +106,69 @@ def arithmetic_note():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md recipe: `-lms 200`).
+
+    One nvidia-smi process per bench process, started before the warm-up steps and read by a thread that stamps every
+    line with its arrival time; a timed region is the slice [start(), stop()] of that stream.  (Starting nvidia-smi at
+    the top of every timed region put its start-up - NVML initialisation under the driver lock, 0.1 s - inside the first
+    timed step: visible as a doubled time per pass on the 40 ms c1 passes.)"""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    _shared = {}
+
+    @classmethod
+    def get(cls, index):
+        if index not in cls._shared:
+            cls._shared[index] = cls(index)
+        return cls._shared[index]
 
     def __init__(self, index):
-        self.lines, self.proc = [], None
+        self.lines, self.proc, self.t0 = [], None, None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", f"--id={index}", f"--query-gpu={self.Q}",
                                           "--format=csv,noheader,nounits", "-lms", "200"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
+            import atexit
+            atexit.register(self.close)
         except Exception:
             self.proc = None
 
     def _read(self):
         for line in self.proc.stdout:
-            self.lines.append(line.strip())
+            self.lines.append((time.time(), line.strip()))
+
+    def close(self):
+        if self.proc is not None and self.proc.poll() is None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+
+    def start(self):
+        self.t0 = time.time()
+        return self
 
     def stop(self):
+        """Summary of the samples that arrived since start(); a region shorter than the sampling interval takes the
+        first sample after it (waits up to 0.5 s for one)."""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=2)
-        except Exception:
-            self.proc.kill()
+        t1 = time.time()
+        sel = [ln for (ts, ln) in list(self.lines) if self.t0 <= ts <= t1]
+        if not sel:
+            deadline = time.time() + 0.5
+            while time.time() < deadline and not any(ts > t1 for ts, _ in list(self.lines)):
+                time.sleep(0.02)
+            after = [ln for (ts, ln) in list(self.lines) if ts > t1]
+            before = [ln for (ts, ln) in list(self.lines) if ts < self.t0]
+            sel = after[:1] or before[-1:]
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ln in self.lines:
+        for ln in sel:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue
@@ -335,12 +367,13 @@ def timed_region(job, steps, warmup, flush, dist, world):
             dist.barrier()
         torch.cuda.synchronize()
 
+    sampler = ClockSampler.get(job.local)          # running before the warm-up, so that its start-up is outside the timed region
     for _ in range(warmup):
         job.step_device(flush)
     job.eng.set_profile(True)
     collect = {"fit": [], "predict": []}
     barrier()
-    clocks = ClockSampler(job.local)
+    clocks = sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record(job.stream)
     res = pred = None
