@@ -39,8 +39,10 @@ __device__ __forceinline__ int urow_exp(const SlotDesc& d) {
 // Split the 128 x 128 tile val(r, c) * 2^(6 - e) into I8L_S exact int8 slice planes (see i8mma.cuh for the
 // rounding trick) and store them in the K-major UMMA layout [slab][plane][k / 16][row][16 B].  Two threads per
 // row; sc(r) = 2^(6 - e_r).
+// ns: planes to produce (I8L_S, or I8L_S - 1 for slots in the low-rho tier, whose consumers read planes 0..6 only - the
+// tier is a property of the slot's current evaluation, so producer and consumers always agree).
 template <typename FV, typename FS>
-__device__ __forceinline__ void slice_tile_f(FV val, FS sc_of_row, int8_t* planes, int tid) {
+__device__ __forceinline__ void slice_tile_f(FV val, FS sc_of_row, int8_t* planes, int tid, int ns = I8L_S) {
   const int r = tid >> 1, h = tid & 1;
   const double sc = sc_of_row(r);
   double magic[I8L_S];
@@ -54,6 +56,7 @@ __device__ __forceinline__ void slice_tile_f(FV val, FS sc_of_row, int8_t* plane
     for (int q = 0; q < 32; ++q) x[q] = val(r, c0 + q) * sc;
 #pragma unroll
     for (int s = 0; s < I8L_S; ++s) {
+      if (s >= ns) break;
 #pragma unroll
       for (int ch = 0; ch < 2; ++ch) {
         uint32_t w[4];
@@ -80,7 +83,7 @@ __device__ __forceinline__ void slice_tile_f(FV val, FS sc_of_row, int8_t* plane
 // The tile held in Cs ([128][LDC]) as a tile of L (per-row scales of rows g0r ..).
 __device__ __forceinline__ void slice_tile_l(const SlotDesc& d, int g0r, const double* Cs, int8_t* planes, int tid) {
   slice_tile_f([&](int r, int c) { return Cs[r * LDC + c]; },
-               [&](int r) { return pow2i(6 - lrow_exp(d, g0r + r)); }, planes, tid);
+               [&](int r) { return pow2i(6 - lrow_exp(d, g0r + r)); }, planes, tid, d.i8_low ? I8L_S - 1 : I8L_S);
 }
 
 // The tile held in Cs as tile (.., column block at g0c) of U: one scale; columns >= n (the -alpha column of the
@@ -88,7 +91,8 @@ __device__ __forceinline__ void slice_tile_l(const SlotDesc& d, int g0r, const d
 __device__ __forceinline__ void slice_tile_u(const SlotDesc& d, int g0c, const double* Cs, int8_t* planes, int tid) {
   const double sc = pow2i(6 - urow_exp(d));
   const int ncol = d.n - g0c;
-  slice_tile_f([&](int r, int c) { return c < ncol ? Cs[r * LDC + c] : 0.0; }, [&](int) { return sc; }, planes, tid);
+  slice_tile_f([&](int r, int c) { return c < ncol ? Cs[r * LDC + c] : 0.0; }, [&](int) { return sc; }, planes, tid,
+               d.i8_low ? I8L_S - 1 : I8L_S);
 }
 
 // Diagonal tile U_ii = W_ii^T after diag_factor_tile: strict upper part in Cs, diagonal in wdiag, zero below;
@@ -97,7 +101,7 @@ __device__ __forceinline__ void slice_tile_udiag(const SlotDesc& d, int ncol, co
                                                  int8_t* planes, int tid) {
   const double sc = pow2i(6 - urow_exp(d));
   slice_tile_f([&](int r, int c) { return c >= ncol ? 0.0 : (c > r ? Cs[r * LDC + c] : (c == r ? wdiag[r] : 0.0)); },
-               [&](int) { return sc; }, planes, tid);
+               [&](int) { return sc; }, planes, tid, d.i8_low ? I8L_S - 1 : I8L_S);
 }
 
 }  // namespace gpsat
