@@ -50,6 +50,9 @@ struct SlotDesc {
   int8_t* Lq_mem;        // the slot's plane storage; Lq / Uq8 point at it for evaluations the precision rule admits
   int8_t* Uq8_mem;       //   (slot_set_theta in engine.cu) and are nullptr otherwise: FP64 mma.sync for that evaluation
   double ynorm2;         // |y|^2 (a-priori scale of the observation row of the factor)
+  int skip_fp64;         // 1: every consumer of this slot's off-diagonal L / U tiles reads the int8 planes (sweep and K^-1
+                         //    products on the planes, no debug extraction), so step_kernel does not store the FP64 tiles of
+                         //    block rows / columns that lie entirely among the observations
   int i8_low;            // 1: low-rho tier of the precision rule - the int8 k-sums of step_kernel drop their last
                          //    slice-pair group (slot_set_theta in engine.cu)
   double inv_ls[GPSAT_DMAX];

@@ -61,6 +61,7 @@ struct BatchDev {
   const double* ynorm2;     // [E] |y|^2 per expert
   double i8_rho_max;        // precision rule: int8-sliced k-sums only while (var + noise) / noise <= this (0 = always)
   double i8_rho_low;        // ... and with one slice-pair group fewer while (var + noise) / noise <= this (0 = never)
+  int skip_fp64;            // see SlotDesc::skip_fp64 (set by the host after engine_alloc_slots)
 };
 
 struct FitDev {
@@ -182,6 +183,7 @@ __device__ __forceinline__ void slot_set_expert(SlotDesc& d, const SlotMem& mem,
   d.pre = nullptr; d.pre_s = nullptr; d.ldpre = 0;
   d.Uq = mem.Uq; d.uex = mem.uex;
   d.Lq = d.Lq_mem = mem.Lq; d.Uq8 = d.Uq8_mem = mem.Uq8; d.ynorm2 = b.ynorm2 ? b.ynorm2[e] : 0.0;
+  d.skip_fp64 = b.skip_fp64;
   *d.notpd = 0;
   *d.quad = 0.0;
 }

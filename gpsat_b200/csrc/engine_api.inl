@@ -209,6 +209,7 @@ int gpsat_gpr_lml_grad(gpsat_engine* h, const gpsat_batch* batch, int mem, const
   const int S = choose_slots(g, E, g.Tmax, g.Tmax, 0);
   int ld = 0;
   if (engine_alloc_slots(g, S, g.Tmax, g.Tmax, ld, grad != nullptr)) return 1;
+  bd.skip_fp64 = g.lauum_planes8 ? 1 : 0;       // the gradient's K^-1 products read the sweep's planes: FP64 tiles unread
   // device-side theta / outputs
   size_t o_theta = 0, o_lml = (size_t)E * P * 8, o_grad = o_lml + (size_t)E * 8, o_status = o_grad + (size_t)E * P * 8;
   if (g.bout.ensure(o_status + (size_t)E * 4)) return 1;
@@ -259,6 +260,7 @@ static int predict_impl(gpsat_engine* h, const gpsat_batch* batch, int mem, cons
   const int S = choose_slots(g, E, g.Tmax, g.TRmax, 0);
   int ld = 0;
   if (engine_alloc_slots(g, S, g.Tmax, g.TRmax, ld, false)) return 1;
+  bd.skip_fp64 = 1;                              // prediction pass: only the rows from the observation row on are read back
   size_t o_theta = 0, o_lml = (size_t)E * P * 8, o_status = o_lml + (size_t)E * 8;
   size_t o_pred = (o_status + (size_t)E * 4 + 15) & ~(size_t)15;
   if (g.bout.ensure(o_pred + (size_t)std::max<int64_t>(M, 1) * 3 * 8)) return 1;

@@ -84,6 +84,7 @@ int gpsat_gpr_fit(gpsat_engine* h, const gpsat_batch* batch, int mem, double* th
   const int S = choose_slots(g, E, g.Tmax, g.Tmax, opt.max_slots);
   int ld = 0;
   if (engine_alloc_slots(g, S, g.Tmax, g.Tmax, ld)) return 1;
+  bd.skip_fp64 = g.lauum_planes8 ? 1 : 0;
 
   FitDev fd;
   if (fit_stage(g, mem, E, P, S, theta_io, tkind, ta, tb, trainable, opt, priors, objective, lml, n_evals, n_iters,

@@ -179,6 +179,7 @@ static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with
   out.ynorm2 = nullptr;
   out.i8_rho_max = g.i8_rho_max;
   out.i8_rho_low = g.i8_rho_low;
+  out.skip_fp64 = 0;
   if (g.i8_step && E > 0) {
     if (g.bynorm.ensure(E * 8)) return 1;
     ynorm_kernel<<<(unsigned)E, 128, 0, g.stream>>>(out.off_n, out.y, g.bynorm.as<double>());

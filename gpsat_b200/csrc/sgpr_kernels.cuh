@@ -93,7 +93,7 @@ __device__ __forceinline__ void sgpr_fill_slot(SlotDesc& s, int expert, int M, i
   s.gpart = nullptr;
   s.notpd = reinterpret_cast<int*>(s.quad + 2);
   s.pre = nullptr; s.pre_s = nullptr; s.ldpre = 0;
-  s.Uq = nullptr; s.uex = nullptr; s.Lq = nullptr; s.Uq8 = nullptr; s.ynorm2 = 0.0; s.i8_low = 0;
+  s.Uq = nullptr; s.uex = nullptr; s.Lq = nullptr; s.Uq8 = nullptr; s.ynorm2 = 0.0; s.i8_low = 0; s.skip_fp64 = 0;
   s.Xs = nullptr;
 }
 

@@ -302,7 +302,11 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv, int S, int nt
   if (tid == 0) atomicAdd(&g_step_phase[phbase + 15], 1ull);
 #endif
   const double sign = is_pot ? 1.0 : -1.0;
-  {
+  // FP64 copy of the tile: read back only by the FP64 mma.sync loops (this slot is not on them in this evaluation), by the
+  // FP64 K^-1 kernel / the debug extraction (skip_fp64 = 0 then), and - rows from the observation row n on, column block of
+  // column n - by the prediction reduction and the alpha column of the gradient.  Everything else reads the planes.
+  const bool dead = d.skip_fp64 && use_i8 && (is_pot ? (rowblk + 1) * NB <= d.n : (d.Uq8 != nullptr && (i + 1) * NB <= d.n));
+  if (!dead) {
     double* Og = d.A + ((size_t)rowblk * NB + 16 * strip + lr) * ld + (size_t)i * NB + 2 * lk;
 #pragma unroll
     for (int rf = 0; rf < 2; ++rf)
