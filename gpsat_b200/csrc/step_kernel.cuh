@@ -350,6 +350,23 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv, int S, int nt
   // so the other tiles of the block row neither update nor touch S_rr.
   const bool diag_i8 = diag_sum && d.Lq != nullptr;
   if (!syrk || (diag_i8 && x != 0)) return;
+  if (x == 0 && i > 0 && diag_i8) {
+    // ---- 5 (int8 path). rowblk == i + 1: the Schur complement of the next diagonal tile in one go, -sum_{k <= i} L_rk L_rk^T
+    // over the planes of block row r INCLUDING the tile this CTA has just sliced (it is the next tile of the packing, so the
+    // slab stream simply runs four slabs further) - no FP64 SYRK of the own tile, nothing parked in the slot matrix.  The
+    // planes were written through the generic proxy and are read back by bulk copies: fence both ways first.
+    __threadfence();
+    asm volatile("fence.proxy.async;\n" ::: "memory");
+    __syncthreads();
+    potrf_mainloop_i8(d, rowblk, i + 1, reinterpret_cast<unsigned char*>(smem), Cs, bars, &tmem_slot, csd, tid, I8M_DIAG,
+                      false, true, tphase, phbase);
+    add_aug_tile(d, rowblk * NB, rowblk * NB, xr, xr, yr, Cs, tid, true);
+    __syncthreads();
+    STEP_PHASE(9);
+    diag_factor_tile(d, rowblk, Cs, wst, tid);    // scratch: the W stages + coordinate arrays
+    STEP_PHASE(10);
+    return;
+  }
   AccStrip sy;
   acc_zero(sy);
   {
@@ -378,19 +395,7 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv, int S, int nt
     const int c = tid & (NB - 1);
     if (x == 0) {
       // ---- 5. rowblk == i + 1: the Schur complement is complete; factor the next diagonal tile ----
-      if (i > 0 && diag_i8) {
-        // park -L_ri L_ri^T in the slot matrix, form -sum_{k<i} L_rk L_rk^T on the int8 path, add K_rr
-#pragma unroll 16
-        for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
-          if (c <= r) Sg[(size_t)r * ld + c] = Cs[r * LDC + c];
-        __syncthreads();
-        potrf_mainloop_i8(d, rowblk, i, reinterpret_cast<unsigned char*>(smem), Cs, bars, &tmem_slot, csd, tid,
-                          I8M_DIAG, false, true, tphase, phbase);
-#pragma unroll 16
-        for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
-          if (c <= r) Cs[r * LDC + c] += Sg[(size_t)r * ld + c];
-        add_aug_tile(d, rowblk * NB, rowblk * NB, xr, xr, yr, Cs, tid, true);
-      } else if (i > 0) {
+      if (i > 0) {                     // (the int8 path has left above)
 #pragma unroll 16
         for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB)
           if (c <= r) Cs[r * LDC + c] += Sg[(size_t)r * ld + c];
