@@ -344,15 +344,21 @@ __device__ __noinline__ void diag_factor_tile(const SlotDesc& d, int i, double* 
   double* Wd = d.Wd + (size_t)i * NB * NB;
   double* Ut = d.A + (size_t)row0 * ld + row0;
   {
+    // W_ii is what the tiles of step i multiply by.  L_ii is read back only for the last diagonal block (prediction
+    // reduction) and by the debug extraction, the FP64 copy of U_ii only by the FP64 K^-1 kernel, the debug extraction and -
+    // the block that holds column n - the alpha column of the gradient: slots whose consumers all read the planes
+    // (SlotDesc::skip_fp64) store neither.
+    const bool st_l = !(d.skip_fp64 && i < d.T - 1);
+    const bool st_u = !(d.skip_fp64 && d.Uq8 != nullptr && (i + 1) * NB <= n);
     const int c = tid & (NB - 1);
     for (int r = tid >> 7; r < NB; r += GPSAT_THREADS / NB) {
       double lv, wv, uv;
       if (c < r) { lv = Cs[r * LDD + c]; wv = Cs[c * LDD + r]; uv = 0.0; }
       else if (c == r) { lv = Cs[r * LDD + r]; wv = wdiag[r]; uv = wv; }
       else { lv = 0.0; wv = 0.0; uv = Cs[r * LDD + c]; }
-      Ld[r * NB + c] = lv;
+      if (st_l) Ld[r * NB + c] = lv;
       Wd[r * NB + c] = wv;
-      Ut[(size_t)r * ld + c] = uv;
+      if (st_u) Ut[(size_t)r * ld + c] = uv;
     }
   }
   // later trtri tiles and the gradient's K^-1 products read U_ii on the int8 path
