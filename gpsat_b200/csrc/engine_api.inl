@@ -130,6 +130,7 @@ int gpsat_engine_create(int device, gpsat_engine** out) {
   if (const char* dp = getenv("GPSAT_B200_DIAGSUM")) h->e.i8_diag_sum = strcmp(dp, "0") != 0;
   if (const char* rp = getenv("GPSAT_B200_RHO_MAX")) h->e.i8_rho_max = std::max(0.0, atof(rp));
   if (const char* rp = getenv("GPSAT_B200_RHO_LOW")) h->e.i8_rho_low = std::max(0.0, atof(rp));
+  if (const char* rp = getenv("GPSAT_B200_TIER_GUARD")) h->e.i8_tier_guard = std::max(0.0, atof(rp));
   h->e.num_sms = prop.multiProcessorCount;
   *out = h;
   return 0;

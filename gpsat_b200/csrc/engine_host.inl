@@ -5,6 +5,7 @@ namespace gpsat {
 // profiles/r02_precision_envelope.md.
 constexpr double I8_RHO_MAX_DEFAULT = 4096.0;
 constexpr double I8_RHO_LOW_DEFAULT = 32.0;
+constexpr double I8_TIER_GUARD_DEFAULT = 1e-5;
 
 struct DevBuf {
   void* p = nullptr;
@@ -56,6 +57,7 @@ struct Engine {
   // precision rule (slot_set_theta in engine.cu): evaluations with (var + noise) / noise above this run on FP64 mma.sync
   double i8_rho_max = I8_RHO_MAX_DEFAULT;
   double i8_rho_low = I8_RHO_LOW_DEFAULT;
+  double i8_tier_guard = I8_TIER_GUARD_DEFAULT;
   DevBuf bLq, bUq8, bynorm;
   bool profile = false;
   std::vector<cudaEvent_t> evpool;
@@ -180,6 +182,7 @@ static int engine_load_batch(Engine& g, const gpsat_batch* b, int mem, bool with
   out.i8_rho_max = g.i8_rho_max;
   out.i8_rho_low = g.i8_rho_low;
   out.skip_fp64 = 0;
+  out.i8_tier_guard = g.i8_tier_guard;
   if (g.i8_step && E > 0) {
     if (g.bynorm.ensure(E * 8)) return 1;
     ynorm_kernel<<<(unsigned)E, 128, 0, g.stream>>>(out.off_n, out.y, g.bynorm.as<double>());
