@@ -171,6 +171,7 @@ static void begin_call(Engine& g) {
   cudaSetDevice(g.device);
   g.stats = gpsat_stats{};
   g.evtype.clear();
+  g.evcount.clear();
   cudaEventRecord(g.ev0, g.stream);
 }
 // Every product call ends here.  A bounded barrier wait of the int8 pipeline that gave up (mbar_wait in i8mma.cuh)

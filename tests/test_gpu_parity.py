@@ -633,3 +633,31 @@ def test_i8_timeout_fails_the_call(engine):
     for e, (X, y, _) in enumerate(experts):
         v, _ = gpr.lml_and_grad("Matern32", X, y, theta[e])
         assert abs(lml[e] - v) <= RTOL_FIXED * abs(v)
+
+
+def test_low_tier_guard_keeps_the_search_path(engine):
+    """During a fit the low-rho tier is offered only while the line search expects a decrease above 1e-5 |f|
+    (lbfgs_kernel in engine.cu): its noise of ~1e-10 |f| must not cost trial steps in the last iterations.  48 c2-shaped
+    experts (rho = 3 .. 35 at the optimum: all inside the tier), optimised with the tier on and off: same status, the
+    optimised LML equal to 1e-8, and the number of evaluations per expert the same up to the +-few steps any change of
+    rounding causes on a flat likelihood (without the guard single experts needed 20+ evaluations more)."""
+    import dataclasses
+    from gpsat_b200 import synthetic as syn
+    spec = dataclasses.replace(syn.WORKLOADS["c2"], E=48, n_lo=300, n_hi=700, m_lo=5, m_hi=9)
+    batch = syn.make_batch(spec, seed=3)
+    th0, tk, ta, tb, tr = syn.default_fit_setup(spec, batch.E)
+    res = {}
+    try:
+        for tier in (True, False):
+            engine.set_precision_low_tier(tier)
+            res[tier] = engine.fit(batch, th0, tk, ta, tb, tr)
+    finally:
+        engine.set_precision_low_tier(True)
+    a, b = res[True], res[False]
+    np.testing.assert_array_equal(a.status, b.status)
+    assert np.all(a.status == 0)
+    np.testing.assert_allclose(a.lml, b.lml, rtol=1e-8)
+    dn = np.abs(a.n_evals.astype(int) - b.n_evals.astype(int))
+    assert dn.max() <= 6 and dn.mean() <= 0.5, (dn.max(), dn.mean(), a.n_evals, b.n_evals)
+    rho = (a.theta[:, 3] + a.theta[:, 4]) / a.theta[:, 4]
+    assert np.all(rho <= 64)                                  # the experts really live where the tier applies
