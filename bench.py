@@ -594,6 +594,11 @@ def run_ours(args):
                 sweep[kind]["status_counts"] = r["rank0"]["status_counts"]
                 sweep[kind]["step_kernel_frac"] = r["rank0"]["step_kernel_frac"]
             extra["c2_kernel_sweep"] = sweep
+            # the reference-facing top-level call: LocalExpertOI.run fed from DataFrames (selection on the GPU, one fit + one
+            # predict call for all experts, result tables), wall clock of the second run - unpinned pandas inputs included
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import driver_bench
+            extra["driver_local_expert_oi_500"] = driver_bench.run_driver(500, None)
 
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
