@@ -738,6 +738,7 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
     t_sel = time.time()
     # ---- phase B ----
     success = np.zeros(K, bool)
+    mean_evals = 0.0
     if K and optimise:
         tol = opt_kwargs.pop("tol", None)
         kw = {} if tol is None else {"ftol": float(tol), "pgtol": float(tol)}
@@ -749,6 +750,7 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
         ok_theta = res.status != _lib.STATUS_NOT_PD
         theta = np.where(ok_theta[:, None], res.theta, theta)
         success = res.status == _lib.STATUS_OK
+        mean_evals = float(np.mean(res.n_evals))
     if K and predict:
         out = eng.predict(batch, theta)
         objective = -np.asarray(out["lml"])
@@ -815,7 +817,8 @@ def _run_vectorised(self, optimise, predict, min_obs, table_suffix, config_id):
                 df.index = midx(locs[keep])
                 tables[name + table_suffix] = df
                 row_expert[name + table_suffix] = keep.copy()
-    self.timings = {"select_s": t_sel - t0, "engine_s": t_fit - t_sel, "tables_s": time.time() - t_fit}
+    self.timings = {"select_s": t_sel - t0, "engine_s": t_fit - t_sel, "tables_s": time.time() - t_fit,
+                    "mean_evals_per_expert": mean_evals}
     self._row_expert = row_expert          # expert index (row of self.expert_locs) of every table row
     return tables
 
