@@ -120,6 +120,7 @@ static int engine_setup_kernels() {
 #undef I8P_ATTR
   CUDA_TRY(cudaFuncSetAttribute(sgpr_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SGPR_GEMM_SMEM_BYTES));
   CUDA_TRY(cudaFuncSetAttribute(vff_grad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, VFF_GRAD_SMEM_BYTES));
+  CUDA_TRY(cudaFuncSetAttribute(vff_dim_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, VFF_DIM_SMEM_BYTES));
   return 0;
 }
 

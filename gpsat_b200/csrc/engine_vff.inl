@@ -51,7 +51,7 @@ static int vff_setup(Engine& g, const gpsat_batch* batch, const gpsat_vff_domain
     int64_t M = 1;
     for (int dd = 0; dd < D; ++dd) {
       const int nf = dom->nfreq[e * D + dd];
-      REQUIRE(nf >= 1 && 2 * nf - 1 <= VFF_MD_MAX, "nfreq out of range [1, 64]");
+      REQUIRE(nf >= 1 && 2 * nf - 1 <= VFF_MD_MAX, "nfreq out of range [1, 128]");
       REQUIRE(dom->a[e * D + dd] < dom->b[e * D + dd], "vff domain needs a < b");
       M *= 2 * nf - 1;
     }
@@ -117,7 +117,7 @@ static int vff_launch_eval(Engine& g, const VffCall& c, bool with_grad, bool wit
   sgpr_gemm_kernel<<<dim3(ntl * c.nsplit, S), GPSAT_THREADS, SGPR_GEMM_SMEM_BYTES, st>>>(c.sds, SGPR_GEMM_SYRK, c.nsplit, 0);
   sgpr_reduce_kernel<<<dim3(std::min(256, (c.Mp * c.Mp + 255) / 256), S), 256, 0, st>>>(c.sds, c.nsplit, 0);
   // this evaluation
-  vff_dim_kernel<<<dim3(D, S), 128, 0, st>>>(c.descs);
+  vff_dim_kernel<<<dim3(D, S), 128, VFF_DIM_SMEM_BYTES, st>>>(c.descs);
   g.stats.kernel_launches += 5;
   if (with_pred) {
     vff_feat_kernel<<<dim3((c.mpad + 255) / 256, D, S), 256, 0, st>>>(c.descs, 1);

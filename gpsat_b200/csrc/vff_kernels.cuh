@@ -24,7 +24,8 @@
 namespace gpsat {
 
 constexpr int VFF_DMAX = 3;
-constexpr int VFF_MD_MAX = 128;          // features per dimension (2 * frequencies - 1)
+constexpr int VFF_MD_MAX = 256;          // features per dimension (2 * frequencies - 1): up to 128 frequencies
+constexpr int VFF_DIM_SMEM_BYTES = 30 * VFF_MD_MAX * 8;      // per-feature tables of vff_dim_kernel (dynamic: 60 KB)
 constexpr int VFF_NPART = 16;            // per-tile partial sums, see vff_grad_kernel
 constexpr int VFF_NMAT = 6;              // K, dK/dl, dK/dv, K^-1, dK^-1/dl, dK^-1/dv
 
@@ -159,7 +160,16 @@ __global__ void __launch_bounds__(128) vff_dim_kernel(const VffDesc* __restrict_
   const int dim = blockIdx.x;
   if (dim >= d.D) return;
   constexpr int MX = VFF_MD_MAX;
-  __shared__ double dv[MX], ddp[2][MX], W[3][MX], dW[2][3][MX], R[3][MX], Y[3][MX], Yd[2][3][MX], Ep[2][3][MX];
+  // per-feature tables (30 rows of MX doubles) in dynamic shared memory
+  extern __shared__ double vff_dim_sm[];
+  double* dv = vff_dim_sm;                                                          // [MX]
+  double (*ddp)[MX] = reinterpret_cast<double (*)[MX]>(vff_dim_sm + MX);            // [2][MX]
+  double (*W)[MX] = reinterpret_cast<double (*)[MX]>(vff_dim_sm + 3 * MX);          // [3][MX]
+  double (*dW)[3][MX] = reinterpret_cast<double (*)[3][MX]>(vff_dim_sm + 6 * MX);   // [2][3][MX]
+  double (*R)[MX] = reinterpret_cast<double (*)[MX]>(vff_dim_sm + 12 * MX);         // [3][MX]
+  double (*Y)[MX] = reinterpret_cast<double (*)[MX]>(vff_dim_sm + 15 * MX);         // [3][MX]
+  double (*Yd)[3][MX] = reinterpret_cast<double (*)[3][MX]>(vff_dim_sm + 18 * MX);  // [2][3][MX]
+  double (*Ep)[3][MX] = reinterpret_cast<double (*)[3][MX]>(vff_dim_sm + 24 * MX);  // [2][3][MX]
   __shared__ double S3[9], C3[9], H[2][9], G[2][9], CGC[2][9], CH[2][9], red[128];
   __shared__ double logdetS;
   const int tid = threadIdx.x, Md = d.Md[dim], nf = d.nf[dim];

@@ -670,7 +670,7 @@ class B200VFFModel(B200GPRModel):
     *last* dimension's kernel, because ``GPR_kron`` registers that one as ``model.kernel``
     (``vff.py:572``, ``gpflow_models.py:281-284``).  ``domain_size=None`` (which raises ``TypeError``
     in the reference, ``vff_model.py:177``) selects the data range +- 1e-8, the branch the reference
-    intended (``:181-184``).  At most 3 input dimensions and 64 frequencies per dimension.
+    intended (``:181-184``).  At most 3 input dimensions and 128 frequencies per dimension.
     """
 
     def __init__(self, data=None, coords_col=None, obs_col=None, coords=None, coords_scale=None, obs=None,
@@ -720,7 +720,7 @@ class B200VFFModel(B200GPRModel):
             nf = [int(k) for k in num_inducing_features]
             nf = nf * D if len(nf) == 1 else nf
         assert len(nf) == D, "Number of ms must match number of kernels."
-        assert all(1 <= k <= 64 for k in nf), "num_inducing_features must be in [1, 64] per dimension"
+        assert all(1 <= k <= 128 for k in nf), "num_inducing_features must be in [1, 128] per dimension"
         self.vff_nfreq = np.asarray(nf, dtype=np.int32)
         P = 2 * D + 1
         self._theta = np.concatenate([ls, var, [1.0]])

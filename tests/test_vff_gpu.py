@@ -42,7 +42,7 @@ def _pre(e):
     return vff.Precomputed(e["X"], e["y"], e["a"], e["b"], [np.arange(k) for k in e["nfreq"]])
 
 
-SHAPES = {1: [(200, [10], 30), (129, [64], 0), (500, [33], 140), (64, [3], 5)],
+SHAPES = {1: [(200, [10], 30), (129, [64], 0), (500, [33], 140), (64, [3], 5), (400, [128], 20), (300, [100], 7)],
           2: [(300, [6, 5], 17), (130, [8, 8], 0), (700, [12, 6], 140), (257, [3, 20], 5), (64, [1, 2], 3)],
           3: [(300, [3, 3, 2], 17), (400, [5, 4, 3], 40), (150, [2, 2, 2], 0)]}
 
@@ -139,9 +139,9 @@ def test_bad_inputs(engine):
     bad = dict(ex, a=np.array([ex["X"].min() + 0.1]))
     with pytest.raises(RuntimeError):
         engine.vff_elbo(_batch("Matern32", [bad]), _dom([bad]), theta)           # data outside (a, b)
-    big = dict(ex, nfreq=np.array([65], dtype=np.int32))
+    big = dict(ex, nfreq=np.array([129], dtype=np.int32))
     with pytest.raises(RuntimeError):
-        engine.vff_elbo(_batch("Matern32", [big]), _dom([big]), theta)           # > 128 features / dim
+        engine.vff_elbo(_batch("Matern32", [big]), _dom([big]), theta)           # > 256 features / dim
 
 
 def test_vff_model_driver_sequence_and_batched(engine):
