@@ -4,6 +4,7 @@
 // in int64 / FP64.  Three modes, each bounded (no unbounded spin: a wait that does not complete
 // sets an error flag and returns):
 //   check : one 128 x 128 x 32 int8 MMA against the host                     (layout / descriptor)
+//   mix   : the rate stream of one thread next to FP64 / FP32 fused multiply-adds in warps 2..7: do they overlap?
 //   rate  : resident operands, 36 MMAs per 32-wide slab, N = 64 / 128 / 256     (int8 TOPS per GPU)
 //   emul  : C[128 x 128] = A[128 x K] B[128 x K]^T in FP64 via S slices, against a host FP64 product,
 //           timed on 148 x 4 CTAs next to the DMMA main loop of tools/mainloop_probe.cu
@@ -152,6 +153,99 @@ __global__ void __launch_bounds__(128, 1) rate_kernel(int iters, int* __restrict
   tc_fence_before();
   __syncthreads();
   if (warp == 0) tmem_dealloc(tb, 512);
+}
+
+// ---- mode mix -------------------------------------------------------------------------------------
+// Does vector arithmetic of the other warps overlap with the int8 MMA stream of one thread?  256 threads; thread 0 issues
+// `iters` slabs of 36 MMAs (operands resident, as in mode rate, N = 128); warps 2..7 run `nf` rounds of 16 independent
+// fused multiply-adds per thread (KIND 0: FP64, 1: FP32).  out[2 b] = cycles of the MMA stream (issue to completion),
+// out[2 b + 1] = cycles of warp 2's arithmetic, for CTA b.
+template <int KIND>
+__global__ void __launch_bounds__(256, 1) mix_kernel(int iters, int nf, long long* __restrict__ out, double seed,
+                                                     int* __restrict__ err) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint32_t tmem_base;
+  __shared__ __align__(8) uint64_t bar;
+  constexpr int N = 128, APL = 128 * 32, BPL = N * 32;
+  uint8_t* sa = smem;
+  uint8_t* sb = smem + 8 * APL;
+  const int tid = threadIdx.x, warp = tid >> 5;
+  for (int i = tid; i < 8 * APL + 8 * BPL; i += 256) smem[i] = (uint8_t)((i * 37 + 11) & 3);
+  if (tid == 0) { mbar_init(smem_u32(&bar), 1); asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+  if (warp == 0) tmem_alloc(smem_u32(&tmem_base), 512);
+  fence_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tb = tmem_base;
+  if (tid == 0) {
+    const long long t0 = clock64();
+    for (int it = 0; it < iters; ++it)
+      for (int g = 0; g < 8; ++g)
+        for (int s = 0; s <= g; ++s)
+          mma_i8(tb + (uint32_t)((g % 4) * N), umma_desc(smem_u32(sa + s * APL), 128 * 16, 128),
+                 umma_desc(smem_u32(sb + (g - s) * BPL), N * 16, 128), idesc_i8(N), 1);
+    mma_commit(smem_u32(&bar));
+    const bool ok = mbar_wait(smem_u32(&bar), 0);
+    out[2 * blockIdx.x] = clock64() - t0;
+    if (!ok) *err = 1;
+  } else if (warp >= 2) {
+    const long long t0 = clock64();
+    if (KIND == 0) {
+      double f[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) f[i] = seed + tid + i;
+      for (int it = 0; it < nf; ++it)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = fma(f[i], seed, 0.5);
+      double a = 0.0;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) a += f[i];
+      if (a == 1.2345) out[2 * gridDim.x] = 1;
+    } else {
+      float f[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) f[i] = (float)seed + tid + i;
+      for (int it = 0; it < nf; ++it)
+#pragma unroll
+        for (int i = 0; i < 16; ++i) f[i] = fmaf(f[i], (float)seed, 0.5f);
+      float a = 0.f;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) a += f[i];
+      if (a == 1.2345f) out[2 * gridDim.x] = 1;
+    }
+    if (tid == 64) out[2 * blockIdx.x + 1] = clock64() - t0;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tb, 512);
+}
+
+template <int KIND>
+static void run_mix(bool first, int nf_full) {
+  const int grid = 148, iters_full = 400;
+  const int smem = 16 * 128 * 32;
+  int* derr; CK(cudaMalloc(&derr, 4)); CK(cudaMemset(derr, 0, 4));
+  long long* dout; CK(cudaMalloc(&dout, (2 * grid + 1) * sizeof(long long)));
+  CK(cudaFuncSetAttribute(mix_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  printf("%s\"%s\": {", first ? "" : ", ", KIND == 0 ? "fp64" : "fp32");
+  const int cfg[3][2] = {{iters_full, 0}, {0, nf_full}, {iters_full, nf_full}};
+  const char* names[3] = {"mma_alone", "fma_alone", "both"};
+  for (int v = 0; v < 3; ++v) {
+    std::vector<long long> h(2 * grid + 1);
+    for (int rep = 0; rep < 2; ++rep) {                       // the first launch warms up
+      CK(cudaMemset(dout, 0, (2 * grid + 1) * sizeof(long long)));
+      mix_kernel<KIND><<<grid, 256, smem>>>(cfg[v][0], cfg[v][1], dout, 0.999, derr);
+      CK(cudaDeviceSynchronize());
+    }
+    CK(cudaMemcpy(h.data(), dout, (2 * grid + 1) * sizeof(long long), cudaMemcpyDeviceToHost));
+    double m = 0, f = 0;
+    for (int b = 0; b < grid; ++b) { m += h[2 * b]; f += h[2 * b + 1]; }
+    printf("%s\"%s\": {\"mma_kcycles\": %.1f, \"fma_kcycles\": %.1f}", v ? ", " : "", names[v], m / grid / 1e3, f / grid / 1e3);
+  }
+  int err; CK(cudaMemcpy(&err, derr, 4, cudaMemcpyDeviceToHost));
+  printf(", \"timeout\": %d}", err);
+  CK(cudaFree(dout)); CK(cudaFree(derr));
 }
 
 // ---- mode emul ------------------------------------------------------------------------------------
@@ -384,6 +478,7 @@ int main(int argc, char** argv) {
   int rc = 0;
   if (!strcmp(mode, "check")) rc = run_check();
   else if (!strcmp(mode, "rate")) { printf("\"rate\": {"); run_rate<64>(true); run_rate<128>(false); run_rate<256>(false); printf("}"); }
+  else if (!strcmp(mode, "mix")) { printf("\"mix\": {"); run_mix<0>(true, 20000); run_mix<1>(false, 80000); printf("}"); }
   else if (!strcmp(mode, "emul")) { printf("\"emul\": {"); run_emul<6>(true); run_emul<7>(false); run_emul<8>(false); printf("}"); }
   printf("}\n");
   return rc;
