@@ -10,6 +10,13 @@ constexpr int I8L_OPER_B = I8L_S * I8_SLAB_B;            // planes of one operan
 constexpr int I8L_STAGE_B = 2 * I8L_OPER_B;
 constexpr int I8L_NST = 3;
 constexpr int I8L_PIPE_B = I8L_NST * I8L_STAGE_B;        // 192 KB: exactly the C tile + the W stages it aliases
+// Pass 0 moves planes 0..3 only, so every stage holds two slabs: a ring of 2 I8L_NST half stages with its own barriers.
+// Half stage h: A planes at i8l_half_off(h), B planes I8L_OPER_B behind them.
+constexpr int I8L_NH = 2 * I8L_NST;
+constexpr int I8L_NBAR = 2 * I8L_NST + 1 + 2 * I8L_NH;   // full[NST], empty[NST], accumulators, full0[NH], empty0[NH]
+__host__ __device__ constexpr uint32_t i8l_half_off(int h) {
+  return (uint32_t)(h >> 1) * I8L_STAGE_B + (uint32_t)(h & 1) * 4 * I8_SLAB_B;
+}
 static_assert(I8L_PIPE_B <= (SM_TILE_D + SM_WST_D) * 8, "int8 pipeline must fit in the tile + W stage area");
 constexpr int I8L_MAX_T = 256;                           // int32 accumulators: k <= 32768 keeps |G_g| < 2^31
 

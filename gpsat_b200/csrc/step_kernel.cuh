@@ -38,15 +38,18 @@ namespace gpsat {
 // MMA issue of one pass over k by the calling thread: for every slab all slice pairs (s, t) of the groups s + t = G0 .. G1-1
 // (accumulator g - G0), straight-line code per slab - the group range is a template parameter because a run-time test in
 // front of each tcgen05.mma costs about 20 cycles of the single issuing thread (measured: 0.1 us per slab).
-template <int G0, int G1>
-__device__ __forceinline__ bool i8_issue_pass(int nslabs, int it0, uint32_t full0, uint32_t empty0, uint32_t accb, int pass,
+// HALF: the ring of pass 0 (I8L_NH half stages, i8slice.cuh), else the I8L_NST full stages; each ring has its own barriers
+// and counts its slabs from 0.
+template <int G0, int G1, bool HALF>
+__device__ __forceinline__ bool i8_issue_pass(int nslabs, uint32_t full0, uint32_t empty0, uint32_t accb, int pass,
                                               uint64_t desc0, bool same, uint32_t tb, bool ok) {
+  constexpr int NST = HALF ? I8L_NH : I8L_NST;
   for (int sl = 0; sl < nslabs; ++sl) {
-    const int itm = it0 + sl, st = itm % I8L_NST;
-    ok = ok && mbar_wait(full0 + 8 * st, (itm / I8L_NST) & 1);
+    const int st = sl % NST;
+    ok = ok && mbar_wait(full0 + 8 * st, (sl / NST) & 1);
     if (!ok) break;
     tc_fence_after();
-    const uint64_t adesc = desc0 + (uint64_t)((st * I8L_STAGE_B) >> 4);
+    const uint64_t adesc = desc0 + (uint64_t)((HALF ? i8l_half_off(st) : (uint32_t)(st * I8L_STAGE_B)) >> 4);
     const uint64_t bdesc = same ? adesc : adesc + (uint64_t)(I8L_OPER_B >> 4);
     const uint32_t acc0 = sl == 0 ? 0u : 1u;
 #pragma unroll
@@ -78,7 +81,7 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
   const bool same = mode == I8M_DIAG;
   const int warp = tid >> 5, lane = tid & 31;
   if (tid == 0) {
-    for (int b = 0; b < 2 * I8L_NST + 1; ++b) {
+    for (int b = 0; b < I8L_NBAR; ++b) {
       if (!first) asm volatile("mbarrier.inval.shared::cta.b64 [%0];\n" :: "r"(smem_u32(&bars[b])) : "memory");
       mbar_init(smem_u32(&bars[b]), 1);
     }
@@ -90,7 +93,8 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
   __syncthreads();
   tc_fence_after();
   const uint32_t tb = *tmem_slot;
-  const uint32_t full0 = smem_u32(&bars[0]), empty0 = smem_u32(&bars[I8L_NST]), accb = smem_u32(&bars[2 * I8L_NST]);
+  const uint32_t full1 = smem_u32(&bars[0]), empty1 = smem_u32(&bars[I8L_NST]), accb = smem_u32(&bars[2 * I8L_NST]);
+  const uint32_t fullh = smem_u32(&bars[2 * I8L_NST + 1]), emptyh = smem_u32(&bars[2 * I8L_NST + 1 + I8L_NH]);
   const uint32_t pipe_s = smem_u32(pipe);
   const uint64_t desc0 = umma_desc_kmajor(pipe_s, NB * 16, 128);
   const int row = (warp & 3) * 32 + lane, chalf = warp >> 2;        // accumulator row, 64-column half
@@ -111,29 +115,44 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
   for (int pass = 0; pass < 2; ++pass) {
     const int np = pass == 0 ? 4 : SG;                        // planes per operand this pass
     const int ng = pass == 0 ? 4 : SG - 4;                    // groups accumulated (and drained) this pass
+    const int nst = pass == 0 ? I8L_NH : I8L_NST;             // pass 0: ring of half stages (two slabs per stage)
+    const uint32_t full0 = pass == 0 ? fullh : full1, empty0 = pass == 0 ? emptyh : empty1;
     if (warp == 0) {
-      // ---- producer: one bulk copy per operand and slab (tiles (r, 0..i-1) are consecutive in the packing) ----
+      // ---- producer of the A planes: one bulk copy per slab (tiles (r, 0..i-1) are consecutive in the packing).  It also
+      // announces the bytes of both operands; the B copies come from a lane of warp 2, because one thread gets a bulk copy
+      // out only every 0.285 us whatever its size (tools/bulk_copy_probe.cu), which bounded pass 0 at two requests per slab ----
       if (elect_one())
       for (int sl = 0; sl < nslabs; ++sl) {
-        const int itp = pass * nslabs + sl, st = itp % I8L_NST;
-        if (itp >= I8L_NST) ok = ok && mbar_wait(empty0 + 8 * st, ((itp / I8L_NST) - 1) & 1);
+        const int st = sl % nst;
+        if (sl >= nst) ok = ok && mbar_wait(empty0 + 8 * st, ((sl / nst) - 1) & 1);
         if (!ok) break;
-        const uint32_t fb = full0 + 8 * st, sbase = pipe_s + st * I8L_STAGE_B;
+        const uint32_t fb = full0 + 8 * st, sbase = pipe_s + (pass == 0 ? i8l_half_off(st) : (uint32_t)(st * I8L_STAGE_B));
         mbar_expect_tx(fb, (same ? 1 : 2) * np * I8_SLAB_B);
         bulk_g2s(sbase, ga0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
-        if (!same) bulk_g2s(sbase + I8L_OPER_B, gb0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
+      }
+    } else if (warp == 2 && !same) {
+      // ---- producer of the B planes.  Its complete_tx may reach the full barrier before the A producer's expect_tx: the
+      // transaction count is then negative for a moment while the pending arrival keeps the phase open (as with multicast
+      // copies issued by a peer CTA).  It cannot run a round ahead: the empty barrier of round k opens after full round k ----
+      if (elect_one())
+      for (int sl = 0; sl < nslabs; ++sl) {
+        const int st = sl % nst;
+        if (sl >= nst) ok = ok && mbar_wait(empty0 + 8 * st, ((sl / nst) - 1) & 1);
+        if (!ok) break;
+        bulk_g2s(pipe_s + (pass == 0 ? i8l_half_off(st) : (uint32_t)(st * I8L_STAGE_B)) + I8L_OPER_B,
+                 gb0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, full0 + 8 * st);
       }
     } else if (warp == 1) {
       // ---- MMA issue: all slice pairs of the pass for every slab ----
       if (elect_one()) {
-        if (pass == 0) ok = i8_issue_pass<0, 4>(nslabs, 0, full0, empty0, accb, 0, desc0, same, tb, ok);
-        else if (SG == I8L_S) ok = i8_issue_pass<4, I8L_S>(nslabs, nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
-        else ok = i8_issue_pass<4, I8L_S - 1>(nslabs, nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
+        if (pass == 0) ok = i8_issue_pass<0, 4, true>(nslabs, full0, empty0, accb, 0, desc0, same, tb, ok);
+        else if (SG == I8L_S) ok = i8_issue_pass<4, I8L_S, false>(nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
+        else ok = i8_issue_pass<4, I8L_S - 1, false>(nslabs, full0, empty0, accb, 1, desc0, same, tb, ok);
       }
-    } else if (pass == 0 && xr != nullptr && tid >= 64) {
-      // warps 2..7 have nothing to do during the loop: they fetch the coordinates the covariance epilogue needs
-      load_block_coords(d, rowblk * NB, xr, yr, tid - 64, GPSAT_THREADS - 64);
-      load_block_coords(d, i * NB, xc, yc, tid - 64, GPSAT_THREADS - 64);
+    } else if (pass == 0 && xr != nullptr && tid >= 96) {
+      // warps 3..7 have nothing to do during the loop: they fetch the coordinates the covariance epilogue needs
+      load_block_coords(d, rowblk * NB, xr, yr, tid - 96, GPSAT_THREADS - 96);
+      load_block_coords(d, i * NB, xc, yc, tid - 96, GPSAT_THREADS - 96);
     }
     __syncwarp();
     ok = __all_sync(0xffffffffu, ok);         // warp-uniform: tcgen05.ld below is warp-collective
@@ -235,7 +254,7 @@ step_kernel(const SlotDesc* __restrict__ slots, int i, int do_inv, int S, int nt
 
   extern __shared__ __align__(128) double smem_step[];
   double* smem = smem_step;
-  __shared__ __align__(8) uint64_t bars[2 * I8L_NST + 1];
+  __shared__ __align__(8) uint64_t bars[I8L_NBAR];
   __shared__ uint32_t tmem_slot;
   __shared__ double csd[NB];
   double* Cs = smem;                       // aliases the pipeline stages
