@@ -128,7 +128,7 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
         if (!ok) break;
         const uint32_t fb = full0 + 8 * st, sbase = pipe_s + (pass == 0 ? i8l_half_off(st) : (uint32_t)(st * I8L_STAGE_B));
         mbar_expect_tx(fb, (same ? 1 : 2) * np * I8_SLAB_B);
-        bulk_g2s(sbase, ga0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, fb);
+        bulk_g2s(sbase, ga0 + (size_t)(pass == 0 ? sl : nslabs - 1 - sl) * I8L_OPER_B, np * I8_SLAB_B, fb);
       }
     } else if (warp == 2 && !same) {
       // ---- producer of the B planes.  Its complete_tx may reach the full barrier before the A producer's expect_tx: the
@@ -140,7 +140,7 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
         if (sl >= nst) ok = ok && mbar_wait(empty0 + 8 * st, ((sl / nst) - 1) & 1);
         if (!ok) break;
         bulk_g2s(pipe_s + (pass == 0 ? i8l_half_off(st) : (uint32_t)(st * I8L_STAGE_B)) + I8L_OPER_B,
-                 gb0 + (size_t)sl * I8L_OPER_B, np * I8_SLAB_B, full0 + 8 * st);
+                 gb0 + (size_t)(pass == 0 ? sl : nslabs - 1 - sl) * I8L_OPER_B, np * I8_SLAB_B, full0 + 8 * st);
       }
     } else if (warp == 1) {
       // ---- MMA issue: all slice pairs of the pass for every slab ----
