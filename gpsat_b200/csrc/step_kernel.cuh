@@ -115,7 +115,7 @@ __device__ __forceinline__ void potrf_mainloop_i8(const SlotDesc& d, int rowblk,
   for (int pass = 0; pass < 2; ++pass) {
     const int np = pass == 0 ? 4 : SG;                        // planes per operand this pass
     const int ng = pass == 0 ? 4 : SG - 4;                    // groups accumulated (and drained) this pass
-    const int nst = pass == 0 ? I8L_NH : I8L_NST;             // pass 0: ring of half stages (two slabs per stage)
+    const int nst = pass == 0 ? I8L_NH : I8L_NST;             // pass 0: ring of half stages (two slabs per stage); pass 1 walks the slabs backwards: what pass 0 read last is still in L2, and the int32 sums are exact in any order
     const uint32_t full0 = pass == 0 ? fullh : full1, empty0 = pass == 0 ? emptyh : empty1;
     if (warp == 0) {
       // ---- producer of the A planes: one bulk copy per slab (tiles (r, 0..i-1) are consecutive in the packing).  It also
